@@ -1,0 +1,82 @@
+"""Pin the CPU oracle against outputs of the reference itself (tests/golden/*.npz). CPU only."""
+import numpy as np
+import pytest
+
+from oracle import qs_oracle as O
+from tests import _golden
+
+TOL = 1e-13
+
+
+def check_case(case, evaluate):
+    """evaluate(circuit, x) -> (U, J[P,N,N]); objective quantities are derived with the oracle's comparison math."""
+    for x, gold in zip(case.xs, case.samples):
+        U, J = evaluate(case.circuit, x)
+        J = np.array(J).reshape((-1,) + U.shape)
+        assert np.abs(U - gold["U"]).max() < TOL
+        if "J" in gold:
+            assert J.shape == gold["J"].shape
+            if J.size:
+                assert np.abs(J - gold["J"]).max() < TOL
+        else:
+            w = _golden.proj_weights(U.shape[0])
+            assert np.abs(J @ w - gold["J_proj"]).max() < 1e-12
+        for tname, T in case.targets.items():
+            f, g = O.matrix_distance_squared_jac(T, U, list(J))
+            assert abs(f - gold["f_" + tname]) < TOL
+            assert abs(O.matrix_distance_squared(T, U) - gold["dist_" + tname]) < TOL
+            if J.size:
+                assert np.abs(g - gold["g_" + tname]).max() < TOL
+            assert np.abs(O.matrix_residuals(T, U) - gold["r_" + tname]).max() < TOL
+            if J.size:
+                Jr = O.matrix_residuals_jac(T, U, list(J))
+                if "Jr_" + tname in gold:
+                    assert np.abs(Jr - gold["Jr_" + tname]).max() < TOL
+                else:
+                    w = _golden.proj_weights(Jr.shape[0])
+                    assert np.abs(w @ Jr - gold["Jr_" + tname + "_proj"]).max() < 1e-11
+
+
+@pytest.mark.parametrize("fname", _golden.ALL_FILES)
+def test_numpy_oracle_matches_reference_fixtures(fname):
+    for case in _golden.load(fname):
+        check_case(case, O.mat_jac)
+        for x, gold in zip(case.xs, case.samples):
+            assert np.abs(O.matrix(case.circuit, x) - gold["U"]).max() < TOL
+
+
+def test_constant_targets_match_reference():
+    import os
+    from qsearch_b200 import unitaries as mu
+    blob = np.load(os.path.join(_golden.GOLDEN_DIR, "targets.npz"))
+    for name in ["toffoli", "fredkin", "peres", "logical_or", "HHL", "mirogate", "sqrt_x", "cnot", "swap", "sqrt_cnot"]:
+        assert np.array_equal(getattr(mu, name), blob[name]), name
+    for n in (8, 16, 32):
+        assert np.array_equal(mu.qft(n), blob["qft{}".format(n)])
+    for key in blob.files:
+        if key.startswith("acnot_"):
+            n, c, t = map(int, key.split("_")[1:])
+            assert np.array_equal(mu.arbitrary_cnot(n, c, t), blob[key])
+
+
+@pytest.mark.reference
+def test_oracle_against_live_reference():
+    """In the build container: compare the oracle with the live reference on fresh random inputs."""
+    import sys
+    sys.path.insert(0, "/root/reference")
+    from qsearch import gatesets as rgs, gates as rg, comparison as rc, unitaries as ru
+    rng = np.random.default_rng(99)
+    for gs, n in [(rgs.QubitCNOTRing(), 4), (rgs.QubitCNOTLinear(), 3), (rgs.QubitCNOTRing(), 5)]:
+        layers = gs.search_layers(n)
+        c = rg.ProductGate(gs.initial_layer(n))
+        for _ in range(6):
+            c = c.appending(layers[int(rng.integers(len(layers)))][0])
+        x = rng.random(c.num_inputs) * 2 * np.pi
+        T = ru.qft(2 ** n)
+        U, J = c.mat_jac(x)
+        Uo, Jo = O.mat_jac(c, x)  # oracle walks the reference's own tree by class name
+        assert np.abs(U - Uo).max() < TOL and max(np.abs(a - b).max() for a, b in zip(J, Jo)) < TOL
+        assert np.abs(rc.matrix_residuals_jac(T, U, J) - O.matrix_residuals_jac(T, Uo, Jo)).max() < TOL
+        f, g = rc.matrix_distance_squared_jac(T, U, J)
+        fo, go = O.matrix_distance_squared_jac(T, Uo, Jo)
+        assert abs(f - fo) < TOL and np.abs(g - go).max() < TOL
