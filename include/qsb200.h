@@ -1,0 +1,160 @@
+/* qsb200.h -- C ABI of libqsb200.so: the B200-native (sm_100a) qsearch hot path.
+ *
+ * This is the boundary the reference crosses with PyO3 in qsrs/src/lib.rs (native_from_object :183-277,
+ * :543-554; PyGateWrapper.matrix / mat_jac :280-369; the native solver classes :391-539; the free functions
+ * matrix_distance_squared(_jac) / matrix_residuals(_jac) :558-629).  Here it is a flat C ABI: plain pointers and
+ * sizes, no torch / numpy types, loaded with ctypes (qsearch_b200/_lib.py).  INTEGRATION.md shows the binding a
+ * maintainer of the reference would add.
+ *
+ * Conventions
+ *   - complex128 matrices are row-major, interleaved (re, im) doubles: exactly NumPy's complex128 layout.
+ *   - qubit 0 is the most significant index bit (big endian, qsearch/unitaries.py:160).
+ *   - every function returns QSB_OK (0) or a negative error code; qsb_last_error() gives the message of the
+ *     last failure on the calling thread.  Nothing throws or aborts across the ABI.
+ *   - all host buffers are caller-owned; the library owns device memory behind opaque handles.
+ *   - a batch of "instances" = (program, parameter vector) pairs; parameters of a batch are one ragged
+ *     concatenation params[param_offset[i] .. +P_i), in instance order; gradients/Jacobians use the same order.
+ */
+#ifndef QSB200_H
+#define QSB200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define QSB_OK 0
+#define QSB_ERR_INVALID (-1)     /* bad argument / malformed program */
+#define QSB_ERR_CUDA (-2)        /* CUDA runtime failure (message has the CUDA error string) */
+#define QSB_ERR_NOMEM (-3)
+#define QSB_ERR_UNSUPPORTED (-4) /* e.g. more than QSB_MAX_QUBITS qubits */
+
+#define QSB_MAX_QUBITS 5
+
+/* Flat gate program: the lowered form of a ProductGate / KroneckerGate tree (qsearch/gates.py:845-1051).
+ * Ops are applied in array order, each one LEFT-multiplying the running unitary (gates.py:959). */
+enum qsb_opcode {
+  QSB_OP_RX = 1,    /* XGate      gates.py:132  1 param  */
+  QSB_OP_RY = 2,    /* YGate      gates.py:151  1 param  */
+  QSB_OP_RZ = 3,    /* ZGate      gates.py:170  1 param  */
+  QSB_OP_U1 = 4,    /* U1Gate     gates.py:387  1 param  */
+  QSB_OP_U2 = 5,    /* U2Gate     gates.py:358  2 params */
+  QSB_OP_U3 = 6,    /* U3Gate     gates.py:318  3 params */
+  QSB_OP_XZXZ = 7,  /* XZXZGate   gates.py:270  2 params */
+  QSB_OP_ZXZXZ = 8, /* ZXZXZGate  gates.py:208  3 params */
+  QSB_OP_CONST1 = 9, /* constant 2x2 on qubit q0; const_off -> 8 doubles in the pool */
+  QSB_OP_CNOT = 10,  /* CNOT(control q0, target q1): CNOTGate :604 / NonadjacentCNOTGate :696 (a row permutation) */
+  QSB_OP_CONSTK = 11 /* constant 2^k x 2^k on contiguous qubits q0..q0+k-1 (k = q1); const_off -> 2*4^k doubles */
+};
+
+typedef struct qsb_op {
+  int32_t opcode;    /* enum qsb_opcode */
+  int32_t q0;        /* qubit (1-qubit ops), control (CNOT), first qubit (CONSTK) */
+  int32_t q1;        /* target (CNOT), k (CONSTK), else 0 */
+  int32_t param_off; /* first parameter of this op within the circuit's parameter vector (param ops) */
+  int32_t const_off; /* offset in doubles into the constant pool (CONST1 / CONSTK) */
+  int32_t reserved;
+} qsb_op;
+
+typedef struct qsb_ctx qsb_ctx;
+typedef struct qsb_program qsb_program;
+typedef struct qsb_batch qsb_batch;
+
+/* what a batch run computes */
+enum qsb_what {
+  QSB_RUN_MATRIX = 1, /* U                       (Gate.matrix,  gates.py:946)                          */
+  QSB_RUN_MATJAC = 2, /* U, J_k = dU/dx_k        (Gate.mat_jac, gates.py:965)                          */
+  QSB_RUN_HS = 3,     /* f, grad f               (comparison.matrix_distance_squared_jac :37)           */
+  QSB_RUN_RESID = 4,  /* r, J_r                  (comparison.matrix_residuals :57 / _residuals_jac :66) */
+  QSB_RUN_DIST = 5,   /* f only                  (comparison.matrix_distance_squared :8)                */
+  QSB_RUN_LMSYS = 6   /* r'r, J_r'J_r, J_r'r     (what a Levenberg-Marquardt step consumes; J_r never stored) */
+};
+
+/* ---- context ------------------------------------------------------------------------------------------ */
+const char* qsb_last_error(void);
+int qsb_device_count(int* out_count);
+/* n_devices <= 0: use every visible device.  CUDA is first touched here (lazy; importing the shim is fork-safe). */
+int qsb_init(int n_devices, const int* device_ids, qsb_ctx** out_ctx);
+int qsb_shutdown(qsb_ctx* ctx);
+int qsb_ctx_num_devices(const qsb_ctx* ctx);
+const char* qsb_version(void);
+
+/* ---- programs (replaces native_from_object, qsrs/src/lib.rs:543-554) ------------------------------------ */
+int qsb_program_create(qsb_ctx* ctx, int n_qubits, int n_ops, const qsb_op* ops, int n_params,
+                       const double* const_pool, size_t const_len, qsb_program** out_prog);
+int qsb_program_destroy(qsb_ctx* ctx, qsb_program* prog);
+int qsb_program_num_params(const qsb_program* prog);
+int qsb_program_num_qubits(const qsb_program* prog);
+
+/* ---- host-buffer evaluation calls (replace PyGateWrapper.matrix / mat_jac and the objective functions) ---
+ * progs[n_programs]; prog_of_instance[n_instances] indexes progs; all programs must have the same qubit count.
+ * params: ragged concatenation, instance i uses the next P_i doubles.  Work is sharded over the context's
+ * devices in contiguous instance ranges; host<->device copies are part of the call. */
+int qsb_eval_matrix(qsb_ctx* ctx, int n_programs, const qsb_program* const* progs, int n_instances,
+                    const int32_t* prog_of_instance, const double* params,
+                    double* out_U /* [inst][N][N][2] */);
+int qsb_eval_mat_jac(qsb_ctx* ctx, int n_programs, const qsb_program* const* progs, int n_instances,
+                     const int32_t* prog_of_instance, const double* params,
+                     double* out_U /* [inst][N][N][2] */, double* out_J /* [sum P][N][N][2] */);
+int qsb_eval_hs_grad(qsb_ctx* ctx, int n_programs, const qsb_program* const* progs, int n_instances,
+                     const int32_t* prog_of_instance, const double* params, const double* target /* [N][N][2] */,
+                     double* out_f /* [inst] */, double* out_grad /* [sum P] */);
+int qsb_eval_distance(qsb_ctx* ctx, int n_programs, const qsb_program* const* progs, int n_instances,
+                      const int32_t* prog_of_instance, const double* params, const double* target,
+                      double* out_f /* [inst] */);
+/* out_Jr is [sum P][2 N^2]: row k = concat(ravel(Re K_k), ravel(Im K_k)), K_k = J_k T^dagger.  That is the memory
+ * the reference builds before its final .T (comparison.py:66-72); the shim returns the transposed view. */
+int qsb_eval_residuals_jac(qsb_ctx* ctx, int n_programs, const qsb_program* const* progs, int n_instances,
+                           const int32_t* prog_of_instance, const double* params, const double* target,
+                           double* out_r /* [inst][2 N^2] */, double* out_Jr /* [sum P][2 N^2] */);
+
+/* ---- device-resident batches (what bench.py times with inputs already in HBM; also used by the solvers) -- */
+int qsb_batch_create(qsb_ctx* ctx, int device_slot, int n_programs, const qsb_program* const* progs,
+                     int n_instances, const int32_t* prog_of_instance, qsb_batch** out_batch);
+int qsb_batch_destroy(qsb_batch* batch);
+int qsb_batch_set_params(qsb_batch* batch, const double* params, size_t n_doubles); /* H2D */
+int qsb_batch_set_target(qsb_batch* batch, const double* target);                   /* H2D, [N][N][2] */
+/* Launch on the batch's stream over instances [first, first+count); outputs land in device buffers sized for
+ * `count` instances.  If elapsed_ms != NULL the launch is bracketed by CUDA events on that stream and the call
+ * waits for completion; otherwise it returns after enqueueing. */
+int qsb_batch_run(qsb_batch* batch, int what, int first, int count, float* elapsed_ms);
+int qsb_batch_sync(qsb_batch* batch);
+/* Copy the outputs of the last run of `what` to host.  Unused pointers may be NULL.
+ *   MATRIX: a=U            MATJAC: a=U, b=J       HS: a=f, b=grad      DIST: a=f
+ *   RESID:  a=r, b=J_r     LMSYS:  a=r'r [inst], b=J'r [sum P], c=J'J [sum P_i^2] */
+int qsb_batch_fetch(qsb_batch* batch, int what, double* a, double* b, double* c);
+/* bytes of device output the last run of `what` wrote (for bandwidth accounting) */
+int qsb_batch_output_bytes(qsb_batch* batch, int what, int count, uint64_t* out_bytes);
+/* number of kernel launches issued by this context so far */
+int qsb_ctx_launch_count(const qsb_ctx* ctx, uint64_t* out);
+
+/* ---- batched on-device solvers (replace BFGS_Jac_SolverNative / LeastSquares_Jac_SolverNative,
+ *      qsrs/src/lib.rs:391-539, qsrs/src/solvers.rs:13-122; scipy drivers qsearch/solvers.py:138-163) -------- */
+typedef struct qsb_solver_opts {
+  int32_t max_iters;   /* LM: max Jacobian evaluations; <=0 -> 100*P like max_nfev (scipy) / max_num_iterations (Ceres) */
+  int32_t lbfgs_memory; /* L-BFGS history length, default 10 (qsrs/src/lib.rs:402-413) */
+  double ftol, xtol, gtol; /* <=0 -> 1e-8 defaults of scipy.least_squares(method='lm') */
+  double stop_value;   /* stop as soon as the objective (HS distance for L-BFGS, r'r/(2N) proxy for LM) < this; <=0 off */
+  double reserved[4];
+} qsb_solver_opts;
+
+/* One independent solve per instance, parameters stay on the device for the whole solve.
+ * x0 / out_x: ragged like params.  out_f: final HS distance 1-|Tr(T^dagger U)|/N per instance.
+ * out_iters: iterations used.  out_status: >0 converged reason, 0 iteration limit. */
+int qsb_solve_lm(qsb_ctx* ctx, int n_programs, const qsb_program* const* progs, int n_instances,
+                 const int32_t* prog_of_instance, const double* x0, const double* target,
+                 const qsb_solver_opts* opts, double* out_x, double* out_f, int32_t* out_iters,
+                 int32_t* out_status);
+int qsb_solve_lbfgs(qsb_ctx* ctx, int n_programs, const qsb_program* const* progs, int n_instances,
+                    const int32_t* prog_of_instance, const double* x0, const double* target,
+                    const qsb_solver_opts* opts, double* out_x, double* out_f, int32_t* out_iters,
+                    int32_t* out_status);
+
+/* ---- device micro-benchmarks (FP64 pipe / DMMA peak measured on the box; bench.py records them) ---------- */
+int qsb_measure_fp64_peak(qsb_ctx* ctx, int device_slot, int use_dmma, double* out_tflops);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* QSB200_H */

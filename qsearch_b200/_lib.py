@@ -1,0 +1,315 @@
+"""ctypes binding of libqsb200.so (include/qsb200.h).  No PyTorch, no CPU fallback.
+
+The library is located next to this file (built in-tree by ``__graft_entry__.build()`` /
+``python -m qsearch_b200.build``).  Nothing CUDA-related happens at import: the shared object is loaded and the
+context created on first use, so the package can be imported before a fork (hard part 4).
+If the library is missing, or no CUDA device is visible, every entry point raises -- there is no other path.
+"""
+import ctypes
+import os
+import threading
+
+import numpy as np
+
+from .lowering import OP_DTYPE
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_NAME = "libqsb200.so"
+
+RUN_MATRIX, RUN_MATJAC, RUN_HS, RUN_RESID, RUN_DIST, RUN_LMSYS = 1, 2, 3, 4, 5, 6
+
+_c_dp = ctypes.POINTER(ctypes.c_double)
+_c_ip = ctypes.POINTER(ctypes.c_int32)
+_vp = ctypes.c_void_p
+
+
+class QsbError(RuntimeError):
+    pass
+
+
+class SolverOpts(ctypes.Structure):
+    _fields_ = [("max_iters", ctypes.c_int32), ("lbfgs_memory", ctypes.c_int32), ("ftol", ctypes.c_double),
+                ("xtol", ctypes.c_double), ("gtol", ctypes.c_double), ("stop_value", ctypes.c_double),
+                ("reserved", ctypes.c_double * 4)]
+
+
+def _dp(a):
+    return None if a is None else a.ctypes.data_as(_c_dp)
+
+
+def _f64(a):
+    return np.ascontiguousarray(a, dtype="float64")
+
+
+class Library:
+    """One loaded copy of the C ABI + one context over the chosen devices."""
+
+    def __init__(self, path=None, devices=None):
+        path = path or os.path.join(_HERE, LIB_NAME)
+        if not os.path.exists(path):
+            raise QsbError("{} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                           "(qsearch_b200 has no CPU fallback)".format(path))
+        self.path = path
+        self.dll = ctypes.CDLL(path)
+        self._declare()
+        self._ctx = None
+        self._devices = devices
+        self._lock = threading.Lock()
+        self._pid = None
+
+    # ------------------------------------------------------------------ plumbing
+    def _declare(self):
+        d = self.dll
+        d.qsb_last_error.restype = ctypes.c_char_p
+        d.qsb_version.restype = ctypes.c_char_p
+        pp = ctypes.POINTER(_vp)
+        d.qsb_init.argtypes = [ctypes.c_int, _c_ip, pp]
+        d.qsb_shutdown.argtypes = [_vp]
+        d.qsb_device_count.argtypes = [ctypes.POINTER(ctypes.c_int)]
+        d.qsb_ctx_num_devices.argtypes = [_vp]
+        d.qsb_ctx_launch_count.argtypes = [_vp, ctypes.POINTER(ctypes.c_uint64)]
+        d.qsb_program_create.argtypes = [_vp, ctypes.c_int, ctypes.c_int, _vp, ctypes.c_int, _c_dp, ctypes.c_size_t, pp]
+        d.qsb_program_destroy.argtypes = [_vp, _vp]
+        common = [_vp, ctypes.c_int, pp, ctypes.c_int, _c_ip, _c_dp]
+        d.qsb_eval_matrix.argtypes = common + [_c_dp]
+        d.qsb_eval_mat_jac.argtypes = common + [_c_dp, _c_dp]
+        d.qsb_eval_hs_grad.argtypes = common + [_c_dp, _c_dp, _c_dp]
+        d.qsb_eval_distance.argtypes = common + [_c_dp, _c_dp]
+        d.qsb_eval_residuals_jac.argtypes = common + [_c_dp, _c_dp, _c_dp]
+        d.qsb_batch_create.argtypes = [_vp, ctypes.c_int, ctypes.c_int, pp, ctypes.c_int, _c_ip, pp]
+        d.qsb_batch_destroy.argtypes = [_vp]
+        d.qsb_batch_set_params.argtypes = [_vp, _c_dp, ctypes.c_size_t]
+        d.qsb_batch_set_target.argtypes = [_vp, _c_dp]
+        d.qsb_batch_run.argtypes = [_vp, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_float)]
+        d.qsb_batch_sync.argtypes = [_vp]
+        d.qsb_batch_fetch.argtypes = [_vp, ctypes.c_int, _c_dp, _c_dp, _c_dp]
+        d.qsb_batch_output_bytes.argtypes = [_vp, ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_uint64)]
+        solve = common + [_c_dp, ctypes.POINTER(SolverOpts), _c_dp, _c_dp, _c_ip, _c_ip]
+        d.qsb_solve_lm.argtypes = solve
+        d.qsb_solve_lbfgs.argtypes = solve
+        d.qsb_measure_fp64_peak.argtypes = [_vp, ctypes.c_int, ctypes.c_int, _c_dp]
+
+    def check(self, rc):
+        if rc != 0:
+            raise QsbError("qsb200 error {}: {}".format(rc, self.dll.qsb_last_error().decode()))
+
+    @property
+    def ctx(self):
+        pid = os.getpid()
+        if self._ctx is None or self._pid != pid:
+            with self._lock:
+                if self._ctx is None or self._pid != pid:  # a forked child gets its own context
+                    ctx = _vp()
+                    if self._devices is None:
+                        self.check(self.dll.qsb_init(0, None, ctypes.byref(ctx)))
+                    else:
+                        ids = (ctypes.c_int32 * len(self._devices))(*self._devices)
+                        self.check(self.dll.qsb_init(len(self._devices), ids, ctypes.byref(ctx)))
+                    self._ctx, self._pid = ctx, pid
+                    self._programs = {}
+        return self._ctx
+
+    @property
+    def num_devices(self):
+        return self.dll.qsb_ctx_num_devices(self.ctx)
+
+    def version(self):
+        return self.dll.qsb_version().decode()
+
+    def launch_count(self):
+        n = ctypes.c_uint64()
+        self.check(self.dll.qsb_ctx_launch_count(self.ctx, ctypes.byref(n)))
+        return n.value
+
+    # ------------------------------------------------------------------ programs
+    def program(self, gp):
+        """Device handle for a lowering.GateProgram (uploaded once per context, cached by identity key)."""
+        ctx = self.ctx
+        key = gp.key if gp.key is not None else id(gp)
+        ent = self._programs.get(key)
+        h = ent[0] if ent is not None else None
+        if h is None:
+            ops = np.ascontiguousarray(gp.ops, dtype=OP_DTYPE)
+            h = _vp()
+            self.check(self.dll.qsb_program_create(ctx, gp.n_qubits, len(ops), ops.ctypes.data_as(_vp), gp.n_params,
+                                                   _dp(gp.consts), gp.consts.size, ctypes.byref(h)))
+            self._programs[key] = (h, gp)  # keep gp alive so an id()-based key cannot be reused
+            if len(self._programs) > 4096:  # bound the cache: drop the oldest half
+                for k in list(self._programs)[:2048]:
+                    if k != key:
+                        self.dll.qsb_program_destroy(ctx, self._programs.pop(k)[0])
+        return h
+
+    def _pack(self, gps, prog_of_instance, params):
+        handles = (_vp * len(gps))(*[self.program(g) for g in gps])
+        poi = np.ascontiguousarray(prog_of_instance, dtype="int32")
+        params = _f64(params).ravel()
+        sizes = np.array([g.n_params for g in gps], dtype="int64")[poi]
+        if params.size != int(sizes.sum()):
+            raise ValueError("expected {} parameters in total, got {}".format(int(sizes.sum()), params.size))
+        return handles, poi, params, sizes
+
+    # ------------------------------------------------------------------ host-buffer evaluation
+    def eval_matrix(self, gps, prog_of_instance, params):
+        handles, poi, params, _ = self._pack(gps, prog_of_instance, params)
+        N = 1 << gps[0].n_qubits
+        U = np.empty((len(poi), N, N), dtype="complex128")
+        self.check(self.dll.qsb_eval_matrix(self.ctx, len(gps), handles, len(poi), poi.ctypes.data_as(_c_ip), _dp(params),
+                                            U.ctypes.data_as(_c_dp)))
+        return U
+
+    def eval_mat_jac(self, gps, prog_of_instance, params):
+        handles, poi, params, sizes = self._pack(gps, prog_of_instance, params)
+        N = 1 << gps[0].n_qubits
+        U = np.empty((len(poi), N, N), dtype="complex128")
+        J = np.empty((int(sizes.sum()), N, N), dtype="complex128")
+        self.check(self.dll.qsb_eval_mat_jac(self.ctx, len(gps), handles, len(poi), poi.ctypes.data_as(_c_ip), _dp(params),
+                                             U.ctypes.data_as(_c_dp), J.ctypes.data_as(_c_dp)))
+        return U, J
+
+    def eval_hs_grad(self, gps, prog_of_instance, params, target):
+        handles, poi, params, sizes = self._pack(gps, prog_of_instance, params)
+        T = np.ascontiguousarray(target, dtype="complex128")
+        f = np.empty(len(poi), dtype="float64")
+        g = np.empty(int(sizes.sum()), dtype="float64")
+        self.check(self.dll.qsb_eval_hs_grad(self.ctx, len(gps), handles, len(poi), poi.ctypes.data_as(_c_ip), _dp(params),
+                                             T.ctypes.data_as(_c_dp), _dp(f), _dp(g)))
+        return f, g
+
+    def eval_distance(self, gps, prog_of_instance, params, target):
+        handles, poi, params, _ = self._pack(gps, prog_of_instance, params)
+        T = np.ascontiguousarray(target, dtype="complex128")
+        f = np.empty(len(poi), dtype="float64")
+        self.check(self.dll.qsb_eval_distance(self.ctx, len(gps), handles, len(poi), poi.ctypes.data_as(_c_ip), _dp(params),
+                                              T.ctypes.data_as(_c_dp), _dp(f)))
+        return f
+
+    def eval_residuals_jac(self, gps, prog_of_instance, params, target, out_r=None, out_Jr=None):
+        """r: [inst, 2N^2]; Jr: [sum P, 2N^2] (row k = parameter k; the reference's array is its transpose view)."""
+        handles, poi, params, sizes = self._pack(gps, prog_of_instance, params)
+        N = 1 << gps[0].n_qubits
+        T = np.ascontiguousarray(target, dtype="complex128")
+        r = out_r if out_r is not None else np.empty((len(poi), 2 * N * N), dtype="float64")
+        Jr = out_Jr if out_Jr is not None else np.empty((int(sizes.sum()), 2 * N * N), dtype="float64")
+        self.check(self.dll.qsb_eval_residuals_jac(self.ctx, len(gps), handles, len(poi), poi.ctypes.data_as(_c_ip),
+                                                   _dp(params), T.ctypes.data_as(_c_dp), _dp(r), _dp(Jr)))
+        return r, Jr
+
+    # ------------------------------------------------------------------ solvers
+    def solve(self, method, gps, prog_of_instance, x0, target, max_iters=0, ftol=0.0, xtol=0.0, gtol=0.0,
+              stop_value=0.0, lbfgs_memory=10):
+        handles, poi, x0, sizes = self._pack(gps, prog_of_instance, x0)
+        T = np.ascontiguousarray(target, dtype="complex128")
+        opts = SolverOpts(max_iters=max_iters, lbfgs_memory=lbfgs_memory, ftol=ftol, xtol=xtol, gtol=gtol,
+                          stop_value=stop_value)
+        x = np.empty_like(x0)
+        f = np.empty(len(poi), dtype="float64")
+        iters = np.empty(len(poi), dtype="int32")
+        status = np.empty(len(poi), dtype="int32")
+        fn = self.dll.qsb_solve_lm if method == "lm" else self.dll.qsb_solve_lbfgs
+        self.check(fn(self.ctx, len(gps), handles, len(poi), poi.ctypes.data_as(_c_ip), _dp(x0), T.ctypes.data_as(_c_dp),
+                      ctypes.byref(opts), _dp(x), _dp(f), iters.ctypes.data_as(_c_ip), status.ctypes.data_as(_c_ip)))
+        return x, f, iters, status
+
+    def measure_fp64_peak(self, slot=0, use_dmma=False):
+        out = ctypes.c_double()
+        self.check(self.dll.qsb_measure_fp64_peak(self.ctx, slot, int(use_dmma), ctypes.byref(out)))
+        return out.value
+
+    # ------------------------------------------------------------------ device-resident batches
+    def batch(self, gps, prog_of_instance, slot=0):
+        return Batch(self, gps, prog_of_instance, slot)
+
+
+class Batch:
+    """Device-resident batch (qsb_batch_*): parameters and outputs stay in HBM between calls."""
+
+    def __init__(self, lib, gps, prog_of_instance, slot=0):
+        self.lib = lib
+        self.gps = list(gps)
+        self.poi = np.ascontiguousarray(prog_of_instance, dtype="int32")
+        self.sizes = np.array([g.n_params for g in self.gps], dtype="int64")[self.poi]
+        self.n_qubits = self.gps[0].n_qubits
+        handles = (_vp * len(self.gps))(*[lib.program(g) for g in self.gps])
+        self.h = _vp()
+        lib.check(lib.dll.qsb_batch_create(lib.ctx, slot, len(self.gps), handles, len(self.poi),
+                                           self.poi.ctypes.data_as(_c_ip), ctypes.byref(self.h)))
+
+    def set_params(self, params):
+        params = _f64(params).ravel()
+        self.lib.check(self.lib.dll.qsb_batch_set_params(self.h, _dp(params), params.size))
+
+    def set_target(self, target):
+        T = np.ascontiguousarray(target, dtype="complex128")
+        self.lib.check(self.lib.dll.qsb_batch_set_target(self.h, T.ctypes.data_as(_c_dp)))
+
+    def run(self, what, first=0, count=None, timed=False):
+        count = len(self.poi) - first if count is None else count
+        ms = ctypes.c_float()
+        self.lib.check(self.lib.dll.qsb_batch_run(self.h, what, first, count, ctypes.byref(ms) if timed else None))
+        self._last = (what, first, count)
+        return ms.value if timed else None
+
+    def sync(self):
+        self.lib.check(self.lib.dll.qsb_batch_sync(self.h))
+
+    def output_bytes(self, what, count):
+        n = ctypes.c_uint64()
+        self.lib.check(self.lib.dll.qsb_batch_output_bytes(self.h, what, count, ctypes.byref(n)))
+        return n.value
+
+    def fetch(self):
+        what, first, count = self._last
+        N = 1 << self.n_qubits
+        npar = int(self.sizes[first:first + count].sum())
+        a = b = c = None
+        if what == RUN_MATRIX:
+            a = np.empty((count, N, N), dtype="complex128")
+        elif what == RUN_MATJAC:
+            a, b = np.empty((count, N, N), dtype="complex128"), np.empty((npar, N, N), dtype="complex128")
+        elif what == RUN_RESID:
+            a, b = np.empty((count, 2 * N * N)), np.empty((npar, 2 * N * N))
+        elif what == RUN_HS:
+            a, b = np.empty(count), np.empty(npar)
+        elif what == RUN_DIST:
+            a = np.empty(count)
+        elif what == RUN_LMSYS:
+            a, b = np.empty(count), np.empty(npar)
+            c = np.empty(int((self.sizes[first:first + count] ** 2).sum()))
+        ptr = [None if x is None else x.ctypes.data_as(_c_dp) for x in (a, b, c)]
+        self.lib.check(self.lib.dll.qsb_batch_fetch(self.h, what, *ptr))
+        return a, b, c
+
+    def close(self):
+        if self.h is not None and self.h.value:
+            self.lib.dll.qsb_batch_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+_LIB = None
+_LIB_LOCK = threading.Lock()
+
+
+def get_library():
+    """The process-wide Library over the in-tree libqsb200.so (raises if it is missing)."""
+    global _LIB
+    if _LIB is None:
+        with _LIB_LOCK:
+            if _LIB is None:
+                devs = os.environ.get("QSB200_DEVICES")
+                _LIB = Library(devices=[int(x) for x in devs.split(",")] if devs else None)
+    return _LIB
+
+
+def use_library(lib):
+    """Select an explicitly constructed Library (e.g. one context per rank; the CPU test-suite passes the
+    host-emulation build of the same kernels from tests/emu here).  Returns the previous one."""
+    global _LIB
+    prev, _LIB = _LIB, lib
+    return prev

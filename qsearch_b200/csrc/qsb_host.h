@@ -1,0 +1,64 @@
+// Host-side objects behind the opaque handles of include/qsb200.h.
+#pragma once
+#include <cstdint>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "qsb_device.cuh"
+
+struct QsbDevice {
+  int id = 0;
+  int sm_count = 148;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+};
+
+struct qsb_ctx {
+  std::vector<QsbDevice> devs;
+  uint64_t launches = 0;
+  std::mutex mu;
+};
+
+struct qsb_program {
+  int n_qubits = 0, n_ops = 0, n_params = 0;
+  std::vector<qsb_op> ops;
+  std::vector<double> consts;
+  bool fast_ok = false;             // only U3/XZXZ/.../CONST1/CNOT ops: eligible for the register-tiled kernels
+  std::vector<qsb_op*> d_ops;       // per device slot
+  std::vector<double*> d_consts;
+};
+
+struct QsbBuf {
+  void* p = nullptr;
+  size_t bytes = 0;
+};
+
+struct qsb_batch {
+  qsb_ctx* ctx = nullptr;
+  int slot = 0;
+  int n_qubits = 0, n_instances = 0, n_programs = 0;
+  int max_ops = 0, max_params = 0;
+  bool fast_ok = false;
+  std::vector<long long> param_off;  // host copy, n_instances + 1
+  std::vector<int32_t> prog_idx;
+  QsbDevProgram* d_progs = nullptr;
+  int32_t* d_prog_idx = nullptr;
+  long long* d_param_off = nullptr;
+  double* d_params = nullptr;
+  double* d_target = nullptr;
+  QsbBuf out_a, out_b, out_c;  // grown on demand
+  int last_first = 0, last_count = 0, last_what = 0;
+  void* solver_scratch = nullptr;
+  size_t solver_scratch_bytes = 0;
+};
+
+void qsb_set_error(const std::string& msg);
+int qsb_fail(int code, const std::string& msg);
+int qsb_cuda_fail(cudaError_t e, const char* what);
+
+#define QSB_CUDA(call)                                            \
+  do {                                                            \
+    cudaError_t _e = (call);                                      \
+    if (_e != cudaSuccess) return qsb_cuda_fail(_e, #call);       \
+  } while (0)

@@ -1,0 +1,79 @@
+// Kernel selection and launch geometry for one batch run (host side).
+#pragma once
+#include <algorithm>
+
+#include "qsb_host.h"
+#include "qsb_generic.cuh"
+
+struct QsbLaunchShape {
+  int threads;
+  size_t smem;
+  int ctas_per_sm;
+};
+
+static inline QsbLaunchShape qsb_shape_generic(int nq, int what, int max_ops, int max_params) {
+  const size_t NN = (size_t)1 << (2 * nq);
+  QsbLaunchShape s;
+  s.threads = (int)std::max<size_t>(32, NN / 2);
+  const size_t trig = (size_t)max_ops * QSB_TRIG_STRIDE * sizeof(double);
+  switch (what) {
+    case QSB_RUN_MATRIX: case QSB_RUN_DIST: s.smem = (NN + 32) * 16 + trig; break;
+    case QSB_RUN_HS: s.smem = (2 * NN + 32 + 96 + (size_t)max_params) * 16 + trig; break;
+    default: s.smem = 3 * NN * 16 + trig; break;
+  }
+  s.smem += 16;
+  int by_threads = 2048 / s.threads, by_smem = (int)((size_t)220 * 1024 / s.smem);
+  s.ctas_per_sm = std::max(1, std::min(std::min(by_threads, by_smem), 32));
+  return s;
+}
+
+template <class K>
+static inline int qsb_prepare_kernel(K kernel, size_t smem) {
+  if (smem > 48 * 1024) QSB_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  return QSB_OK;
+}
+
+template <int NQ>
+static int qsb_launch_generic_nq(qsb_batch* b, int what, const QsbBatchArgs& args, cudaStream_t st, int sm_count) {
+  QsbLaunchShape sh = qsb_shape_generic(NQ, what, b->max_ops, b->max_params);
+  if (sh.smem > 227 * 1024) return qsb_fail(QSB_ERR_UNSUPPORTED, "program too long for the shared-memory gate cache");
+  int grid = std::max(1, std::min(args.count, sm_count * sh.ctas_per_sm));
+  int rc = QSB_OK;
+  switch (what) {
+    case QSB_RUN_MATRIX:
+      if ((rc = qsb_prepare_kernel(qsb_k_forward<NQ, QSB_RUN_MATRIX>, sh.smem))) return rc;
+      QSB_LAUNCH((qsb_k_forward<NQ, QSB_RUN_MATRIX>), grid, sh.threads, sh.smem, st, args);
+      break;
+    case QSB_RUN_DIST:
+      if ((rc = qsb_prepare_kernel(qsb_k_forward<NQ, QSB_RUN_DIST>, sh.smem))) return rc;
+      QSB_LAUNCH((qsb_k_forward<NQ, QSB_RUN_DIST>), grid, sh.threads, sh.smem, st, args);
+      break;
+    case QSB_RUN_MATJAC:
+      if ((rc = qsb_prepare_kernel(qsb_k_jac<NQ, QSB_RUN_MATJAC>, sh.smem))) return rc;
+      QSB_LAUNCH((qsb_k_jac<NQ, QSB_RUN_MATJAC>), grid, sh.threads, sh.smem, st, args);
+      break;
+    case QSB_RUN_RESID:
+      if ((rc = qsb_prepare_kernel(qsb_k_jac<NQ, QSB_RUN_RESID>, sh.smem))) return rc;
+      QSB_LAUNCH((qsb_k_jac<NQ, QSB_RUN_RESID>), grid, sh.threads, sh.smem, st, args);
+      break;
+    case QSB_RUN_HS:
+      if ((rc = qsb_prepare_kernel(qsb_k_hs<NQ>, sh.smem))) return rc;
+      QSB_LAUNCH((qsb_k_hs<NQ>), grid, sh.threads, sh.smem, st, args);
+      break;
+    default:
+      return qsb_fail(QSB_ERR_INVALID, "unknown run kind");
+  }
+  QSB_CUDA(cudaGetLastError());
+  return QSB_OK;
+}
+
+static inline int qsb_launch_generic(qsb_batch* b, int what, const QsbBatchArgs& args, cudaStream_t st, int sm_count) {
+  switch (b->n_qubits) {
+    case 1: return qsb_launch_generic_nq<1>(b, what, args, st, sm_count);
+    case 2: return qsb_launch_generic_nq<2>(b, what, args, st, sm_count);
+    case 3: return qsb_launch_generic_nq<3>(b, what, args, st, sm_count);
+    case 4: return qsb_launch_generic_nq<4>(b, what, args, st, sm_count);
+    case 5: return qsb_launch_generic_nq<5>(b, what, args, st, sm_count);
+    default: return qsb_fail(QSB_ERR_UNSUPPORTED, "unsupported qubit count");
+  }
+}

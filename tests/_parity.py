@@ -1,0 +1,79 @@
+"""Shared parity checks: a Library (CUDA build on the B200, or the host emulation of the same kernel sources in the
+CPU suite) against the reference-generated fixtures and the NumPy oracle.  Tolerance = north_star's 1e-12 max-abs."""
+import numpy as np
+
+from oracle import qs_oracle as O
+from qsearch_b200 import lowering
+from tests import _golden
+
+TOL = 1e-12
+
+
+def check_fixture_case(lib, case, tol=TOL):
+    gp = lowering.lower(case.circuit)
+    n = len(case.xs)
+    poi = np.zeros(n, dtype="int32")
+    xs = np.asarray(case.xs, dtype="float64")
+    U = lib.eval_matrix([gp], poi, xs)
+    U2, J = lib.eval_mat_jac([gp], poi, xs)
+    P, N = gp.n_params, 1 << gp.n_qubits
+    J = J.reshape(n, P, N, N)
+    for s, gold in enumerate(case.samples):
+        assert np.abs(U[s] - gold["U"]).max() < tol
+        assert np.abs(U2[s] - gold["U"]).max() < tol
+        if "J" in gold:
+            assert J[s].shape == gold["J"].shape
+            if P:
+                assert np.abs(J[s] - gold["J"]).max() < tol
+        else:
+            w = _golden.proj_weights(N)
+            assert np.abs(J[s] @ w - gold["J_proj"]).max() < 10 * tol
+    for tname, T in case.targets.items():
+        d = lib.eval_distance([gp], poi, xs, T)
+        for s, gold in enumerate(case.samples):
+            assert abs(d[s] - gold["dist_" + tname]) < tol
+        if not P:
+            continue
+        f, g = lib.eval_hs_grad([gp], poi, xs, T)
+        r, Jr = lib.eval_residuals_jac([gp], poi, xs, T)
+        g, Jr = g.reshape(n, P), Jr.reshape(n, P, 2 * N * N)
+        for s, gold in enumerate(case.samples):
+            assert abs(f[s] - gold["f_" + tname]) < tol
+            assert np.abs(g[s] - gold["g_" + tname]).max() < tol
+            assert np.abs(r[s] - gold["r_" + tname]).max() < tol
+            if "Jr_" + tname in gold:
+                assert np.abs(Jr[s].T - gold["Jr_" + tname]).max() < tol  # reference layout: (2N^2, P)
+            else:
+                w = _golden.proj_weights(2 * N * N)
+                assert np.abs(Jr[s] @ w - gold["Jr_" + tname + "_proj"]).max() < 50 * tol
+
+
+def check_against_oracle(lib, circuits, xs_per_circuit, T, tol=TOL):
+    """One ragged batch (several structures, several vectors each) against the NumPy oracle."""
+    gps = [lowering.lower(c) for c in circuits]
+    poi, params = [], []
+    for ci, xs in enumerate(xs_per_circuit):
+        for x in xs:
+            poi.append(ci)
+            params.append(np.asarray(x, dtype="float64"))
+    flat = np.concatenate(params) if params else np.zeros(0)
+    N = 1 << gps[0].n_qubits
+    U = lib.eval_matrix(gps, poi, flat)
+    U2, J = lib.eval_mat_jac(gps, poi, flat)
+    f, g = lib.eval_hs_grad(gps, poi, flat, T)
+    d = lib.eval_distance(gps, poi, flat, T)
+    r, Jr = lib.eval_residuals_jac(gps, poi, flat, T)
+    k = 0
+    for i, (ci, x) in enumerate(zip(poi, params)):
+        c, P = circuits[ci], gps[ci].n_params
+        Uo, Jo = O.mat_jac(c, x)
+        Jo = np.array(Jo).reshape(P, N, N)
+        assert np.abs(U[i] - Uo).max() < tol and np.abs(U2[i] - Uo).max() < tol
+        assert np.abs(J[k:k + P] - Jo).max() < tol
+        fo, go = O.matrix_distance_squared_jac(T, Uo, list(Jo))
+        assert abs(f[i] - fo) < tol and np.abs(g[k:k + P] - go).max() < tol
+        assert abs(d[i] - O.matrix_distance_squared(T, Uo)) < tol
+        assert np.abs(r[i] - O.matrix_residuals(T, Uo)).max() < tol
+        assert np.abs(Jr[k:k + P].T - O.matrix_residuals_jac(T, Uo, list(Jo))).max() < tol
+        k += P
+    return len(poi)

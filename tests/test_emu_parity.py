@@ -1,0 +1,45 @@
+"""CPU suite: the CUDA kernel sources, compiled for the host by tests/emu (threads + barriers), against the
+reference-generated fixtures.  This checks kernel indexing / synchronisation logic without a GPU; the real parity
+gate is tests/test_gpu_parity.py on the B200."""
+import numpy as np
+import pytest
+
+from tests import _golden, _parity
+from tests.emu import emulated_library
+
+
+@pytest.mark.parametrize("fname,stride", [("gates_small", 1), ("gateset_layers", 3), ("microbench", 4), ("leap_long", 2)])
+def test_emulated_kernels_match_reference_fixtures(fname, stride):
+    lib = emulated_library()
+    cases = _golden.load(fname)
+    for case in cases[::stride]:
+        if case.circuit.qudits == 5 and len(case.circuit._subgates) > 12:
+            continue  # 512 emulated threads x long programs: left to the GPU suite
+        _parity.check_fixture_case(lib, case)
+
+
+def test_emulated_ragged_batch_matches_oracle():
+    from qsearch_b200 import gatesets, unitaries
+    lib = emulated_library()
+    rng = np.random.default_rng(5)
+    g = gatesets.QubitCNOTLinear()
+    c0 = gatesets.ProductGate(g.initial_layer(3))
+    c1 = g.successors(c0)[0][0]
+    c2 = g.successors(c1)[1][0]
+    circuits = [c0, c1, c2]
+    xs = [rng.random((k, c.num_inputs)) * 2 * np.pi for k, c in zip((2, 1, 3), circuits)]
+    assert _parity.check_against_oracle(lib, circuits, xs, unitaries.qft(8)) == 6
+
+
+def test_bad_programs_are_rejected():
+    from qsearch_b200 import lowering, gates, _lib
+    lib = emulated_library()
+    gp = lowering.lower(gates.KroneckerGate(gates.U3Gate(), gates.U3Gate()))
+    bad = lowering.GateProgram(gp.n_qubits, gp.n_params, gp.ops.copy(), gp.consts)
+    bad.ops["q0"][1] = 7
+    with pytest.raises(_lib.QsbError):
+        lib.eval_matrix([bad], [0], np.zeros(6))
+    with pytest.raises(ValueError):
+        lowering.lower(gates.SingleQutritGate())
+    with pytest.raises(ValueError):
+        lib.eval_matrix([gp], [0], np.zeros(5))
