@@ -1,0 +1,154 @@
+"""GPU parity gate (-m gpu): the CUDA path through the C ABI against (i) the reference-generated fixtures,
+(ii) the NumPy oracle on seeded inputs, (iii) size-independent properties at the benchmark's full size.
+Tolerance: 1e-12 max-abs (north_star).  Modelled on the reference's tests/test_circuit.py and tests/test_gradients.py."""
+import numpy as np
+import pytest
+
+from oracle import qs_oracle as O
+from qsearch_b200 import _lib, gates, gatesets, lowering, unitaries, workloads
+from qsearch_b200.backends import CudaBackend, CudaCircuit
+from tests import _golden, _parity
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def lib():
+    return _lib.get_library()
+
+
+@pytest.mark.parametrize("fname", _golden.ALL_FILES)
+def test_fixtures(lib, fname):
+    for case in _golden.load(fname):
+        _parity.check_fixture_case(lib, case)
+
+
+def _reference_gate_list():
+    u, xzxz, zxzxz, cnot = gates.U3Gate(), gates.XZXZGate(), gates.ZXZXZGate(), gates.CNOTGate()
+    return [gates.XGate(), gates.YGate(), gates.ZGate(), xzxz, zxzxz, u, gates.U2Gate(), gates.U1Gate(),
+            gates.ProductGate(u, xzxz, u), gates.KroneckerGate(u, xzxz, u), gates.ProductGate(u, zxzxz, u),
+            gates.KroneckerGate(u, zxzxz, u), gates.KroneckerGate(u, u), gates.KroneckerGate(u, cnot, xzxz),
+            gates.ProductGate(gates.KroneckerGate(u, u, u),
+                              gates.KroneckerGate(gates.ProductGate(cnot, gates.KroneckerGate(xzxz, u)), gates.IdentityGate()))]
+
+
+@pytest.mark.parametrize("gate", _reference_gate_list(), ids=lambda g: repr(g)[:40])
+def test_backend_matches_oracle(lib, gate):
+    """tests/test_circuit.py:8-23 with the CUDA backend in place of qsrs."""
+    circ = CudaBackend().prepare_circuit(gate)
+    assert not isinstance(circ, gates.Gate)  # tests/test_defaults.py:42
+    assert CudaBackend().prepare_circuit(circ) is circ  # tests/test_circuit.py:60-62
+    rng = np.random.default_rng(3)
+    for _ in range(10):
+        v = rng.random(gate.num_inputs) * 2 * np.pi
+        U, J = circ.mat_jac(v)
+        Uo, Jo = O.mat_jac(gate, v)
+        assert np.abs(circ.matrix(v) - Uo).max() < 1e-12 and np.abs(U - Uo).max() < 1e-12
+        assert len(J) == len(Jo) == circ.num_inputs
+        for a, b in zip(J, Jo):
+            assert np.abs(a - b).max() < 1e-12
+        assert O.matrix_distance_squared(U, Uo) < 1e-10
+
+
+@pytest.mark.parametrize("gate", _reference_gate_list(), ids=lambda g: repr(g)[:40])
+def test_finite_difference(lib, gate):
+    """tests/test_gradients.py:29-50: central differences of matrix() against mat_jac()."""
+    circ = CudaCircuit(gate)
+    rng = np.random.default_rng(4)
+    eps = 1e-5
+    P = gate.num_inputs
+    V = rng.random((20, P)) * 2 * np.pi
+    for v in V:
+        _, J = circ.mat_jac(v)
+        pts = np.concatenate([v + eps * np.eye(P), v - eps * np.eye(P)])
+        Us = circ.matrix_batch(pts)
+        fd = (Us[:P] - Us[P:]) / (2 * eps)
+        assert np.abs(fd - J).sum(axis=(1, 2)).max() < 1e-7
+
+
+@pytest.mark.parametrize("n", [2, 3, 4, 5])
+def test_ragged_batches_against_oracle(lib, n):
+    rng = np.random.default_rng(100 + n)
+    circuits = []
+    for gs in (gatesets.QubitCNOTLinear(), gatesets.QubitCNOTRing(),
+               gatesets.QubitCNOTAdjacencyList([(0, 1), (0, 2), (1, 2), (2, 3), (2, 4), (3, 4)])):
+        layers = gs.search_layers(n)
+        for depth in (0, 1, 3, 7):
+            c = gates.ProductGate(gs.initial_layer(n))
+            for _ in range(depth):
+                c = c.appending(layers[int(rng.integers(len(layers)))][0])
+            circuits.append(c)
+    xs = [rng.random((int(rng.integers(1, 4)), c.num_inputs)) * 2 * np.pi for c in circuits]
+    for T in (unitaries.qft(1 << n), workloads.haar_unitary(1 << n, 77)):
+        _parity.check_against_oracle(lib, circuits, xs, T)
+
+
+def test_empty_and_zero_parameter_inputs(lib):
+    gp = lowering.lower(gates.KroneckerGate(gates.CNOTGate(), gates.IdentityGate()))
+    U = lib.eval_matrix([gp], [0, 0], np.zeros(0))
+    assert np.array_equal(U[0], np.kron(unitaries.cnot, np.eye(2))) and np.array_equal(U[0], U[1])
+    U2, J = lib.eval_mat_jac([gp], [0], np.zeros(0))
+    assert J.shape == (0, 8, 8)
+    gp2 = lowering.lower(gates.U3Gate())
+    assert lib.eval_matrix([gp2], np.zeros(0, dtype="int32"), np.zeros(0)).shape == (0, 2, 2)
+
+
+@pytest.mark.parametrize("n", [4, 5])
+def test_full_size_properties(lib, n):
+    """At the benchmark's size the oracle is too slow; use properties that hold for every instance:
+    unitarity, |r|^2 = 2N - 2 Re Tr(U T^dagger), J_r[k].r = -Re Tr(K_k), f from HS equals f from the residual trace,
+    and bit-identical results for an instance evaluated alone or inside the big batch."""
+    n_circ, n_vec = (100, 200) if n == 4 else (40, 50)
+    circuits, params, targets = workloads.microbench_workload(n, n_circ, n_vec)
+    n_circ, n_vec = params.shape[:2]
+    gps = [lowering.lower(c) for c in circuits]
+    P, N = circuits[0].num_inputs, 1 << n
+    poi = np.repeat(np.arange(n_circ, dtype="int32"), n_vec)
+    flat = params.reshape(-1, P)
+    T = targets["haar"]
+    U = lib.eval_matrix(gps, poi, flat)
+    assert np.abs(U @ U.conj().transpose(0, 2, 1) - np.eye(N)).max() < 1e-12
+    f, g = lib.eval_hs_grad(gps, poi, flat, T)
+    d = lib.eval_distance(gps, poi, flat, T)
+    tr = np.einsum("bij,ij->b", U, T.conj())  # Tr(U T^dagger)
+    assert np.abs(f - (1 - np.abs(tr) / N)).max() < 1e-12 and np.abs(d - np.abs(f)).max() < 1e-12
+    sel = np.arange(0, len(poi), max(1, len(poi) // 512))
+    r, Jr = lib.eval_residuals_jac(gps, poi[sel], flat[sel], T)
+    Jr = Jr.reshape(len(sel), P, 2 * N * N)
+    assert np.abs((r * r).sum(1) - (2 * N - 2 * tr[sel].real)).max() < 1e-11
+    diag = np.arange(N) * (N + 1)
+    assert np.abs(np.einsum("bkm,bm->bk", Jr, r) + Jr[:, :, diag].sum(2)).max() < 1e-11
+    # gradient of f from J_r: S_k = Tr(T^dagger J_k) = conj-symmetric pieces of K_k's diagonal
+    trK = Jr[:, :, diag].sum(2) + 1j * Jr[:, :, N * N + diag].sum(2)  # Tr(K_k) = Tr(J_k T^dagger)
+    S = tr[sel]
+    g_from_J = -(S.real[:, None] * trK.real + S.imag[:, None] * trK.imag) / (N * np.abs(S)[:, None])
+    assert np.abs(g.reshape(-1, P)[sel] - g_from_J).max() < 1e-12
+    for i in (0, len(sel) // 2, len(sel) - 1):
+        r1, J1 = lib.eval_residuals_jac(gps, poi[sel[i]:sel[i] + 1], flat[sel[i]:sel[i] + 1], T)
+        assert np.array_equal(r1[0], r[i]) and np.array_equal(J1, Jr[i])
+    # a slice against the oracle itself
+    for i in sel[:3]:
+        ro, Jo = O.eval_lm(circuits[poi[i]], T, flat[i])
+        k = int(np.where(sel == i)[0][0])
+        assert np.abs(r[k] - ro).max() < 1e-12 and np.abs(Jr[k].T - Jo).max() < 1e-12
+
+
+def test_device_resident_batch_matches_host_calls(lib):
+    circuits, params, targets = workloads.microbench_workload(4, 6, 5)
+    gps = [lowering.lower(c) for c in circuits]
+    poi = np.repeat(np.arange(6, dtype="int32"), 5)
+    flat = params.reshape(30, -1)
+    T = targets["qft"]
+    b = lib.batch(gps, poi)
+    b.set_params(flat)
+    b.set_target(T)
+    ms = b.run(_lib.RUN_RESID, first=7, count=11, timed=True)
+    assert ms > 0
+    r, Jr, _ = b.fetch()
+    r2, Jr2 = lib.eval_residuals_jac(gps, poi[7:18], flat[7:18], T)
+    assert np.array_equal(r, r2) and np.array_equal(Jr, Jr2)
+    b.run(_lib.RUN_HS)
+    f, g, _ = b.fetch()
+    f2, g2 = lib.eval_hs_grad(gps, poi, flat, T)
+    assert np.array_equal(f, f2) and np.array_equal(g, g2)
+    b.close()
