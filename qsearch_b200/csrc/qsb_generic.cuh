@@ -200,8 +200,64 @@ QSB_GLOBAL qsb_k_forward(QsbBatchArgs a) {
   }
 }
 
-// MATJAC: out_a = U [N][N][2], out_b = J_k [N][N][2] interleaved (T = I).
-// RESID:  out_a = r = [Re(U T^dagger) - I ; Im(U T^dagger)], out_b row k = [Re K_k ; Im K_k], K_k = J_k T^dagger.
+// One instance of the Jacobian sweep.  X, S, Y: N*N cplx tiles in shared memory; trig: sin/cos cache.
+// MATJAC: out_u = U [N][N][2], out_j[k] = J_k [N][N][2] interleaved (T = I).
+// RESID:  out_u = r = [Re(U T^dagger) - I ; Im(U T^dagger)], out_j[k] = [Re K_k ; Im K_k], K_k = J_k T^dagger.
+template <int NQ, int WHAT>
+QSB_DEVICE void qsb_jac_instance(cplx* X, cplx* S, cplx* Y, double* trig, const QsbDevProgram& P, const double* x,
+                                 const double* target, double* out_u, double* out_j) {
+  constexpr int N = 1 << NQ, NN = N * N;
+  qsb_fill_trig(P, x, trig);
+  qsb_load_init<NQ>(X, WHAT == QSB_RUN_RESID ? target : nullptr, true);
+  qsb_load_init<NQ>(S, nullptr, false);
+  __syncthreads();
+  qsb_forward<NQ>(X, P, trig);
+  for (int e = threadIdx.x; e < NN; e += blockDim.x) {
+    if (WHAT == QSB_RUN_MATJAC) { out_u[2 * e] = X[e].x; out_u[2 * e + 1] = X[e].y; }
+    else { out_u[e] = X[e].x - (((e >> NQ) == (e & (N - 1))) ? 1.0 : 0.0); out_u[NN + e] = X[e].y; }
+  }
+  __syncthreads();  // X is about to be peeled by other threads
+  for (int j = P.n_ops - 1; j >= 0; --j) {
+    const qsb_op op = P.ops[j];
+    const double* tj = trig + j * QSB_TRIG_STRIDE;
+    const int np = qsb_num_params(op.opcode);
+    if (np == 0 && j == 0) break;  // nothing left to differentiate
+    qsb_apply_left<NQ>(X, op, tj, P.consts, true);  // X = R_j T^dagger
+    __syncthreads();
+    for (int k = 0; k < np; ++k) {
+      cplx dg[4];
+      qsb_gate2x2(op.opcode, tj, 1 + k, dg);
+      {  // Y = (dg (x) I) X, out of place
+        const int sh = NQ - 1 - op.q0, s = 1 << sh;
+        for (int idx = threadIdx.x; idx < NN / 2; idx += blockDim.x) {
+          int c = idx & (N - 1), r0 = qsb_insert_zero_bit(idx >> NQ, sh), r1 = r0 | s;
+          cplx xa = X[r0 * N + c], xb = X[r1 * N + c];
+          Y[r0 * N + c] = cfma(dg[1], xb, cmul(dg[0], xa));
+          Y[r1 * N + c] = cfma(dg[3], xb, cmul(dg[2], xa));
+        }
+      }
+      __syncthreads();
+      double* o = out_j + (size_t)(op.param_off + k) * 2 * NN;
+      for (int pidx = threadIdx.x; pidx < NN / 2; pidx += blockDim.x) {  // K = S Y, two outputs per thread
+        int i = pidx / (N / 2), c0 = 2 * (pidx % (N / 2));
+        cplx acc0 = cmk(0, 0), acc1 = cmk(0, 0);
+#pragma unroll 4
+        for (int m = 0; m < N; ++m) {
+          cplx sv = S[i * N + m];
+          acc0 = cfma(sv, Y[m * N + c0], acc0);
+          acc1 = cfma(sv, Y[m * N + c0 + 1], acc1);
+        }
+        int e = i * N + c0;
+        if (WHAT == QSB_RUN_MATJAC) { o[2 * e] = acc0.x; o[2 * e + 1] = acc0.y; o[2 * e + 2] = acc1.x; o[2 * e + 3] = acc1.y; }
+        else { o[e] = acc0.x; o[e + 1] = acc1.x; o[NN + e] = acc0.y; o[NN + e + 1] = acc1.y; }
+      }
+      __syncthreads();
+    }
+    if (j > 0) { qsb_apply_right<NQ>(S, op, tj, P.consts); __syncthreads(); }
+  }
+  __syncthreads();
+}
+
 template <int NQ, int WHAT>
 QSB_GLOBAL qsb_k_jac(QsbBatchArgs a) {
   constexpr int N = 1 << NQ, NN = N * N;
@@ -214,65 +270,86 @@ QSB_GLOBAL qsb_k_jac(QsbBatchArgs a) {
   for (int li = blockIdx.x; li < a.count; li += gridDim.x) {
     const int inst = a.first + li;
     const QsbDevProgram P = a.progs[a.prog_idx[inst]];
-    qsb_fill_trig(P, a.params + a.param_off[inst], trig);
-    qsb_load_init<NQ>(X, WHAT == QSB_RUN_RESID ? a.target : nullptr, true);
-    qsb_load_init<NQ>(S, nullptr, false);
-    __syncthreads();
-    qsb_forward<NQ>(X, P, trig);
-    {
-      double* out = a.out_a + (size_t)li * 2 * NN;
-      for (int e = threadIdx.x; e < NN; e += blockDim.x) {
-        if (WHAT == QSB_RUN_MATJAC) { out[2 * e] = X[e].x; out[2 * e + 1] = X[e].y; }
-        else { out[e] = X[e].x - (((e >> NQ) == (e & (N - 1))) ? 1.0 : 0.0); out[NN + e] = X[e].y; }
-      }
-    }
-    __syncthreads();  // X is about to be peeled by other threads
-    double* outJ = a.out_b + (size_t)(a.param_off[inst] - p_base) * 2 * NN;
-    for (int j = P.n_ops - 1; j >= 0; --j) {
-      const qsb_op op = P.ops[j];
-      const double* tj = trig + j * QSB_TRIG_STRIDE;
-      const int np = qsb_num_params(op.opcode);
-      if (np == 0 && j == 0) break;  // nothing left to differentiate
-      qsb_apply_left<NQ>(X, op, tj, P.consts, true);  // X = R_j T^dagger
-      __syncthreads();
-      for (int k = 0; k < np; ++k) {
-        cplx dg[4];
-        qsb_gate2x2(op.opcode, tj, 1 + k, dg);
-        {  // Y = (dg (x) I) X, out of place
-          const int sh = NQ - 1 - op.q0, s = 1 << sh;
-          for (int idx = threadIdx.x; idx < NN / 2; idx += blockDim.x) {
-            int c = idx & (N - 1), r0 = qsb_insert_zero_bit(idx >> NQ, sh), r1 = r0 | s;
-            cplx xa = X[r0 * N + c], xb = X[r1 * N + c];
-            Y[r0 * N + c] = cfma(dg[1], xb, cmul(dg[0], xa));
-            Y[r1 * N + c] = cfma(dg[3], xb, cmul(dg[2], xa));
-          }
-        }
-        __syncthreads();
-        double* o = outJ + (size_t)(op.param_off + k) * 2 * NN;
-        for (int pidx = threadIdx.x; pidx < NN / 2; pidx += blockDim.x) {  // K = S Y, two outputs per thread
-          int i = pidx / (N / 2), c0 = 2 * (pidx % (N / 2));
-          cplx acc0 = cmk(0, 0), acc1 = cmk(0, 0);
-#pragma unroll 4
-          for (int m = 0; m < N; ++m) {
-            cplx sv = S[i * N + m];
-            acc0 = cfma(sv, Y[m * N + c0], acc0);
-            acc1 = cfma(sv, Y[m * N + c0 + 1], acc1);
-          }
-          int e = i * N + c0;
-          if (WHAT == QSB_RUN_MATJAC) { o[2 * e] = acc0.x; o[2 * e + 1] = acc0.y; o[2 * e + 2] = acc1.x; o[2 * e + 3] = acc1.y; }
-          else { o[e] = acc0.x; o[e + 1] = acc1.x; o[NN + e] = acc0.y; o[NN + e + 1] = acc1.y; }
-        }
-        __syncthreads();
-      }
-      if (j > 0) { qsb_apply_right<NQ>(S, op, tj, P.consts); __syncthreads(); }
-    }
-    __syncthreads();
+    qsb_jac_instance<NQ, WHAT>(X, S, Y, trig, P, a.params + a.param_off[inst], a.target,
+                               a.out_a + (size_t)li * 2 * NN, a.out_b + (size_t)(a.param_off[inst] - p_base) * 2 * NN);
   }
 }
 
-// HS: out_a[li] = f = 1 - |S|/N, out_b = grad, S = sum(T o conj(U)), S_k = sum(T o conj(J_k))   (comparison.py:37-55)
+// HS form of one instance: returns f = 1 - |S|/N and fills grad[0..P) (comparison.matrix_distance_squared_jac,
+// comparison.py:37-55), S = sum(T o conj(U)), S_k = sum(T o conj(J_k)).
 // Adjoint sweep: S_k = conj(<L_j, (dg_k (x) I) R_j>) with L_j = (g_{M-1}..g_{j+1})^dagger T, R_j = g_{j-1}..g_0:
 // only structured one-qubit updates, no dense product.  Gradient is +inf when S == 0 (qsrs/src/utils.rs:144-146).
+// X, L: N*N tiles; red: 32 cplx; wpart: 96 cplx; acc: P cplx; all in shared memory.  grad may be shared or global.
+template <int NQ>
+QSB_DEVICE double qsb_hs_instance(cplx* X, cplx* L, cplx* red, cplx* wpart, cplx* acc, double* trig,
+                                  const QsbDevProgram& P, const double* x, const double* target, double* grad) {
+  constexpr int N = 1 << NQ, NN = N * N;
+  __syncthreads();
+  qsb_fill_trig(P, x, trig);
+  qsb_load_init<NQ>(X, nullptr, false);
+  qsb_load_init<NQ>(L, target, false);
+  __syncthreads();
+  qsb_forward<NQ>(X, P, trig);
+  cplx part = cmk(0, 0);
+  for (int e = threadIdx.x; e < NN; e += blockDim.x) part = cfma_conj(L[e], X[e], part);  // <T, U>
+  const cplx tr = qsb_block_sum(part, red);
+  const int w = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+  for (int j = P.n_ops - 1; j >= 0; --j) {
+    const qsb_op op = P.ops[j];
+    const double* tj = trig + j * QSB_TRIG_STRIDE;
+    const int np = qsb_num_params(op.opcode);
+    if (np == 0) {
+      if (j == 0) break;
+      qsb_apply_left<NQ>(X, op, tj, P.consts, true);
+      qsb_apply_left<NQ>(L, op, tj, P.consts, true);
+      __syncthreads();
+      continue;
+    }
+    cplx gd[4], dg[3][4];
+    qsb_op2x2(op, tj, P.consts, true, gd);
+    for (int k = 0; k < np; ++k) qsb_gate2x2(op.opcode, tj, 1 + k, dg[k]);
+    cplx pk[3] = {cmk(0, 0), cmk(0, 0), cmk(0, 0)};
+    const int sh = NQ - 1 - op.q0, s = 1 << sh;
+    for (int idx = threadIdx.x; idx < NN / 2; idx += blockDim.x) {
+      int c = idx & (N - 1), r0 = qsb_insert_zero_bit(idx >> NQ, sh), r1 = r0 | s;
+      cplx xa = X[r0 * N + c], xb = X[r1 * N + c];
+      cplx ra = cfma(gd[1], xb, cmul(gd[0], xa)), rb = cfma(gd[3], xb, cmul(gd[2], xa));  // R_j pair
+      X[r0 * N + c] = ra; X[r1 * N + c] = rb;
+      cplx la = L[r0 * N + c], lb = L[r1 * N + c];
+      for (int k = 0; k < np; ++k) {
+        cplx ya = cfma(dg[k][1], rb, cmul(dg[k][0], ra)), yb = cfma(dg[k][3], rb, cmul(dg[k][2], ra));
+        pk[k] = cfma_conj(la, ya, pk[k]);
+        pk[k] = cfma_conj(lb, yb, pk[k]);
+      }
+      L[r0 * N + c] = cfma(gd[1], lb, cmul(gd[0], la));
+      L[r1 * N + c] = cfma(gd[3], lb, cmul(gd[2], la));
+    }
+    for (int k = 0; k < np; ++k) {
+      for (int m = 16; m > 0; m >>= 1) {
+        pk[k].x += __shfl_xor_sync(0xffffffffu, pk[k].x, m);
+        pk[k].y += __shfl_xor_sync(0xffffffffu, pk[k].y, m);
+      }
+      if ((threadIdx.x & 31) == 0) wpart[k * 32 + w] = pk[k];
+    }
+    __syncthreads();
+    if ((int)threadIdx.x < np) {
+      cplx sk = cmk(0, 0);
+      for (int i = 0; i < nw; ++i) sk = cadd(sk, wpart[threadIdx.x * 32 + i]);
+      acc[op.param_off + threadIdx.x] = sk;
+    }
+    __syncthreads();
+  }
+  __syncthreads();
+  const double mag = sqrt(tr.x * tr.x + tr.y * tr.y);
+  for (int k = threadIdx.x; k < P.n_params; k += blockDim.x) {
+    // Re(S) Re(S_k) + Im(S) Im(S_k) is invariant under conjugating both, so the <T,U>-form values can be used as is
+    double num = tr.x * acc[k].x + tr.y * acc[k].y;
+    grad[k] = (mag == 0.0) ? __longlong_as_double(0x7ff0000000000000LL) : -num / (N * mag);
+  }
+  __syncthreads();
+  return 1.0 - mag / N;
+}
+
 template <int NQ>
 QSB_GLOBAL qsb_k_hs(QsbBatchArgs a) {
   constexpr int N = 1 << NQ, NN = N * N;
@@ -281,76 +358,14 @@ QSB_GLOBAL qsb_k_hs(QsbBatchArgs a) {
   cplx* L = X + NN;
   cplx* red = L + NN;           // 32
   cplx* wpart = red + 32;       // [3][32]
-  cplx* acc = wpart + 96;       // [max_params] filled per op
+  cplx* acc = wpart + 96;       // [max_params]
   const long long p_base = a.param_off[a.first];
   for (int li = blockIdx.x; li < a.count; li += gridDim.x) {
     const int inst = a.first + li;
     const QsbDevProgram P = a.progs[a.prog_idx[inst]];
     double* trig = (double*)(acc + P.n_params);
-    qsb_fill_trig(P, a.params + a.param_off[inst], trig);
-    qsb_load_init<NQ>(X, nullptr, false);
-    qsb_load_init<NQ>(L, a.target, false);
-    __syncthreads();
-    qsb_forward<NQ>(X, P, trig);
-    cplx part = cmk(0, 0);
-    for (int e = threadIdx.x; e < NN; e += blockDim.x) part = cfma_conj(L[e], X[e], part);  // <T, U>
-    const cplx tr = qsb_block_sum(part, red);
-    const int w = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
-    for (int j = P.n_ops - 1; j >= 0; --j) {
-      const qsb_op op = P.ops[j];
-      const double* tj = trig + j * QSB_TRIG_STRIDE;
-      const int np = qsb_num_params(op.opcode);
-      if (np == 0) {
-        if (j == 0) break;
-        qsb_apply_left<NQ>(X, op, tj, P.consts, true);
-        qsb_apply_left<NQ>(L, op, tj, P.consts, true);
-        __syncthreads();
-        continue;
-      }
-      cplx gd[4], dg[3][4];
-      qsb_op2x2(op, tj, P.consts, true, gd);
-      for (int k = 0; k < np; ++k) qsb_gate2x2(op.opcode, tj, 1 + k, dg[k]);
-      cplx pk[3] = {cmk(0, 0), cmk(0, 0), cmk(0, 0)};
-      const int sh = NQ - 1 - op.q0, s = 1 << sh;
-      for (int idx = threadIdx.x; idx < NN / 2; idx += blockDim.x) {
-        int c = idx & (N - 1), r0 = qsb_insert_zero_bit(idx >> NQ, sh), r1 = r0 | s;
-        cplx xa = X[r0 * N + c], xb = X[r1 * N + c];
-        cplx ra = cfma(gd[1], xb, cmul(gd[0], xa)), rb = cfma(gd[3], xb, cmul(gd[2], xa));  // R_j pair
-        X[r0 * N + c] = ra; X[r1 * N + c] = rb;
-        cplx la = L[r0 * N + c], lb = L[r1 * N + c];
-        for (int k = 0; k < np; ++k) {
-          cplx ya = cfma(dg[k][1], rb, cmul(dg[k][0], ra)), yb = cfma(dg[k][3], rb, cmul(dg[k][2], ra));
-          pk[k] = cfma_conj(la, ya, pk[k]);
-          pk[k] = cfma_conj(lb, yb, pk[k]);
-        }
-        L[r0 * N + c] = cfma(gd[1], lb, cmul(gd[0], la));
-        L[r1 * N + c] = cfma(gd[3], lb, cmul(gd[2], la));
-      }
-      for (int k = 0; k < np; ++k) {
-        for (int m = 16; m > 0; m >>= 1) {
-          pk[k].x += __shfl_xor_sync(0xffffffffu, pk[k].x, m);
-          pk[k].y += __shfl_xor_sync(0xffffffffu, pk[k].y, m);
-        }
-        if ((threadIdx.x & 31) == 0) wpart[k * 32 + w] = pk[k];
-      }
-      __syncthreads();
-      if ((int)threadIdx.x < np) {
-        cplx sk = cmk(0, 0);
-        for (int i = 0; i < nw; ++i) sk = cadd(sk, wpart[threadIdx.x * 32 + i]);
-        acc[op.param_off + threadIdx.x] = sk;
-      }
-      // wpart is rewritten only after the next op's __syncthreads-separated phase; acc is read after the loop
-      __syncthreads();
-    }
-    __syncthreads();
-    const double mag = sqrt(tr.x * tr.x + tr.y * tr.y);
-    if (threadIdx.x == 0) a.out_a[li] = 1.0 - mag / N;
-    double* og = a.out_b + (a.param_off[inst] - p_base);
-    for (int k = threadIdx.x; k < P.n_params; k += blockDim.x) {
-      // Re(S) Re(S_k) + Im(S) Im(S_k) is invariant under conjugating both, so the <T,U>-form values can be used as is
-      double num = tr.x * acc[k].x + tr.y * acc[k].y;
-      og[k] = (mag == 0.0) ? __longlong_as_double(0x7ff0000000000000LL) : -num / (N * mag);
-    }
-    __syncthreads();
+    double f = qsb_hs_instance<NQ>(X, L, red, wpart, acc, trig, P, a.params + a.param_off[inst], a.target,
+                                   a.out_b + (a.param_off[inst] - p_base));
+    if (threadIdx.x == 0) a.out_a[li] = f;
   }
 }

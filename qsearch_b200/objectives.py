@@ -1,0 +1,64 @@
+"""Objective closures (reference: qsearch/objectives.py:37-61, MatrixDistanceObjective) evaluated on the GPU.
+
+Each ``gen_*`` binds ``options.target`` and a circuit and returns ``f(parameters)`` exactly like the reference, but
+the closure calls one fused device entry point (distance, HS value+gradient, residuals, residual Jacobian) instead of
+``circuit.matrix`` / ``circuit.mat_jac`` followed by NumPy arithmetic (qsearch/comparison.py:8-72).  The circuit may be
+a prepared ``CudaCircuit`` or any gate tree the lowering accepts.
+"""
+import numpy as np
+
+from . import _lib
+from .backends import program_for
+
+
+class Objective:
+    def gen_eval_func(self, circuit, options):
+        return self.gen_error_func(circuit, options)
+
+    def __eq__(self, other):
+        return type(self) == type(other)
+
+    def __hash__(self):
+        return hash(type(self).__name__)
+
+
+class MatrixDistanceObjective(Objective):
+    def gen_error_func(self, circuit, options):
+        """f(x) = |1 - |Tr(T^dagger U)|/N|   (comparison.matrix_distance_squared, comparison.py:8-22)."""
+        gp, T = program_for(circuit), np.asarray(options.target, dtype="complex128")
+
+        def generated_error_func(parameters):
+            return float(_lib.get_library().eval_distance([gp], [0], parameters, T)[0])
+        return generated_error_func
+
+    def gen_error_jac(self, circuit, options):
+        """(f, grad f)   (comparison.matrix_distance_squared_jac, comparison.py:37-55)."""
+        gp, T = program_for(circuit), np.asarray(options.target, dtype="complex128")
+
+        def generated_error_jac(parameters):
+            f, g = _lib.get_library().eval_hs_grad([gp], [0], parameters, T)
+            return float(f[0]), g
+        return generated_error_jac
+
+    def gen_error_residuals(self, circuit, options):
+        """r = [Re(U T^dagger - I); Im(U T^dagger)]   (comparison.matrix_residuals, comparison.py:57-64)."""
+        gp, T = program_for(circuit), np.asarray(options.target, dtype="complex128")
+
+        def generated_error_residuals(parameters):
+            return _lib.get_library().eval_residuals_jac([gp], [0], parameters, T)[0][0]
+        return generated_error_residuals
+
+    def gen_error_residuals_jac(self, circuit, options):
+        """J_r of shape (2N^2, P)   (comparison.matrix_residuals_jac, comparison.py:66-72)."""
+        gp, T = program_for(circuit), np.asarray(options.target, dtype="complex128")
+
+        def generated_error_residuals_jac(parameters):
+            return _lib.get_library().eval_residuals_jac([gp], [0], parameters, T)[1].T
+        return generated_error_residuals_jac
+
+    # batched form used by the search loop: distances of many (circuit, parameters) pairs in one launch
+    def eval_batch(self, circuits, parameter_vectors, options):
+        gps = [program_for(c) for c in circuits]
+        T = np.asarray(options.target, dtype="complex128")
+        flat = np.concatenate([np.asarray(v, dtype="float64").ravel() for v in parameter_vectors]) if gps else np.zeros(0)
+        return _lib.get_library().eval_distance(gps, np.arange(len(gps), dtype="int32"), flat, T)

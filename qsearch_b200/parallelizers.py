@@ -1,0 +1,79 @@
+"""Fan-out of one frontier expansion (reference: qsearch/parallelizers.py:34-157).
+
+The reference maps ``evaluate_step`` over the children of the popped nodes with one OS process per child
+(parallelizers.py:34-36, 67-84).  ``GpuParallelizer`` instead lowers every child, submits ONE batched solve
+(children x start vectors) that the C library splits into contiguous shards over the GPUs of its context (one stream
+per GPU, no collective: SURVEY.md section 8e), and yields the reference's tuples ``(step, (U, xopt), depth, weight)``.
+It runs in-process: no fork after CUDA initialisation (hard part 4).
+"""
+from . import _lib
+
+
+def default_num_tasks(opts):
+    """beams = num_tasks // branching_factor (compiler.py:89-93): one beam per visible GPU by default."""
+    import math
+    try:
+        ndev = _lib.get_library().num_devices
+    except Exception:
+        ndev = 1
+    bf = 1
+    try:
+        bf = max(1, opts.gateset.branching_factor(int(round(math.log2(opts.target.shape[0])))))
+    except Exception:
+        pass
+    return bf * max(1, ndev)
+
+
+class Parallelizer:
+    def __init__(self, options):
+        pass
+
+    def solve_circuits_parallel(self, tuples):
+        raise NotImplementedError
+
+    def done(self):
+        pass
+
+
+class GpuParallelizer(Parallelizer):
+    def __init__(self, options):
+        self.options = options
+        options.set_smart_defaults(num_tasks=default_num_tasks)
+
+    def solve_frontier(self, tuples):
+        """One batched solve for a whole expansion.  Returns (step, (U, xopt), depth, weight, distance): the final
+        objective value rides along, which saves the two host re-evaluations per child the reference performs
+        (compiler.py:147,155)."""
+        tuples = list(tuples)
+        if not tuples:
+            return []
+        options = self.options
+        solver = options.solver
+        steps = [t[0] for t in tuples]
+        if hasattr(solver, "solve_batch"):
+            res = solver.solve_batch(steps, options)
+            return [(step, (res.matrices[i], res.x[i]), depth, weight, res.distance[i])
+                    for i, (step, depth, weight) in enumerate(tuples)]
+        # a solver without a batched form: evaluate_step one by one (parallelizers.py:34-36)
+        backend, out = options.backend, []
+        for step, depth, weight in tuples:
+            U, x = solver.solve_for_unitary(backend.prepare_circuit(step, options), options)
+            out.append((step, (U, x), depth, weight, options.objective.gen_eval_func(step, options)(x)))
+        return out
+
+    def solve_circuits_parallel(self, tuples):
+        """The reference's contract (parallelizers.py:44-52): iterable of (step, (U, xopt), depth, weight)."""
+        return [t[:4] for t in self.solve_frontier(tuples)]
+
+
+class SequentialParallelizer(Parallelizer):
+    """One solve at a time through Backend.prepare_circuit + Solver.solve_for_unitary (parallelizers.py:149-157)."""
+
+    def __init__(self, options):
+        self.options = options
+        options.set_smart_defaults(num_tasks=lambda opts: 1)
+
+    def solve_circuits_parallel(self, tuples):
+        o = self.options
+        return [(step, o.solver.solve_for_unitary(o.backend.prepare_circuit(step, o), o), depth, weight)
+                for step, depth, weight in tuples]

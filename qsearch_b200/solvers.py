@@ -1,0 +1,201 @@
+"""Solvers behind the reference's ``Solver.solve_for_unitary(circuit, options, x0=None) -> (U, xopt)`` interface
+(qsearch/solvers.py:88-163), running as batched on-device optimisers (csrc/qsb_solver.cuh, csrc/qsb_lbfgs.cuh).
+
+* ``LeastSquares_Jac_Solver``: Levenberg-Marquardt on the residuals ``[Re(U T^dagger - I); Im(U T^dagger)]``
+  (role of scipy ``least_squares(method='lm')``, solvers.py:146-163, and of Ceres LM, qsrs/src/solvers.rs:88-121).
+* ``BFGS_Jac_Solver``: L-BFGS on the Hilbert-Schmidt distance (role of scipy BFGS, solvers.py:138-144, and of NLopt
+  LD_LBFGS, qsrs/src/solvers.rs:33-74).
+* ``MultiStart_Solver`` / ``NaiveMultiStart_Solver``: the multistart axis of qsearch/multistart_solvers.py:32-144 as a
+  batch axis: sample points are scored in one launch and the local solves run as one batch.
+
+Every solver also has ``solve_batch(circuits, options, x0s=None)``: one launch for a whole frontier expansion
+(children x starts), which is what ``GpuParallelizer`` calls.  Start vectors are uniform in [0, 2 pi) unless given
+(solvers.py:155,157).  Solvers are stateless and picklable (constructor arguments only).
+"""
+import numpy as np
+
+from . import _lib
+from .backends import program_for
+
+
+def _target_of(options):
+    return np.ascontiguousarray(options.target, dtype="complex128")
+
+
+def _tolerances(options):
+    # solvers.py:154-155: tighter tolerances under max_quality_optimization
+    if "max_quality_optimization" in options and options.max_quality_optimization:
+        return dict(ftol=5e-16, xtol=5e-16, gtol=1e-15)
+    return dict(ftol=1e-8, xtol=1e-8, gtol=1e-8)
+
+
+class BatchResult:
+    """Best start per circuit of one batched solve."""
+    __slots__ = ("x", "distance", "iterations", "status", "matrices")
+
+    def __init__(self, x, distance, iterations, status, matrices):
+        self.x, self.distance, self.iterations, self.status, self.matrices = x, distance, iterations, status, matrices
+
+
+class Solver:
+    """Interface (reference: qsearch/solvers.py:88-104)."""
+    method = None
+    starts = 1
+
+    def solve_for_unitary(self, circuit, options, x0=None):
+        res = self.solve_batch([circuit], options, None if x0 is None else [np.asarray(x0, dtype="float64")])
+        return (res.matrices[0], res.x[0])
+
+    def _start_points(self, gp, options, rng):
+        return rng.random((self.starts, gp.n_params)) * (2 * np.pi)
+
+    def _solve_opts(self, options):
+        return _tolerances(options)
+
+    def solve_batch(self, circuits, options, x0s=None, want_matrices=True):
+        """Solve every circuit from `starts` start vectors each, in one launch; keep the best start per circuit.
+        x0s: optional list (one entry per circuit) of a vector or an array [k, P] of start vectors."""
+        lib = _lib.get_library()
+        T = _target_of(options)
+        gps = [program_for(c) for c in circuits]
+        rng = np.random.default_rng(options.seed) if "seed" in options and options.seed is not None else np.random.default_rng()
+        poi, chunks, owner = [], [], []
+        for ci, gp in enumerate(gps):
+            if x0s is not None and x0s[ci] is not None:
+                pts = np.atleast_2d(np.asarray(x0s[ci], dtype="float64"))
+            else:
+                pts = self._start_points(gp, options, rng)
+            for p in pts:
+                if p.size != gp.n_params:
+                    raise ValueError("start vector of length {} for a circuit with {} parameters".format(p.size, gp.n_params))
+                poi.append(ci)
+                chunks.append(p)
+                owner.append(ci)
+        flat = np.concatenate(chunks) if chunks else np.zeros(0)
+        x, f, iters, status = lib.solve(self.method, gps, poi, flat, T, **self._solve_opts(options))
+        owner = np.asarray(owner)
+        offs = np.concatenate([[0], np.cumsum([gps[c].n_params for c in owner])]).astype(np.int64)
+        best_x, best_f, best_it, best_st = [], [], [], []
+        for ci in range(len(gps)):
+            idx = np.nonzero(owner == ci)[0]
+            fi = np.where(np.isnan(f[idx]), np.inf, f[idx])
+            b = idx[int(np.argmin(fi))]
+            best_x.append(x[offs[b]:offs[b + 1]].copy())
+            best_f.append(float(f[b]))
+            best_it.append(int(iters[b]))
+            best_st.append(int(status[b]))
+        mats = None
+        if want_matrices and gps:
+            mats = lib.eval_matrix(gps, np.arange(len(gps), dtype="int32"), np.concatenate(best_x) if best_x else np.zeros(0))
+        return BatchResult(best_x, best_f, best_it, best_st, mats)
+
+    def __eq__(self, other):
+        return type(self) == type(other) and self.__dict__ == other.__dict__
+
+    def __hash__(self):
+        return hash(type(self).__name__)
+
+
+class LeastSquares_Jac_Solver(Solver):
+    """Batched Levenberg-Marquardt on the device (qsb_solve_lm)."""
+    method = "lm"
+
+    def __init__(self, starts=1, max_iters=0):
+        self.starts = int(starts)
+        self.max_iters = int(max_iters)
+
+    def _solve_opts(self, options):
+        o = _tolerances(options)
+        o["max_iters"] = self.max_iters
+        return o
+
+    @property
+    def distance_metric(self):
+        return "Residuals"
+
+
+class BFGS_Jac_Solver(Solver):
+    """Batched L-BFGS on the device (qsb_solve_lbfgs); memory 10 like the native solver (qsrs/src/lib.rs:402-413)."""
+    method = "lbfgs"
+
+    def __init__(self, starts=1, memory_size=10, max_iters=0):
+        self.starts = int(starts)
+        self.memory_size = int(memory_size)
+        self.max_iters = int(max_iters)
+
+    def _solve_opts(self, options):
+        thr = options.threshold if "threshold" in options else 1e-10
+        strict = "max_quality_optimization" in options and options.max_quality_optimization
+        # scipy BFGS: gtol = options.threshold (solvers.py:142); NLopt: stopval 1e-16 (solvers.rs:64)
+        return dict(gtol=1e-15 if strict else thr, ftol=1e-15, stop_value=1e-16, lbfgs_memory=self.memory_size,
+                    max_iters=self.max_iters)
+
+    @property
+    def distance_metric(self):
+        return "Frobenius"
+
+
+class NaiveMultiStart_Solver(Solver):
+    """`num_threads` uniform random starts of the inner solver, best result kept
+    (reference: qsearch/multistart_solvers.py:112-144)."""
+
+    def __init__(self, num_threads, inner_solver=None):
+        self.num_threads = int(num_threads)
+        self.inner_solver = inner_solver
+
+    def _inner(self, options):
+        inner = self.inner_solver
+        if inner is None:
+            inner = options.inner_solver if "inner_solver" in options else LeastSquares_Jac_Solver()
+        return inner
+
+    @property
+    def distance_metric(self):
+        return (self.inner_solver or LeastSquares_Jac_Solver()).distance_metric
+
+    def solve_batch(self, circuits, options, x0s=None, want_matrices=True):
+        inner = self._inner(options)
+        gps = [program_for(c) for c in circuits]
+        rng = np.random.default_rng(options.seed) if "seed" in options and options.seed is not None else np.random.default_rng()
+        starts = []
+        for ci, gp in enumerate(gps):
+            pts = rng.random((self.num_threads, gp.n_params)) * (2 * np.pi)
+            if x0s is not None and x0s[ci] is not None:
+                pts[0] = np.asarray(x0s[ci], dtype="float64")
+            starts.append(pts)
+        return inner.solve_batch(circuits, options, starts, want_matrices)
+
+
+class MultiStart_Solver(NaiveMultiStart_Solver):
+    """Sample-then-refine multistart (reference: qsearch/multistart_solvers.py:44-110): 100 uniform samples of the
+    error function per circuit (scored in ONE launch), then `num_threads` local solves from the best distinct
+    samples, run as one batch, argmin kept.  The reference picks its start points with APOSMM's r_k rule
+    (persistent_aposmm.py:421-541); here the starts are simply the lowest-valued samples - the APOSMM bookkeeping is
+    host-side control flow outside the hot path."""
+    n_samples = 100
+
+    def solve_batch(self, circuits, options, x0s=None, want_matrices=True):
+        inner = self._inner(options)
+        lib = _lib.get_library()
+        T = _target_of(options)
+        gps = [program_for(c) for c in circuits]
+        rng = np.random.default_rng(options.seed) if "seed" in options and options.seed is not None else np.random.default_rng()
+        samples = [rng.random((self.n_samples, gp.n_params)) * (2 * np.pi) for gp in gps]
+        poi = np.repeat(np.arange(len(gps), dtype="int32"), self.n_samples)
+        vals = lib.eval_distance(gps, poi, np.concatenate([s.ravel() for s in samples]) if gps else np.zeros(0), T)
+        vals = vals.reshape(len(gps), self.n_samples)
+        starts = []
+        for ci in range(len(gps)):
+            order = np.argsort(vals[ci])[: self.num_threads]
+            pts = samples[ci][order]
+            if x0s is not None and x0s[ci] is not None:
+                pts = np.vstack([np.asarray(x0s[ci], dtype="float64")[None, :], pts[:-1]]) if len(pts) > 1 else \
+                    np.asarray(x0s[ci], dtype="float64")[None, :]
+            starts.append(pts)
+        return inner.solve_batch(circuits, options, starts, want_matrices)
+
+
+def default_solver(options=None):
+    """The reference picks the least-squares solver whenever the gateset has Jacobians (solvers.py:19-86); every gate
+    the lowering accepts has one on the device, so that is always the choice here."""
+    return LeastSquares_Jac_Solver()

@@ -2,12 +2,13 @@
 //
 // A tiny host emulation of the CUDA execution model so that the *same* kernel source in
 // qsearch_b200/csrc/ can be compiled with g++ (-DQSB_EMU) and exercised by the CPU test-suite in the
-// build container, which has no GPU.  Every CUDA thread of a block is a real std::thread; __syncthreads
-// and warp primitives are std::barrier exchanges.  Blocks of a launch run one after another.
+// build container, which has no GPU.  Every CUDA thread of a block is a user-level fiber (own stack, hand-written
+// x86-64 context switch) scheduled round-robin inside one OS thread; __syncthreads and the warp primitives are
+// barrier counters that yield to the next fiber.  Blocks of a launch are spread over a few OS worker threads.
 // The product library (libqsb200.so) is built by nvcc without QSB_EMU and never sees this file.
 #pragma once
+#include <algorithm>
 #include <atomic>
-#include <barrier>
 #include <cmath>
 #include <cstdint>
 #include <cstdio>
@@ -29,25 +30,54 @@
 
 struct double2 { double x, y; };
 static inline double2 make_double2(double x, double y) { return double2{x, y}; }
-struct dim3 { unsigned x = 1, y = 1, z = 1; dim3(unsigned a = 1, unsigned b = 1, unsigned c = 1) : x(a), y(b), z(c) {} };
 
 namespace qsb_emu {
+struct Fiber {
+  void* sp = nullptr;
+  unsigned tid = 0;
+  bool done = false;
+  std::vector<unsigned char> stack;
+};
 struct BlockState {
-  std::unique_ptr<std::barrier<>> block_bar;
-  std::vector<std::unique_ptr<std::barrier<>>> warp_bar;
+  unsigned nthreads = 0, block = 0, grid = 0;
+  std::vector<Fiber> fibers;
+  unsigned current = 0, alive = 0;
+  void* sched_sp = nullptr;
+  unsigned block_arrived = 0;
+  unsigned long block_gen = 0;
+  std::vector<unsigned> warp_arrived, warp_alive;
+  std::vector<unsigned long> warp_gen;
   std::vector<std::vector<uint64_t>> warp_buf;  // [warp][32]
   unsigned char* smem = nullptr;
+  const std::function<void()>* body = nullptr;
 };
-inline BlockState*& cur() { static BlockState* p = nullptr; return p; }
+inline BlockState*& cur() { static thread_local BlockState* p = nullptr; return p; }
+extern "C" void qsb_emu_switch(void** save_sp, void* load_sp);
+inline void yield_to_scheduler() {
+  BlockState* st = cur();
+  qsb_emu_switch(&st->fibers[st->current].sp, st->sched_sp);
+}
 }  // namespace qsb_emu
 
-extern thread_local dim3 threadIdx, blockIdx, blockDim, gridDim;
-#ifdef QSB_EMU_DEFINE
-thread_local dim3 threadIdx, blockIdx, blockDim, gridDim;
-#endif
+struct qsb_emu_idx { unsigned x, y, z; };
+#define threadIdx (qsb_emu_idx{qsb_emu::cur()->fibers[qsb_emu::cur()->current].tid, 0u, 0u})
+#define blockIdx (qsb_emu_idx{qsb_emu::cur()->block, 0u, 0u})
+#define blockDim (qsb_emu_idx{qsb_emu::cur()->nthreads, 1u, 1u})
+#define gridDim (qsb_emu_idx{qsb_emu::cur()->grid, 1u, 1u})
 
-static inline void __syncthreads() { qsb_emu::cur()->block_bar->arrive_and_wait(); }
-static inline void __syncwarp(unsigned = 0xffffffffu) { qsb_emu::cur()->warp_bar[threadIdx.x / 32]->arrive_and_wait(); }
+static inline void __syncthreads() {
+  auto* st = qsb_emu::cur();
+  const unsigned long gen = st->block_gen;
+  if (++st->block_arrived >= st->alive) { st->block_arrived = 0; ++st->block_gen; return; }
+  while (st->block_gen == gen) qsb_emu::yield_to_scheduler();
+}
+static inline void __syncwarp(unsigned = 0xffffffffu) {
+  auto* st = qsb_emu::cur();
+  const unsigned w = st->fibers[st->current].tid / 32;
+  const unsigned long gen = st->warp_gen[w];
+  if (++st->warp_arrived[w] >= st->warp_alive[w]) { st->warp_arrived[w] = 0; ++st->warp_gen[w]; return; }
+  while (st->warp_gen[w] == gen) qsb_emu::yield_to_scheduler();
+}
 
 template <class T>
 static inline T qsb_emu_xchg(T v, int src_lane) {
@@ -57,9 +87,9 @@ static inline T qsb_emu_xchg(T v, int src_lane) {
   uint64_t raw = 0;
   std::memcpy(&raw, &v, sizeof(T));
   st->warp_buf[w][l] = raw;
-  st->warp_bar[w]->arrive_and_wait();
+  __syncwarp();
   uint64_t got = st->warp_buf[w][src_lane & 31];
-  st->warp_bar[w]->arrive_and_wait();
+  __syncwarp();
   T out;
   std::memcpy(&out, &got, sizeof(T));
   return out;
@@ -121,33 +151,100 @@ static inline cudaError_t cudaMemGetInfo(size_t* f, size_t* t) { *f = *t = (size
 
 // ------------------------------------------------------------------ kernel launch
 namespace qsb_emu {
-template <class F>
-inline void launch(unsigned grid, unsigned block, size_t smem_bytes, F body) {
-  BlockState st;
-  st.block_bar = std::make_unique<std::barrier<>>(block);
-  unsigned nw = (block + 31) / 32;
-  for (unsigned w = 0; w < nw; ++w) {
-    unsigned cnt = (w + 1) * 32 <= block ? 32 : block - w * 32;
-    st.warp_bar.push_back(std::make_unique<std::barrier<>>(cnt));
-    st.warp_buf.emplace_back(32, 0);
+#ifdef QSB_EMU_DEFINE
+asm(R"(
+.text
+.globl qsb_emu_switch
+.type qsb_emu_switch,@function
+qsb_emu_switch:
+  pushq %rbp
+  pushq %rbx
+  pushq %r12
+  pushq %r13
+  pushq %r14
+  pushq %r15
+  movq %rsp, (%rdi)
+  movq %rsi, %rsp
+  popq %r15
+  popq %r14
+  popq %r13
+  popq %r12
+  popq %rbx
+  popq %rbp
+  ret
+)");
+extern "C" void qsb_emu_fiber_main() {
+  BlockState* st = cur();
+  (*st->body)();
+  st = cur();
+  Fiber& f = st->fibers[st->current];
+  f.done = true;
+  --st->alive;
+  const unsigned w = f.tid / 32;
+  --st->warp_alive[w];
+  // a finished fiber may complete a barrier the others are already waiting on
+  if (st->alive && st->block_arrived >= st->alive) { st->block_arrived = 0; ++st->block_gen; }
+  if (st->warp_alive[w] && st->warp_arrived[w] >= st->warp_alive[w]) { st->warp_arrived[w] = 0; ++st->warp_gen[w]; }
+  yield_to_scheduler();
+  std::abort();  // a finished fiber is never resumed
+}
+#else
+extern "C" void qsb_emu_fiber_main();
+#endif
+
+inline void run_block(BlockState& st, unsigned block_index) {
+  constexpr size_t STACK = 96 * 1024;
+  st.block = block_index;
+  st.alive = st.nthreads;
+  st.block_arrived = 0;
+  const unsigned nw = (st.nthreads + 31) / 32;
+  st.warp_arrived.assign(nw, 0);
+  st.warp_gen.assign(nw, 0);
+  st.warp_alive.assign(nw, 0);
+  for (unsigned t = 0; t < st.nthreads; ++t) {
+    Fiber& f = st.fibers[t];
+    if (f.stack.empty()) f.stack.resize(STACK);
+    f.tid = t;
+    f.done = false;
+    ++st.warp_alive[t / 32];
+    uintptr_t top = ((uintptr_t)f.stack.data() + STACK) & ~(uintptr_t)15;
+    void** sp = (void**)top;
+    *--sp = nullptr;                              // fake return address of the entry function
+    *--sp = (void*)&qsb_emu_fiber_main;           // popped by `ret` of the first switch
+    for (int i = 0; i < 6; ++i) *--sp = nullptr;  // rbp rbx r12..r15
+    f.sp = sp;
   }
-  std::vector<unsigned char> sm(smem_bytes + 64);
-  st.smem = (unsigned char*)(((uintptr_t)sm.data() + 63) & ~(uintptr_t)63);
   cur() = &st;
+  while (st.alive) {
+    for (unsigned t = 0; t < st.nthreads && st.alive; ++t) {
+      if (st.fibers[t].done) continue;
+      st.current = t;
+      qsb_emu_switch(&st.sched_sp, st.fibers[t].sp);
+    }
+  }
+}
+
+inline void launch(unsigned grid, unsigned block, size_t smem_bytes, const std::function<void()>& body) {
+  unsigned workers = std::min<unsigned>(grid, std::max(1u, std::thread::hardware_concurrency()));
+  std::atomic<unsigned> next{0};
+  auto work = [&] {
+    BlockState st;
+    st.nthreads = block;
+    st.grid = grid;
+    st.fibers.resize(block);
+    st.warp_buf.assign((block + 31) / 32, std::vector<uint64_t>(32, 0));
+    std::vector<unsigned char> sm(smem_bytes + 64);
+    st.smem = (unsigned char*)(((uintptr_t)sm.data() + 63) & ~(uintptr_t)63);
+    st.body = &body;
+    for (unsigned b = next.fetch_add(1); b < grid; b = next.fetch_add(1)) run_block(st, b);
+    cur() = nullptr;
+  };
+  if (workers <= 1) { work(); return; }
   std::vector<std::thread> th;
-  for (unsigned t = 0; t < block; ++t)
-    th.emplace_back([&, t] {
-      threadIdx = dim3(t); blockDim = dim3(block); gridDim = dim3(grid);
-      for (unsigned b = 0; b < grid; ++b) {
-        blockIdx = dim3(b);
-        body();
-        st.block_bar->arrive_and_wait();
-      }
-    });
+  for (unsigned w = 0; w < workers; ++w) th.emplace_back(work);
   for (auto& x : th) x.join();
-  cur() = nullptr;
 }
 }  // namespace qsb_emu
 #define QSB_DYN_SMEM(name) unsigned char* name = qsb_emu::cur()->smem
 #define QSB_LAUNCH(kernel, grid, block, smem, stream, ...) \
-  qsb_emu::launch((grid), (block), (smem), [&] { kernel(__VA_ARGS__); })
+  qsb_emu::launch((grid), (block), (smem), std::function<void()>([&] { kernel(__VA_ARGS__); }))

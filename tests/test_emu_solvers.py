@@ -1,0 +1,118 @@
+"""CPU suite: the batched on-device solvers and the search host code, run on the host emulation of the kernels."""
+import pickle
+
+import numpy as np
+import pytest
+
+import qsearch_b200 as q
+from oracle import qs_oracle as O
+from qsearch_b200 import _lib, gates, gatesets, lowering, solvers, unitaries
+from tests.emu import emulated_library
+
+
+@pytest.fixture(scope="module")
+def emu():
+    lib = emulated_library()
+    prev = _lib.use_library(lib)
+    yield lib
+    _lib.use_library(prev)
+
+
+def _reachable_problem(n, depth, seed):
+    rng = np.random.default_rng(seed)
+    g = gatesets.QubitCNOTLinear()
+    c = gates.ProductGate(g.initial_layer(n))
+    layers = g.search_layers(n)
+    for _ in range(depth):
+        c = c.appending(layers[int(rng.integers(len(layers)))][0])
+    return c, O.matrix(c, rng.random(c.num_inputs) * 2 * np.pi), rng
+
+
+@pytest.mark.parametrize("method", ["lm", "lbfgs"])
+def test_solvers_reach_a_reachable_target(emu, method):
+    c, T, rng = _reachable_problem(2, 3, 11)
+    gp = lowering.lower(c)
+    x0 = rng.random((4, gp.n_params)) * 2 * np.pi
+    x, f, iters, status = emu.solve(method, [gp], np.zeros(4, dtype="int32"), x0, T)
+    assert f.min() < 1e-12
+    for k, xk in enumerate(x.reshape(4, -1)):  # the reported distance is the distance at the returned parameters
+        assert abs(O.matrix_distance_squared(T, O.matrix(c, xk)) - f[k]) < 1e-12
+    assert (iters > 0).all()
+
+
+def test_solver_interface_and_pickle(emu):
+    c, T, _ = _reachable_problem(2, 2, 5)
+    opts = q.Options(target=T, seed=3)
+    opts.set_defaults(**q.defaults.standard_defaults)
+    for s in (solvers.LeastSquares_Jac_Solver(starts=3), solvers.BFGS_Jac_Solver(starts=3),
+              solvers.NaiveMultiStart_Solver(3), solvers.MultiStart_Solver(3)):
+        s2 = pickle.loads(pickle.dumps(s))
+        assert s2 == s
+        U, x = s2.solve_for_unitary(q.backends.CudaBackend().prepare_circuit(c), opts)
+        assert U.shape == T.shape and x.shape == (c.num_inputs,)
+        assert O.matrix_distance_squared(T, U) < 1e-10
+        assert np.abs(U - O.matrix(c, x)).max() < 1e-12
+    assert solvers.LeastSquares_Jac_Solver().distance_metric == "Residuals"
+    assert solvers.BFGS_Jac_Solver().distance_metric == "Frobenius"
+    b = pickle.loads(pickle.dumps(q.backends.CudaBackend()))
+    circ = pickle.loads(pickle.dumps(b.prepare_circuit(c)))
+    assert circ.num_inputs == c.num_inputs
+
+
+def test_objective_closures_match_oracle(emu):
+    c, T, rng = _reachable_problem(3, 2, 9)
+    opts = q.Options(target=T)
+    obj = q.objectives.MatrixDistanceObjective()
+    x = rng.random(c.num_inputs) * 2 * np.pi
+    U, J = O.mat_jac(c, x)
+    assert abs(obj.gen_error_func(c, opts)(x) - O.matrix_distance_squared(T, U)) < 1e-12
+    f, g = obj.gen_error_jac(c, opts)(x)
+    fo, go = O.matrix_distance_squared_jac(T, U, J)
+    assert abs(f - fo) < 1e-12 and np.abs(g - go).max() < 1e-12
+    assert np.abs(obj.gen_error_residuals(c, opts)(x) - O.matrix_residuals(T, U)).max() < 1e-12
+    Jr = obj.gen_error_residuals_jac(c, opts)(x)
+    assert Jr.shape == (2 * 64, c.num_inputs) and np.abs(Jr - O.matrix_residuals_jac(T, U, J)).max() < 1e-12
+
+
+def test_search_compiler_qft2(emu):
+    T = unitaries.qft(4)
+    res = q.SearchCompiler().compile(q.Options(target=T, seed=1))
+    assert repr(res["structure"]).count("CNOTGate") == 3  # tests/test_solvers.py compiles qft(4); reference finds 3 CNOTs
+    assert O.matrix_distance_squared(T, O.matrix(res["structure"], res["parameters"])) < 1e-10
+
+
+def test_leap_compiler_qft2(emu):
+    T = unitaries.qft(4)
+    res = q.LeapCompiler().compile(q.Options(target=T, seed=2, min_depth=1))
+    assert O.matrix_distance_squared(T, O.matrix(res["structure"], res["parameters"])) < 1e-10
+    assert res["cut_depths"][0] == 0 and res["cut_depths"][-1] == repr(res["structure"]).count("CNOTGate")
+
+
+def test_options_semantics():
+    o = q.Options(a=1)
+    o.set_defaults(b=2, c=3)
+    o.set_smart_defaults(c=lambda opts: opts.a + opts.b)
+    assert (o.a, o.b, o.c) == (1, 2, 3) and "c" in o and "zzz" not in o
+    o2 = o.updated(a=10)
+    assert o2.c == 12 and o.c == 3
+    with pytest.raises(AttributeError):
+        o.make_required("target")
+    assert pickle.loads(pickle.dumps(q.Options(a=1, b=[1, 2]))).b == [1, 2]
+
+
+@pytest.mark.reference
+def test_drop_in_for_the_reference_compiler(emu):
+    """The GPU Backend / Solver / Parallelizer plugged into the reference's own SearchCompiler and Options."""
+    import sys
+    sys.path.insert(0, "/root/reference")
+    import qsearch
+    from qsearch import unitaries as ru
+    opts = qsearch.Options(target=ru.qft(4), backend=q.backends.CudaBackend(), solver=solvers.LeastSquares_Jac_Solver(),
+                           parallelizer=q.parallelizers.GpuParallelizer, verbosity=0, stdout_enabled=False)
+    res = qsearch.SearchCompiler().compile(opts)
+    assert repr(res["structure"]).count("CNOTGate") == 3
+    assert qsearch.comparison.matrix_distance_squared(ru.qft(4), res["structure"].matrix(res["parameters"])) < 1e-10
+    # and through the reference's evaluate_step with its sequential parallelizer
+    opts2 = opts.updated(parallelizer=qsearch.parallelizers.SequentialParallelizer)
+    res2 = qsearch.SearchCompiler().compile(opts2)
+    assert qsearch.comparison.matrix_distance_squared(ru.qft(4), res2["structure"].matrix(res2["parameters"])) < 1e-10

@@ -1,0 +1,64 @@
+#!/usr/bin/env python
+"""End-to-end synthesis timings on the GPU box (BASELINE.json configs 0,1,2,4): wall seconds, CNOT counts, distances.
+
+    python tools/synth_bench.py [--cases qft3,toffoli,...] [--reps 3] [--starts 4] [--solver lm|lbfgs]
+"""
+import argparse
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import qsearch_b200 as q  # noqa: E402
+from qsearch_b200 import gatesets, solvers, unitaries, _lib  # noqa: E402
+
+YORKTOWN = [(0, 1), (0, 2), (1, 2), (2, 3), (2, 4), (3, 4)]  # examples/qft5_ibm_yorktown.py:21
+
+CASES = {
+    "qft3": (lambda: unitaries.qft(8), gatesets.QubitCNOTLinear, "search"),
+    "toffoli": (lambda: unitaries.toffoli, gatesets.QubitCNOTLinear, "search"),
+    "fredkin": (lambda: unitaries.fredkin, gatesets.QubitCNOTLinear, "search"),
+    "peres": (lambda: unitaries.peres, gatesets.QubitCNOTLinear, "search"),
+    "or": (lambda: unitaries.logical_or, gatesets.QubitCNOTLinear, "search"),
+    "toffoli_ring": (lambda: unitaries.toffoli, gatesets.QubitCNOTRing, "search"),
+    "qft3_ring": (lambda: unitaries.qft(8), gatesets.QubitCNOTRing, "search"),
+    "qft4_leap": (lambda: unitaries.qft(16), gatesets.QubitCNOTLinear, "leap"),
+    "qft4_search": (lambda: unitaries.qft(16), gatesets.QubitCNOTLinear, "search"),
+    "qft5_yorktown_leap": (lambda: unitaries.qft(32), lambda: gatesets.QubitCNOTAdjacencyList(YORKTOWN), "leap"),
+}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--cases", default="qft3,toffoli,qft4_leap")
+    ap.add_argument("--reps", type=int, default=2)
+    ap.add_argument("--starts", type=int, default=1)
+    ap.add_argument("--solver", default="lm")
+    ap.add_argument("--min-depth", type=int, default=3)
+    ap.add_argument("--timeout", type=float, default=600)
+    a = ap.parse_args()
+    lib = _lib.get_library()
+    print("library:", lib.version(), "devices:", lib.num_devices, flush=True)
+    for name in a.cases.split(","):
+        mk_t, mk_gs, kind = CASES[name]
+        T = mk_t()
+        for rep in range(a.reps):
+            solver = solvers.LeastSquares_Jac_Solver(starts=a.starts) if a.solver == "lm" else solvers.BFGS_Jac_Solver(starts=a.starts)
+            opts = q.Options(target=T, gateset=mk_gs(), solver=solver, seed=1000 + rep, timeout=a.timeout)
+            if kind == "leap":
+                opts.min_depth = a.min_depth
+            comp = q.LeapCompiler() if kind == "leap" else q.SearchCompiler()
+            l0 = lib.launch_count()
+            t0 = time.perf_counter()
+            res = comp.compile(opts)
+            dt = time.perf_counter() - t0
+            print(json.dumps({"case": name, "rep": rep, "solver": a.solver, "starts": a.starts, "wall_s": round(dt, 3),
+                              "cnots": repr(res["structure"]).count("CNOTGate"), "distance": float(res["distance"]),
+                              "stats": res["stats"], "launches": lib.launch_count() - l0}), flush=True)
+
+
+if __name__ == "__main__":
+    main()
