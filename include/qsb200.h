@@ -113,6 +113,12 @@ int qsb_eval_residuals_jac(qsb_ctx* ctx, int n_programs, const qsb_program* cons
 int qsb_batch_create(qsb_ctx* ctx, int device_slot, int n_programs, const qsb_program* const* progs,
                      int n_instances, const int32_t* prog_of_instance, qsb_batch** out_batch);
 int qsb_batch_destroy(qsb_batch* batch);
+/* Kernel family of a batch: QSB_KERNEL_AUTO picks the register-resident DMMA warp kernels where they apply (one-qubit
+ * leaves + CNOT, 3..5 qubits) and the shared-memory interpreter otherwise; QSB_KERNEL_GENERIC forces the interpreter
+ * (parity tests and profiling compare the two).  QSB_KERNEL=generic in the environment sets the default of a context. */
+#define QSB_KERNEL_AUTO 0
+#define QSB_KERNEL_GENERIC 1
+int qsb_batch_set_kernel(qsb_batch* batch, int kind);
 int qsb_batch_set_params(qsb_batch* batch, const double* params, size_t n_doubles); /* H2D */
 int qsb_batch_set_target(qsb_batch* batch, const double* target);                   /* H2D, [N][N][2] */
 /* Launch on the batch's stream over instances [first, first+count); outputs land in device buffers sized for

@@ -2,6 +2,7 @@
 // host-buffer evaluation calls.  Replaces the PyO3 boundary of the reference (qsrs/src/lib.rs).
 #include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <string>
@@ -9,6 +10,7 @@
 
 #include "qsb_host.h"
 #include "qsb_generic.cuh"
+#include "qsb_warp.cuh"
 #include "qsb_launch.h"
 
 // ---------------------------------------------------------------------------- errors
@@ -51,6 +53,7 @@ extern "C" int qsb_init(int n_devices, const int* device_ids, qsb_ctx** out_ctx)
   }
   qsb_ctx* ctx = new (std::nothrow) qsb_ctx();
   if (!ctx) return qsb_fail(QSB_ERR_NOMEM, "out of host memory");
+  if (const char* k = getenv("QSB_KERNEL")) ctx->force_generic = (strcmp(k, "generic") == 0);
   for (int id : ids) {
     QsbDevice d;
     d.id = id;
@@ -143,16 +146,31 @@ extern "C" int qsb_program_create(qsb_ctx* ctx, int n_qubits, int n_ops, const q
   p->n_qubits = n_qubits; p->n_ops = n_ops; p->n_params = n_params; p->fast_ok = fast;
   p->ops.assign(ops, ops + n_ops);
   if (const_len) p->consts.assign(const_pool, const_pool + const_len);
+  std::vector<double> pscale(std::max(1, n_params), 1.0);  // angle scale per parameter (half angles: gates.py:324-346 etc.)
+  for (int j = 0; j < n_ops; ++j) {
+    const qsb_op& o = ops[j];
+    switch (o.opcode) {
+      case QSB_OP_RX: case QSB_OP_RY: case QSB_OP_RZ: pscale[o.param_off] = 0.5; break;
+      case QSB_OP_U3: pscale[o.param_off] = 0.5; break;
+      case QSB_OP_XZXZ: pscale[o.param_off] = pscale[o.param_off + 1] = 0.5; break;
+      case QSB_OP_ZXZXZ: pscale[o.param_off] = pscale[o.param_off + 1] = pscale[o.param_off + 2] = 0.5; break;
+      default: break;
+    }
+  }
   for (auto& d : ctx->devs) {
     qsb_op* dops = nullptr;
     double* dc = nullptr;
+    double* dps = nullptr;
     QSB_CUDA(cudaSetDevice(d.id));
     QSB_CUDA(cudaMalloc((void**)&dops, sizeof(qsb_op) * std::max(1, n_ops)));
     QSB_CUDA(cudaMalloc((void**)&dc, sizeof(double) * std::max<size_t>(1, const_len)));
     if (n_ops) QSB_CUDA(cudaMemcpy(dops, ops, sizeof(qsb_op) * n_ops, cudaMemcpyHostToDevice));
     if (const_len) QSB_CUDA(cudaMemcpy(dc, const_pool, sizeof(double) * const_len, cudaMemcpyHostToDevice));
+    QSB_CUDA(cudaMalloc((void**)&dps, sizeof(double) * pscale.size()));
+    QSB_CUDA(cudaMemcpy(dps, pscale.data(), sizeof(double) * pscale.size(), cudaMemcpyHostToDevice));
     p->d_ops.push_back(dops);
     p->d_consts.push_back(dc);
+    p->d_pscale.push_back(dps);
   }
   *out_prog = p;
   return QSB_OK;
@@ -165,6 +183,7 @@ extern "C" int qsb_program_destroy(qsb_ctx* ctx, qsb_program* prog) {
       cudaSetDevice(ctx->devs[s].id);
       cudaFree(prog->d_ops[s]);
       cudaFree(prog->d_consts[s]);
+      cudaFree(prog->d_pscale[s]);
     }
   }
   delete prog;
@@ -201,9 +220,10 @@ extern "C" int qsb_batch_create(qsb_ctx* ctx, int slot, int n_programs, const qs
   if (!b) return qsb_fail(QSB_ERR_NOMEM, "out of host memory");
   b->ctx = ctx; b->slot = slot; b->n_qubits = progs[0]->n_qubits; b->n_instances = n_instances; b->n_programs = n_programs;
   b->fast_ok = true;
+  b->force_generic = ctx->force_generic;
   std::vector<QsbDevProgram> dp(n_programs);
   for (int p = 0; p < n_programs; ++p) {
-    dp[p].ops = progs[p]->d_ops[slot]; dp[p].consts = progs[p]->d_consts[slot];
+    dp[p].ops = progs[p]->d_ops[slot]; dp[p].consts = progs[p]->d_consts[slot]; dp[p].pscale = progs[p]->d_pscale[slot];
     dp[p].n_ops = progs[p]->n_ops; dp[p].n_params = progs[p]->n_params;
     b->max_ops = std::max(b->max_ops, progs[p]->n_ops);
     b->max_params = std::max(b->max_params, progs[p]->n_params);
@@ -244,6 +264,12 @@ extern "C" int qsb_batch_destroy(qsb_batch* b) {
   cudaFree(b->d_progs); cudaFree(b->d_prog_idx); cudaFree(b->d_param_off); cudaFree(b->d_params); cudaFree(b->d_target);
   cudaFree(b->out_a.p); cudaFree(b->out_b.p); cudaFree(b->out_c.p); cudaFree(b->solver_scratch);
   delete b;
+  return QSB_OK;
+}
+
+extern "C" int qsb_batch_set_kernel(qsb_batch* b, int kind) {
+  if (!b || kind < 0 || kind > 1) return qsb_fail(QSB_ERR_INVALID, "bad argument");
+  b->force_generic = (kind == QSB_KERNEL_GENERIC);
   return QSB_OK;
 }
 
@@ -349,8 +375,9 @@ int qsb_batch_enqueue(qsb_batch* b, int what, int first, int count) {
   QsbBatchArgs args;
   args.progs = b->d_progs; args.prog_idx = b->d_prog_idx; args.param_off = b->d_param_off; args.params = b->d_params;
   args.target = b->d_target; args.first = first; args.count = count; args.max_ops = b->max_ops;
+  args.max_params = std::max(1, b->max_params);
   args.out_a = (double*)b->out_a.p; args.out_b = (double*)b->out_b.p; args.out_c = (double*)b->out_c.p;
-  int rc = qsb_launch_generic(b, what, args, d.stream, d.sm_count);
+  int rc = qsb_launch(b, what, args, d.stream, d.sm_count);
   if (rc == QSB_OK) {
     std::lock_guard<std::mutex> g(b->ctx->mu);
     b->ctx->launches += 1;

@@ -22,6 +22,7 @@
 struct QsbDevProgram {
   const qsb_op* ops;
   const double* consts;
+  const double* pscale;  // [n_params]: factor applied to a parameter before its sin/cos (0.5 for half-angle gates)
   int n_ops;
   int n_params;
 };

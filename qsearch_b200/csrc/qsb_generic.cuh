@@ -28,6 +28,7 @@ struct QsbBatchArgs {
   const double* target;         // [N][N][2] (may be null for MATRIX / MATJAC)
   int first, count;
   int max_ops;
+  int max_params;
   double* out_a;
   double* out_b;
   double* out_c;
@@ -174,7 +175,7 @@ QSB_DEVICE cplx qsb_block_sum(cplx v, cplx* red) {
 // ---------------------------------------------------------------------------- kernels
 // MATRIX: out_a[li] = U.    DIST: out_a[li] = |1 - |Tr(U T^dagger)|/N|   (comparison.py:8-22)
 template <int NQ, int WHAT>
-QSB_GLOBAL qsb_k_forward(QsbBatchArgs a) {
+QSB_GLOBAL __launch_bounds__(QsbGeom<NQ>::T) qsb_k_forward(QsbBatchArgs a) {
   constexpr int N = 1 << NQ;
   QSB_DYN_SMEM(smem_raw);
   cplx* X = (cplx*)smem_raw;
@@ -259,7 +260,7 @@ QSB_DEVICE void qsb_jac_instance(cplx* X, cplx* S, cplx* Y, double* trig, const 
 }
 
 template <int NQ, int WHAT>
-QSB_GLOBAL qsb_k_jac(QsbBatchArgs a) {
+QSB_GLOBAL __launch_bounds__(QsbGeom<NQ>::T) qsb_k_jac(QsbBatchArgs a) {
   constexpr int N = 1 << NQ, NN = N * N;
   QSB_DYN_SMEM(smem_raw);
   cplx* X = (cplx*)smem_raw;
@@ -351,7 +352,7 @@ QSB_DEVICE double qsb_hs_instance(cplx* X, cplx* L, cplx* red, cplx* wpart, cplx
 }
 
 template <int NQ>
-QSB_GLOBAL qsb_k_hs(QsbBatchArgs a) {
+QSB_GLOBAL __launch_bounds__(QsbGeom<NQ>::T) qsb_k_hs(QsbBatchArgs a) {
   constexpr int N = 1 << NQ, NN = N * N;
   QSB_DYN_SMEM(smem_raw);
   cplx* X = (cplx*)smem_raw;

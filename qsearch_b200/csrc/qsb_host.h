@@ -17,6 +17,7 @@ struct QsbDevice {
 struct qsb_ctx {
   std::vector<QsbDevice> devs;
   uint64_t launches = 0;
+  bool force_generic = false;  // QSB_KERNEL=generic in the environment at qsb_init
   std::mutex mu;
 };
 
@@ -27,6 +28,7 @@ struct qsb_program {
   bool fast_ok = false;             // only U3/XZXZ/.../CONST1/CNOT ops: eligible for the register-tiled kernels
   std::vector<qsb_op*> d_ops;       // per device slot
   std::vector<double*> d_consts;
+  std::vector<double*> d_pscale;
 };
 
 struct QsbBuf {
@@ -40,6 +42,7 @@ struct qsb_batch {
   int n_qubits = 0, n_instances = 0, n_programs = 0;
   int max_ops = 0, max_params = 0;
   bool fast_ok = false;
+  bool force_generic = false;       // tests / profiling: run the shared-memory interpreter even where a warp kernel exists
   std::vector<long long> param_off;  // host copy, n_instances + 1
   std::vector<int32_t> prog_idx;
   QsbDevProgram* d_progs = nullptr;

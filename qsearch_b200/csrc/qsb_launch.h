@@ -4,6 +4,7 @@
 
 #include "qsb_host.h"
 #include "qsb_generic.cuh"
+#include "qsb_warp.cuh"
 
 struct QsbLaunchShape {
   int threads;
@@ -75,5 +76,49 @@ static inline int qsb_launch_generic(qsb_batch* b, int what, const QsbBatchArgs&
     case 4: return qsb_launch_generic_nq<4>(b, what, args, st, sm_count);
     case 5: return qsb_launch_generic_nq<5>(b, what, args, st, sm_count);
     default: return qsb_fail(QSB_ERR_UNSUPPORTED, "unsupported qubit count");
+  }
+}
+
+// ---------------------------------------------------------------------------- warp (register / DMMA) kernels
+// 4 warps per CTA, one instance tile per warp, grid = SMs x resident CTAs (persistent warps stride over the items).
+template <class K>
+static inline int qsb_resident_ctas(K kernel, int threads, size_t smem) {
+#ifdef QSB_EMU
+  (void)kernel; (void)threads; (void)smem;
+  return 2;
+#else
+  int n = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kernel, threads, smem) != cudaSuccess || n < 1) n = 1;
+  return n;
+#endif
+}
+
+template <int NQ, int WHAT>
+static int qsb_launch_warp_kernel(const QsbBatchArgs& args, cudaStream_t st, int sm_count) {
+  constexpr int threads = 128, wpb = threads / 32;
+  const size_t smem = (size_t)wpb * 2 * args.max_params * sizeof(double) + 16;
+  if (smem > 200 * 1024) return qsb_fail(QSB_ERR_UNSUPPORTED, "too many parameters for the warp kernels");
+  int rc = qsb_prepare_kernel(qsb_k_warp_jac<NQ, WHAT>, smem);
+  if (rc) return rc;
+  const long long items = (long long)args.count * QsbWarpGeom<NQ>::WARPS;
+  const long long want = (items + wpb - 1) / wpb;
+  const int resident = sm_count * qsb_resident_ctas(qsb_k_warp_jac<NQ, WHAT>, threads, smem);
+  const int grid = (int)std::max<long long>(1, std::min<long long>(want, resident));
+  QSB_LAUNCH((qsb_k_warp_jac<NQ, WHAT>), grid, threads, smem, st, args);
+  QSB_CUDA(cudaGetLastError());
+  return QSB_OK;
+}
+
+static inline bool qsb_warp_path(const qsb_batch* b, int what) {
+  return b->fast_ok && !b->force_generic && b->n_qubits >= 3 && (what == QSB_RUN_MATJAC || what == QSB_RUN_RESID);
+}
+
+static inline int qsb_launch(qsb_batch* b, int what, const QsbBatchArgs& args, cudaStream_t st, int sm_count) {
+  if (!qsb_warp_path(b, what)) return qsb_launch_generic(b, what, args, st, sm_count);
+  const bool mj = what == QSB_RUN_MATJAC;
+  switch (b->n_qubits) {
+    case 3: return mj ? qsb_launch_warp_kernel<3, QSB_RUN_MATJAC>(args, st, sm_count) : qsb_launch_warp_kernel<3, QSB_RUN_RESID>(args, st, sm_count);
+    case 4: return mj ? qsb_launch_warp_kernel<4, QSB_RUN_MATJAC>(args, st, sm_count) : qsb_launch_warp_kernel<4, QSB_RUN_RESID>(args, st, sm_count);
+    default: return mj ? qsb_launch_warp_kernel<5, QSB_RUN_MATJAC>(args, st, sm_count) : qsb_launch_warp_kernel<5, QSB_RUN_RESID>(args, st, sm_count);
   }
 }

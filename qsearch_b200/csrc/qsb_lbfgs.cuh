@@ -36,7 +36,7 @@ QSB_DEVICE double qsb_hs_value_at(cplx* X, double* trig, const QsbDevProgram& P,
 }
 
 template <int NQ>
-QSB_GLOBAL qsb_k_lbfgs(QsbSolveArgs a) {
+QSB_GLOBAL __launch_bounds__(QsbGeom<NQ>::T) qsb_k_lbfgs(QsbSolveArgs a) {
   constexpr int N = 1 << NQ, NN = N * N;
   QSB_DYN_SMEM(smem_raw);
   cplx* X = (cplx*)smem_raw;

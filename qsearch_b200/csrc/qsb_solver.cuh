@@ -152,7 +152,7 @@ QSB_DEVICE void qsb_chol_solve(const double* L, int P, double* b, double* y, dou
 }
 
 template <int NQ>
-QSB_GLOBAL qsb_k_lm(QsbSolveArgs a) {
+QSB_GLOBAL __launch_bounds__(QsbGeom<NQ>::T) qsb_k_lm(QsbSolveArgs a) {
   constexpr int N = 1 << NQ, NN = N * N, M = 2 * NN;
   QSB_DYN_SMEM(smem_raw);
   cplx* X = (cplx*)smem_raw;

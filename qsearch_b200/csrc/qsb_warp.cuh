@@ -1,0 +1,335 @@
+// Register-resident warp kernels for the standard search gatesets (one-qubit leaves + CNOT), n = 3, 4, 5 qubits.
+//
+// One WARP owns one 16x16 (n = 3: 8x8) complex tile of every output matrix of one circuit instance: the whole matrix
+// for n <= 4, one quadrant for n = 5 (four independent warps per instance, no communication between them).  The
+// running prefix X (= R_j T^dagger), the running suffix S and the accumulators live in registers in the fragment
+// layouts of the FP64 tensor-core instruction mma.sync.m8n8k4.f64 (DMMA):
+//
+//     lane = 4 g + t,  g = lane >> 2 (0..7),  t = lane & 3
+//     X[ks][nt]  = X[row 4 ks + t][col c0 + 8 nt + g]       B fragment (k x n), the warp's column block c0
+//     S[ks][mt]  = S[row r0 + 8 mt + g][col 4 ks + t]       A fragment (m x k), the warp's row block r0
+//     K[mt][nt]  = K[row r0 + 8 mt + g][col c0 + 8 nt + 2 t + {0,1}]          C fragment
+//
+// The contracted index k = 4 ks + t carries the qubit that a one-qubit gate acts on: bit (n-1-q) of k.  Bits >= 2 are
+// k-step bits (partner element in the same thread), bits 0..1 are lane bits (partner one __shfl_xor away), so every
+// structured update of X (left multiplication, rows) and of S (right multiplication, columns) is thread-local or a
+// warp shuffle: no shared memory tiles, no block barrier.  The dense products K_k = S (dg_k (x) I) X
+// (qsearch/gates.py:993-995 with the T^dagger of comparison.py:70 folded into X) run on DMMA: 4 real m8n8k4
+// products per complex tile product, Y = (dg_k (x) I) X generated per k-step on the fly.
+//
+// Algorithm = the same peel sweep as qsb_generic.cuh (restating ProductGate.mat_jac, qsearch/gates.py:965-1004).
+#pragma once
+#include "qsb_generic.cuh"
+
+#ifdef QSB_EMU
+// emulated DMMA (tests only): D[g][2t+j] += sum_k A[g][k] B[k][2t+j];  A[g][k] sits in lane 4g+k, B[k][n] in lane 4n+k
+static inline void qsb_dmma884(double& d0, double& d1, double a, double b) {
+  auto* st = qsb_emu::cur();
+  const int w = threadIdx.x / 32, l = threadIdx.x % 32, g = l >> 2, t = l & 3;
+  uint64_t ra, rb;
+  std::memcpy(&ra, &a, 8); std::memcpy(&rb, &b, 8);
+  st->warp_buf[w][l] = ra; st->warp_buf2[w][l] = rb;
+  __syncwarp();
+  for (int k = 0; k < 4; ++k) {
+    double av, b0, b1;
+    std::memcpy(&av, &st->warp_buf[w][4 * g + k], 8);
+    std::memcpy(&b0, &st->warp_buf2[w][4 * (2 * t) + k], 8);
+    std::memcpy(&b1, &st->warp_buf2[w][4 * (2 * t + 1) + k], 8);
+    d0 = std::fma(av, b0, d0); d1 = std::fma(av, b1, d1);
+  }
+  __syncwarp();
+}
+#else
+__device__ __forceinline__ void qsb_dmma884(double& d0, double& d1, double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
+               : "+d"(d0), "+d"(d1) : "d"(a), "d"(b));
+}
+#endif
+
+template <int NQ>
+struct QsbWarpGeom {
+  static constexpr int N = 1 << NQ;
+  static constexpr int NN = N * N;
+  static constexpr int KS = N / 4;                 // k-steps of the m8n8k4 instruction
+  static constexpr int TT = (NQ >= 4) ? 2 : 1;     // 8-wide tiles per warp along rows and along columns
+  static constexpr int WR = N / (8 * TT);          // warps along one side of the matrix
+  static constexpr int WARPS = WR * WR;            // warps per instance
+};
+
+template <int KS, int TT>
+struct QsbFrag {
+  double re[KS][TT], im[KS][TT];
+};
+
+#define QSB_FULL 0xffffffffu
+
+// dst[k] = m[b][0] src[k with bit = 0] + m[b][1] src[k with bit = 1], b = that bit of k; the bit belongs to qubit q.
+// m = {m00, m01, m10, m11}.  In-thread variant: partner k-step = ks ^ KB.
+template <int KS, int TT, int KB>
+QSB_DEVICE void qsb_mix_thread(QsbFrag<KS, TT>& F, const cplx* m) {
+#pragma unroll
+  for (int ks = 0; ks < KS; ++ks) {
+    if (ks & KB) continue;
+#pragma unroll
+    for (int o = 0; o < TT; ++o) {
+      const double ar = F.re[ks][o], ai = F.im[ks][o], br = F.re[ks | KB][o], bi = F.im[ks | KB][o];
+      F.re[ks][o] = fma(m[1].x, br, fma(-m[1].y, bi, fma(m[0].x, ar, -m[0].y * ai)));
+      F.im[ks][o] = fma(m[1].x, bi, fma(m[1].y, br, fma(m[0].x, ai, m[0].y * ar)));
+      F.re[ks | KB][o] = fma(m[3].x, br, fma(-m[3].y, bi, fma(m[2].x, ar, -m[2].y * ai)));
+      F.im[ks | KB][o] = fma(m[3].x, bi, fma(m[3].y, br, fma(m[2].x, ai, m[2].y * ar)));
+    }
+  }
+}
+
+template <int KS, int TT>
+QSB_DEVICE void qsb_mix_lane(QsbFrag<KS, TT>& F, const cplx* m, int lbit, int lane) {
+  const bool hi = (lane >> lbit) & 1;
+  const cplx ca = hi ? m[3] : m[0], cb = hi ? m[2] : m[1];
+  const int mask = 1 << lbit;
+#pragma unroll
+  for (int ks = 0; ks < KS; ++ks)
+#pragma unroll
+    for (int o = 0; o < TT; ++o) {
+      const double ar = F.re[ks][o], ai = F.im[ks][o];
+      const double pr = __shfl_xor_sync(QSB_FULL, ar, mask), pi = __shfl_xor_sync(QSB_FULL, ai, mask);
+      F.re[ks][o] = fma(cb.x, pr, fma(-cb.y, pi, fma(ca.x, ar, -ca.y * ai)));
+      F.im[ks][o] = fma(cb.x, pi, fma(cb.y, pr, fma(ca.x, ai, ca.y * ar)));
+    }
+}
+
+template <int NQ, int TT>
+QSB_DEVICE void qsb_mix(QsbFrag<(1 << NQ) / 4, TT>& F, int q, const cplx* m, int lane) {
+  constexpr int KS = (1 << NQ) / 4;
+  const int bit = NQ - 1 - q;
+  switch (bit) {
+    case 0: case 1: qsb_mix_lane<KS, TT>(F, m, bit, lane); break;
+    case 2: qsb_mix_thread<KS, TT, 1>(F, m); break;
+    case 3: if (NQ >= 4) qsb_mix_thread<KS, TT, (NQ >= 4 ? 2 : 1)>(F, m); break;
+    default: if (NQ >= 5) qsb_mix_thread<KS, TT, (NQ >= 5 ? 4 : 1)>(F, m); break;
+  }
+}
+
+// CNOT(control c, target tq) as a permutation of the k index: F'[k] = F[k ^ tbit] where the control bit of k is set.
+template <int KS, int TT, int KB>
+QSB_DEVICE void qsb_cnot_thread(QsbFrag<KS, TT>& F, int cbit, int lane) {
+#pragma unroll
+  for (int ks = 0; ks < KS; ++ks) {
+    if (ks & KB) continue;
+    const bool ctrl = (((4 * ks) | (lane & 3)) >> cbit) & 1;
+#pragma unroll
+    for (int o = 0; o < TT; ++o) {
+      const double ar = F.re[ks][o], ai = F.im[ks][o], br = F.re[ks | KB][o], bi = F.im[ks | KB][o];
+      F.re[ks][o] = ctrl ? br : ar; F.im[ks][o] = ctrl ? bi : ai;
+      F.re[ks | KB][o] = ctrl ? ar : br; F.im[ks | KB][o] = ctrl ? ai : bi;
+    }
+  }
+}
+
+template <int KS, int TT>
+QSB_DEVICE void qsb_cnot_lane(QsbFrag<KS, TT>& F, int cbit, int tbit, int lane) {
+  const int mask = 1 << tbit;
+#pragma unroll
+  for (int ks = 0; ks < KS; ++ks) {
+    const bool ctrl = (((4 * ks) | (lane & 3)) >> cbit) & 1;
+#pragma unroll
+    for (int o = 0; o < TT; ++o) {
+      const double pr = __shfl_xor_sync(QSB_FULL, F.re[ks][o], mask), pi = __shfl_xor_sync(QSB_FULL, F.im[ks][o], mask);
+      if (ctrl) { F.re[ks][o] = pr; F.im[ks][o] = pi; }
+    }
+  }
+}
+
+template <int NQ, int TT>
+QSB_DEVICE void qsb_cnot(QsbFrag<(1 << NQ) / 4, TT>& F, int c, int tq, int lane) {
+  constexpr int KS = (1 << NQ) / 4;
+  const int cbit = NQ - 1 - c, tbit = NQ - 1 - tq;
+  switch (tbit) {
+    case 0: case 1: qsb_cnot_lane<KS, TT>(F, cbit, tbit, lane); break;
+    case 2: qsb_cnot_thread<KS, TT, 1>(F, cbit, lane); break;
+    case 3: if (NQ >= 4) qsb_cnot_thread<KS, TT, (NQ >= 4 ? 2 : 1)>(F, cbit, lane); break;
+    default: if (NQ >= 5) qsb_cnot_thread<KS, TT, (NQ >= 5 ? 4 : 1)>(F, cbit, lane); break;
+  }
+}
+
+// K = S (m (x) I) X on the tensor cores.  KB > 0: the qubit of m is k-step bit KB; KB == 0: lane bit lbit.
+template <int KS, int TT, int KB>
+QSB_DEVICE void qsb_dmma_product(double (&cr)[TT][TT][2], double (&ci)[TT][TT][2], const QsbFrag<KS, TT>& S,
+                                 const QsbFrag<KS, TT>& X, const cplx* m, int lbit, int lane) {
+#pragma unroll
+  for (int a = 0; a < TT; ++a)
+#pragma unroll
+    for (int b = 0; b < TT; ++b) { cr[a][b][0] = cr[a][b][1] = ci[a][b][0] = ci[a][b][1] = 0.0; }
+  const bool hi = (lane >> lbit) & 1;
+  const int mask = 1 << lbit;
+#pragma unroll
+  for (int ks = 0; ks < KS; ++ks) {
+    double yr[TT], yi[TT], ny[TT];
+#pragma unroll
+    for (int nt = 0; nt < TT; ++nt) {
+      cplx ca, cb;
+      double pr, pi;
+      const double xr = X.re[ks][nt], xi = X.im[ks][nt];
+      if (KB > 0) {
+        const bool up = (ks & KB) != 0;
+        ca = up ? m[3] : m[0]; cb = up ? m[2] : m[1];
+        pr = X.re[ks ^ KB][nt]; pi = X.im[ks ^ KB][nt];
+      } else {
+        ca = hi ? m[3] : m[0]; cb = hi ? m[2] : m[1];
+        pr = __shfl_xor_sync(QSB_FULL, xr, mask); pi = __shfl_xor_sync(QSB_FULL, xi, mask);
+      }
+      yr[nt] = fma(cb.x, pr, fma(-cb.y, pi, fma(ca.x, xr, -ca.y * xi)));
+      yi[nt] = fma(cb.x, pi, fma(cb.y, pr, fma(ca.x, xi, ca.y * xr)));
+      ny[nt] = -yi[nt];
+    }
+#pragma unroll
+    for (int nt = 0; nt < TT; ++nt)
+#pragma unroll
+      for (int mt = 0; mt < TT; ++mt) {
+        qsb_dmma884(cr[mt][nt][0], cr[mt][nt][1], S.re[ks][mt], yr[nt]);
+        qsb_dmma884(ci[mt][nt][0], ci[mt][nt][1], S.re[ks][mt], yi[nt]);
+        qsb_dmma884(cr[mt][nt][0], cr[mt][nt][1], S.im[ks][mt], ny[nt]);
+        qsb_dmma884(ci[mt][nt][0], ci[mt][nt][1], S.im[ks][mt], yr[nt]);
+      }
+  }
+}
+
+template <int NQ, int TT>
+QSB_DEVICE void qsb_product(double (&cr)[TT][TT][2], double (&ci)[TT][TT][2], const QsbFrag<(1 << NQ) / 4, TT>& S,
+                            const QsbFrag<(1 << NQ) / 4, TT>& X, int q, const cplx* m, int lane) {
+  constexpr int KS = (1 << NQ) / 4;
+  const int bit = NQ - 1 - q;
+  switch (bit) {
+    case 0: case 1: qsb_dmma_product<KS, TT, 0>(cr, ci, S, X, m, bit, lane); break;
+    case 2: qsb_dmma_product<KS, TT, 1>(cr, ci, S, X, m, 0, lane); break;
+    case 3: if (NQ >= 4) qsb_dmma_product<KS, TT, (NQ >= 4 ? 2 : 1)>(cr, ci, S, X, m, 0, lane); break;
+    default: if (NQ >= 5) qsb_dmma_product<KS, TT, (NQ >= 5 ? 4 : 1)>(cr, ci, S, X, m, 0, lane); break;
+  }
+}
+
+QSB_DEVICE void qsb_dagger2x2(cplx* g) {
+  const cplx t = g[1];
+  g[0] = cconj(g[0]); g[1] = cconj(g[2]); g[2] = cconj(t); g[3] = cconj(g[3]);
+}
+QSB_DEVICE void qsb_transpose2x2(cplx* g) { const cplx t = g[1]; g[1] = g[2]; g[2] = t; }
+
+// the 2x2 of a one-qubit op; trig holds (cos, sin) of the scaled angle of every parameter, in parameter order
+QSB_DEVICE void qsb_warp_gate(const qsb_op& op, const double* trig, const double* consts, cplx* g) {
+  if (op.opcode == QSB_OP_CONST1) {
+    const double* c = consts + op.const_off;
+    g[0] = cmk(c[0], c[1]); g[1] = cmk(c[2], c[3]); g[2] = cmk(c[4], c[5]); g[3] = cmk(c[6], c[7]);
+  } else {
+    qsb_gate2x2(op.opcode, trig + 2 * op.param_off, 0, g);
+  }
+}
+
+// One warp, one tile of one instance.  WHAT = QSB_RUN_MATJAC: out_u = U, out_j[k] = J_k, interleaved complex;
+// WHAT = QSB_RUN_RESID: out_u = r, out_j[k] = [Re K_k ; Im K_k] (see qsb_jac_instance in qsb_generic.cuh).
+// trig: 2 * n_params doubles of this warp's shared memory.  tile = warp-row * WR + warp-col of this warp's block.
+template <int NQ, int WHAT>
+QSB_DEVICE void qsb_warp_jac(const QsbDevProgram& P, const double* x, const double* target, double* trig, int tile,
+                             int lane, double* out_u, double* out_j) {
+  using G = QsbWarpGeom<NQ>;
+  constexpr int N = G::N, NN = G::NN, KS = G::KS, TT = G::TT;
+  const int g = lane >> 2, t = lane & 3;
+  const int r0 = (tile / G::WR) * 8 * TT, c0 = (tile % G::WR) * 8 * TT;
+  __syncwarp();
+  for (int p = lane; p < P.n_params; p += 32) {
+    double s, c;
+    sincos(P.pscale[p] * x[p], &s, &c);
+    trig[2 * p] = c; trig[2 * p + 1] = s;
+  }
+  __syncwarp();
+  QsbFrag<KS, TT> X, S;
+#pragma unroll
+  for (int ks = 0; ks < KS; ++ks)
+#pragma unroll
+    for (int o = 0; o < TT; ++o) {
+      const int k = 4 * ks + t, c = c0 + 8 * o + g, r = r0 + 8 * o + g;
+      if (WHAT == QSB_RUN_RESID) {  // X = T^dagger
+        const double2 tv = *reinterpret_cast<const double2*>(target + 2 * (c * N + k));
+        X.re[ks][o] = tv.x; X.im[ks][o] = -tv.y;
+      } else {
+        X.re[ks][o] = (k == c) ? 1.0 : 0.0; X.im[ks][o] = 0.0;
+      }
+      S.re[ks][o] = (k == r) ? 1.0 : 0.0; S.im[ks][o] = 0.0;
+    }
+  // forward sweep: X <- g_j X
+  for (int j = 0; j < P.n_ops; ++j) {
+    const qsb_op op = P.ops[j];
+    if (op.opcode == QSB_OP_CNOT) { qsb_cnot<NQ, TT>(X, op.q0, op.q1, lane); continue; }
+    cplx m[4];
+    qsb_warp_gate(op, trig, P.consts, m);
+    qsb_mix<NQ, TT>(X, op.q0, m, lane);
+  }
+  if (r0 == 0) {  // the warps of the first block row write U T^dagger (their column block of it)
+#pragma unroll
+    for (int ks = 0; ks < KS; ++ks)
+#pragma unroll
+      for (int o = 0; o < TT; ++o) {
+        const int k = 4 * ks + t, c = c0 + 8 * o + g, e = k * N + c;
+        if (WHAT == QSB_RUN_MATJAC) *reinterpret_cast<double2*>(out_u + 2 * e) = make_double2(X.re[ks][o], X.im[ks][o]);
+        else { out_u[e] = X.re[ks][o] - (k == c ? 1.0 : 0.0); out_u[NN + e] = X.im[ks][o]; }
+      }
+  }
+  // backward sweep
+  for (int j = P.n_ops - 1; j >= 0; --j) {
+    const qsb_op op = P.ops[j];
+    if (op.opcode == QSB_OP_CNOT) {
+      if (j == 0) break;
+      qsb_cnot<NQ, TT>(X, op.q0, op.q1, lane);
+      qsb_cnot<NQ, TT>(S, op.q0, op.q1, lane);
+      continue;
+    }
+    const int np = qsb_num_params(op.opcode);
+    if (np == 0 && j == 0) break;
+    cplx m[4];
+    qsb_warp_gate(op, trig, P.consts, m);
+    {
+      cplx md[4] = {m[0], m[1], m[2], m[3]};
+      qsb_dagger2x2(md);
+      qsb_mix<NQ, TT>(X, op.q0, md, lane);  // X = R_j T^dagger
+    }
+    for (int k = 0; k < np; ++k) {
+      cplx dg[4];
+      qsb_gate2x2(op.opcode, trig + 2 * op.param_off, 1 + k, dg);
+      double cr[TT][TT][2], ci[TT][TT][2];
+      qsb_product<NQ, TT>(cr, ci, S, X, op.q0, dg, lane);
+      double* o = out_j + (size_t)(op.param_off + k) * 2 * NN;
+#pragma unroll
+      for (int mt = 0; mt < TT; ++mt)
+#pragma unroll
+        for (int nt = 0; nt < TT; ++nt) {
+          const int e = (r0 + 8 * mt + g) * N + c0 + 8 * nt + 2 * t;
+          if (WHAT == QSB_RUN_MATJAC) {
+            *reinterpret_cast<double2*>(o + 2 * e) = make_double2(cr[mt][nt][0], ci[mt][nt][0]);
+            *reinterpret_cast<double2*>(o + 2 * e + 2) = make_double2(cr[mt][nt][1], ci[mt][nt][1]);
+          } else {
+            *reinterpret_cast<double2*>(o + e) = make_double2(cr[mt][nt][0], cr[mt][nt][1]);
+            *reinterpret_cast<double2*>(o + NN + e) = make_double2(ci[mt][nt][0], ci[mt][nt][1]);
+          }
+        }
+    }
+    if (j > 0) {
+      qsb_transpose2x2(m);
+      qsb_mix<NQ, TT>(S, op.q0, m, lane);  // S <- S g_j
+    }
+  }
+}
+
+template <int NQ, int WHAT>
+QSB_GLOBAL __launch_bounds__(128) qsb_k_warp_jac(QsbBatchArgs a) {
+  using G = QsbWarpGeom<NQ>;
+  constexpr int NN = G::NN;
+  QSB_DYN_SMEM(smem_raw);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpb = blockDim.x >> 5;
+  double* trig = (double*)smem_raw + (size_t)warp * 2 * a.max_params;
+  const long long p_base = a.param_off[a.first];
+  const long long items = (long long)a.count * G::WARPS;
+  for (long long it = (long long)blockIdx.x * wpb + warp; it < items; it += (long long)gridDim.x * wpb) {
+    const int li = (int)(it / G::WARPS), tile = (int)(it % G::WARPS);
+    const int inst = a.first + li;
+    const QsbDevProgram P = a.progs[a.prog_idx[inst]];
+    qsb_warp_jac<NQ, WHAT>(P, a.params + a.param_off[inst], a.target, trig, tile, lane,
+                           a.out_a + (size_t)li * 2 * NN, a.out_b + (size_t)(a.param_off[inst] - p_base) * 2 * NN);
+  }
+}

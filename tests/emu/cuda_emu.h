@@ -47,7 +47,7 @@ struct BlockState {
   unsigned long block_gen = 0;
   std::vector<unsigned> warp_arrived, warp_alive;
   std::vector<unsigned long> warp_gen;
-  std::vector<std::vector<uint64_t>> warp_buf;  // [warp][32]
+  std::vector<std::vector<uint64_t>> warp_buf, warp_buf2;  // [warp][32]
   unsigned char* smem = nullptr;
   const std::function<void()>* body = nullptr;
 };
@@ -233,6 +233,7 @@ inline void launch(unsigned grid, unsigned block, size_t smem_bytes, const std::
     st.grid = grid;
     st.fibers.resize(block);
     st.warp_buf.assign((block + 31) / 32, std::vector<uint64_t>(32, 0));
+    st.warp_buf2 = st.warp_buf;
     std::vector<unsigned char> sm(smem_bytes + 64);
     st.smem = (unsigned char*)(((uintptr_t)sm.data() + 63) & ~(uintptr_t)63);
     st.body = &body;
