@@ -79,6 +79,7 @@ class Library:
         d.qsb_batch_create.argtypes = [_vp, ctypes.c_int, ctypes.c_int, pp, ctypes.c_int, _c_ip, pp]
         d.qsb_batch_destroy.argtypes = [_vp]
         d.qsb_batch_set_params.argtypes = [_vp, _c_dp, ctypes.c_size_t]
+        d.qsb_batch_set_kernel.argtypes = [_vp, ctypes.c_int]
         d.qsb_batch_set_target.argtypes = [_vp, _c_dp]
         d.qsb_batch_run.argtypes = [_vp, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_float)]
         d.qsb_batch_sync.argtypes = [_vp]
@@ -234,6 +235,10 @@ class Batch:
         self.h = _vp()
         lib.check(lib.dll.qsb_batch_create(lib.ctx, slot, len(self.gps), handles, len(self.poi),
                                            self.poi.ctypes.data_as(_c_ip), ctypes.byref(self.h)))
+
+    def set_kernel(self, kind):
+        """0 = automatic (DMMA warp kernels where they apply), 1 = shared-memory interpreter."""
+        self.lib.check(self.lib.dll.qsb_batch_set_kernel(self.h, int(kind)))
 
     def set_params(self, params):
         params = _f64(params).ravel()

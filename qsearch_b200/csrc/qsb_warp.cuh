@@ -222,16 +222,8 @@ QSB_DEVICE void qsb_warp_gate(const qsb_op& op, const double* trig, const double
   }
 }
 
-// One warp, one tile of one instance.  WHAT = QSB_RUN_MATJAC: out_u = U, out_j[k] = J_k, interleaved complex;
-// WHAT = QSB_RUN_RESID: out_u = r, out_j[k] = [Re K_k ; Im K_k] (see qsb_jac_instance in qsb_generic.cuh).
-// trig: 2 * n_params doubles of this warp's shared memory.  tile = warp-row * WR + warp-col of this warp's block.
-template <int NQ, int WHAT>
-QSB_DEVICE void qsb_warp_jac(const QsbDevProgram& P, const double* x, const double* target, double* trig, int tile,
-                             int lane, double* out_u, double* out_j) {
-  using G = QsbWarpGeom<NQ>;
-  constexpr int N = G::N, NN = G::NN, KS = G::KS, TT = G::TT;
-  const int g = lane >> 2, t = lane & 3;
-  const int r0 = (tile / G::WR) * 8 * TT, c0 = (tile % G::WR) * 8 * TT;
+// (cos, sin) of the scaled angle of every parameter, in parameter order (one parameter per lane and round)
+QSB_DEVICE void qsb_warp_trig(const QsbDevProgram& P, const double* x, double* trig, int lane) {
   __syncwarp();
   for (int p = lane; p < P.n_params; p += 32) {
     double s, c;
@@ -239,6 +231,21 @@ QSB_DEVICE void qsb_warp_jac(const QsbDevProgram& P, const double* x, const doub
     trig[2 * p] = c; trig[2 * p + 1] = s;
   }
   __syncwarp();
+}
+
+// One warp, one tile of one instance, ops [jb, je) of the program (the whole program: jb = 0, je = n_ops).
+// WHAT = QSB_RUN_MATJAC: out_u = U, out_j[k] = J_k, interleaved complex;
+// WHAT = QSB_RUN_RESID: out_u = r, out_j[k] = [Re K_k ; Im K_k] (see qsb_jac_instance in qsb_generic.cuh).
+// trig: (cos, sin) per parameter.  tile = warp-row * WR + warp-col of this warp's block.  A segment [jb, je) first
+// builds its own prefix X = g_{je-1} .. g_0 T^dagger and suffix S = g_{M-1} .. g_{je} with structured updates only,
+// so several warps can share the parameters of one instance without exchanging data (used by the LM solver).
+template <int NQ, int WHAT>
+QSB_DEVICE void qsb_warp_jac_range(const QsbDevProgram& P, const double* target, const double* trig, int tile, int lane,
+                                   int jb, int je, double* out_u, double* out_j) {
+  using G = QsbWarpGeom<NQ>;
+  constexpr int N = G::N, NN = G::NN, KS = G::KS, TT = G::TT;
+  const int g = lane >> 2, t = lane & 3;
+  const int r0 = (tile / G::WR) * 8 * TT, c0 = (tile % G::WR) * 8 * TT;
   QsbFrag<KS, TT> X, S;
 #pragma unroll
   for (int ks = 0; ks < KS; ++ks)
@@ -253,15 +260,24 @@ QSB_DEVICE void qsb_warp_jac(const QsbDevProgram& P, const double* x, const doub
       }
       S.re[ks][o] = (k == r) ? 1.0 : 0.0; S.im[ks][o] = 0.0;
     }
-  // forward sweep: X <- g_j X
-  for (int j = 0; j < P.n_ops; ++j) {
+  // forward sweep: X <- g_j X for the ops below je
+  for (int j = 0; j < je; ++j) {
     const qsb_op op = P.ops[j];
     if (op.opcode == QSB_OP_CNOT) { qsb_cnot<NQ, TT>(X, op.q0, op.q1, lane); continue; }
     cplx m[4];
     qsb_warp_gate(op, trig, P.consts, m);
     qsb_mix<NQ, TT>(X, op.q0, m, lane);
   }
-  if (r0 == 0) {  // the warps of the first block row write U T^dagger (their column block of it)
+  // suffix of a segment that does not end at the last op: S <- S g_j for j = M-1 .. je
+  for (int j = P.n_ops - 1; j >= je; --j) {
+    const qsb_op op = P.ops[j];
+    if (op.opcode == QSB_OP_CNOT) { qsb_cnot<NQ, TT>(S, op.q0, op.q1, lane); continue; }
+    cplx m[4];
+    qsb_warp_gate(op, trig, P.consts, m);
+    qsb_transpose2x2(m);
+    qsb_mix<NQ, TT>(S, op.q0, m, lane);
+  }
+  if (r0 == 0 && je == P.n_ops) {  // the warps of the first block row write U T^dagger (their column block of it)
 #pragma unroll
     for (int ks = 0; ks < KS; ++ks)
 #pragma unroll
@@ -271,17 +287,17 @@ QSB_DEVICE void qsb_warp_jac(const QsbDevProgram& P, const double* x, const doub
         else { out_u[e] = X.re[ks][o] - (k == c ? 1.0 : 0.0); out_u[NN + e] = X.im[ks][o]; }
       }
   }
-  // backward sweep
-  for (int j = P.n_ops - 1; j >= 0; --j) {
+  // backward sweep over the segment
+  for (int j = je - 1; j >= jb; --j) {
     const qsb_op op = P.ops[j];
     if (op.opcode == QSB_OP_CNOT) {
-      if (j == 0) break;
+      if (j == jb) break;
       qsb_cnot<NQ, TT>(X, op.q0, op.q1, lane);
       qsb_cnot<NQ, TT>(S, op.q0, op.q1, lane);
       continue;
     }
     const int np = qsb_num_params(op.opcode);
-    if (np == 0 && j == 0) break;
+    if (np == 0 && j == jb) break;
     cplx m[4];
     qsb_warp_gate(op, trig, P.consts, m);
     {
@@ -309,11 +325,18 @@ QSB_DEVICE void qsb_warp_jac(const QsbDevProgram& P, const double* x, const doub
           }
         }
     }
-    if (j > 0) {
+    if (j > jb) {
       qsb_transpose2x2(m);
       qsb_mix<NQ, TT>(S, op.q0, m, lane);  // S <- S g_j
     }
   }
+}
+
+template <int NQ, int WHAT>
+QSB_DEVICE void qsb_warp_jac(const QsbDevProgram& P, const double* x, const double* target, double* trig, int tile,
+                             int lane, double* out_u, double* out_j) {
+  qsb_warp_trig(P, x, trig, lane);
+  qsb_warp_jac_range<NQ, WHAT>(P, target, trig, tile, lane, 0, P.n_ops, out_u, out_j);
 }
 
 template <int NQ, int WHAT>

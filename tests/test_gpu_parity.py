@@ -152,3 +152,45 @@ def test_device_resident_batch_matches_host_calls(lib):
     f2, g2 = lib.eval_hs_grad(gps, poi, flat, T)
     assert np.array_equal(f, f2) and np.array_equal(g, g2)
     b.close()
+
+
+@pytest.mark.parametrize("n", [3, 4, 5])
+def test_warp_kernels_match_interpreter(lib, n):
+    """The register/DMMA warp kernels against the shared-memory interpreter on the same device-resident batch."""
+    circuits, params, targets = workloads.microbench_workload(n, 6, 5)
+    gps = [lowering.lower(c) for c in circuits]
+    poi = np.repeat(np.arange(6, dtype="int32"), 5)
+    out = {}
+    for kind in (0, 1):
+        b = lib.batch(gps, poi)
+        b.set_kernel(kind)
+        b.set_params(params.reshape(len(poi), -1))
+        b.set_target(targets["haar"] if "haar" in targets else targets["qft"])
+        res = []
+        for what in (_lib.RUN_MATJAC, _lib.RUN_RESID):
+            b.run(what)
+            res.extend(x for x in b.fetch() if x is not None)
+        out[kind] = res
+        b.close()
+    for a, g in zip(out[0], out[1]):
+        assert a.shape == g.shape and np.abs(a - g).max() < 1e-13
+
+
+def test_tensor_core_lm_matches_interpreter_lm(lib, monkeypatch):
+    """Same LM trajectory from both kernel families: identical iteration counts, same end point."""
+    rng = np.random.default_rng(12)
+    g = gatesets.QubitCNOTRing()
+    c = gates.ProductGate(g.initial_layer(4))
+    layers = g.search_layers(4)
+    for _ in range(5):
+        c = c.appending(layers[int(rng.integers(len(layers)))][0])
+    T = O.matrix(c, rng.random(c.num_inputs) * 2 * np.pi)
+    gp = lowering.lower(c)
+    x0 = rng.random((8, gp.n_params)) * 2 * np.pi
+    poi = np.zeros(8, dtype="int32")
+    x1, f1, it1, st1 = lib.solve("lm", [gp], poi, x0, T)
+    monkeypatch.setenv("QSB_KERNEL", "generic")
+    lib2 = _lib.Library(devices=[0])
+    x2, f2, it2, st2 = lib2.solve("lm", [gp], poi, x0, T)
+    assert f1.min() < 1e-10 and f2.min() < 1e-10
+    assert np.abs(f1 - f2).max() < 1e-9
