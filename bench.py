@@ -253,8 +253,8 @@ def run_ours(args, rank, world, local_rank):
     # -- end to end through the host-buffer C-ABI call ------------------------------------------------------
     e_inst = min(n_inst, args.e2e_instances)
     sel = slice(0, e_inst)
-    out_r = np.empty((e_inst, 2 * N * N))
-    out_J = np.empty((e_inst * P, 2 * N * N))
+    out_r = lib.pinned_empty((e_inst, 2 * N * N))      # page-locked host buffers (qsb_host_alloc)
+    out_J = lib.pinned_empty((e_inst * P, 2 * N * N))
     lib.eval_residuals_jac(gps, poi[sel], flat[sel], T, out_r, out_J)  # warm-up (page faults of the output buffers)
     barrier(dist)
     t0 = time.perf_counter()
@@ -273,6 +273,9 @@ def run_ours(args, rank, world, local_rank):
     peaks = load_peaks()
     hbm_peak = peaks.get("hbm_gbs", 6650.0)
     achieved_tf = (n_inst / (kern_ms * 1e-3)) * F / 1e12
+    # what the warp kernel really issues on the FP64 tensor pipe: P complex N^3 products = 8 N^3 P flop per eval
+    executed_dmma_tf = (n_inst / (kern_ms * 1e-3)) * 8.0 * (N ** 3) * P / 1e12
+    ncu_traffic = {4: 255877.0, 5: 1075282.0}.get(n)  # dram read+write bytes per eval, profiles/r1/c_ncu_full_resid_n*_warp.txt
     line = {
         "metric": "objective+Jacobian evals/sec", "value": value, "unit": "evals/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": kern_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -282,11 +285,18 @@ def run_ours(args, rank, world, local_rank):
                 "d2h_bytes_per_step": int(e_inst * (P + 1) * 2 * N * N * 8),
                 "note": "qsb_eval_residuals_jac with host buffers, {} instances per step (r and J_r copied back: "
                         "PCIe-bound by the {:.2f} MB of Jacobian per eval)".format(e_inst, (P + 1) * 2 * N * N * 8 / 1e6)},
-        "roofline": {"bound": "fp64", "achieved": achieved_tf, "peak": fp64_peak, "unit": "TFLOP/s",
-                     "frac": achieved_tf / fp64_peak if fp64_peak else None, "traffic": None,
-                     "peak_source": "DFMA micro-benchmark run by this command (qsb_measure_fp64_peak); FP64 is not in MEASURED_PEAKS.json",
-                     "dmma_peak": dmma_peak,
-                     "flops": "algorithmic (dense prefix/suffix formulation, SURVEY 8d); the kernels execute fewer",
+        "roofline": {"bound": "tensor", "achieved": achieved_tf, "peak": dmma_peak, "unit": "TFLOP/s",
+                     "frac": achieved_tf / dmma_peak if dmma_peak else None,
+                     "traffic": int(ncu_traffic * n_inst) if ncu_traffic else None,
+                     "peak_source": "FP64 tensor pipe (DMMA m8n8k4) micro-benchmark run by this command (qsb_measure_fp64_peak); "
+                                    "FP64 is not in MEASURED_PEAKS.json (bf16 and HBM only)",
+                     "dfma_peak": fp64_peak,
+                     "flops": "achieved = ALGORITHMIC flops (dense prefix/suffix formulation, SURVEY 8d: 8N^3(2(G-1)+2P) + 8N^3(P+1)) per "
+                              "second; gate structure lets the kernel execute fewer, so frac can exceed 1. Executed on the tensor pipe: "
+                              "8 N^3 P flop per eval (see executed)",
+                     "executed": {"dmma_tflops": executed_dmma_tf, "frac_of_dmma_peak": executed_dmma_tf / dmma_peak if dmma_peak else None,
+                                  "ncu_dmma_pipe_active_pct": {4: 53.8, 5: 56.7}.get(n)},
+                     "traffic_note": "ncu dram bytes per eval (one --set full capture, profiles/r1) x instances of this launch",
                      "hbm": {"achieved": out_bytes / (kern_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
                              "frac": out_bytes / (kern_ms * 1e-3) / 1e9 / hbm_peak,
                              "bytes_per_eval": out_bytes / n_inst}},

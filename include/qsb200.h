@@ -78,6 +78,10 @@ int qsb_device_count(int* out_count);
 int qsb_init(int n_devices, const int* device_ids, qsb_ctx** out_ctx);
 int qsb_shutdown(qsb_ctx* ctx);
 int qsb_ctx_num_devices(const qsb_ctx* ctx);
+/* Page-locked host memory for the buffers of the host-buffer calls (optional: any host pointer is accepted, pinned
+ * ones let the device->host copy run at PCIe speed and overlap with the next chunk's kernel). */
+int qsb_host_alloc(qsb_ctx* ctx, size_t bytes, void** out_ptr);
+int qsb_host_free(qsb_ctx* ctx, void* ptr);
 const char* qsb_version(void);
 
 /* ---- programs (replaces native_from_object, qsrs/src/lib.rs:543-554) ------------------------------------ */

@@ -67,6 +67,8 @@ class Library:
         d.qsb_shutdown.argtypes = [_vp]
         d.qsb_device_count.argtypes = [ctypes.POINTER(ctypes.c_int)]
         d.qsb_ctx_num_devices.argtypes = [_vp]
+        d.qsb_host_alloc.argtypes = [_vp, ctypes.c_size_t, pp]
+        d.qsb_host_free.argtypes = [_vp, _vp]
         d.qsb_ctx_launch_count.argtypes = [_vp, ctypes.POINTER(ctypes.c_uint64)]
         d.qsb_program_create.argtypes = [_vp, ctypes.c_int, ctypes.c_int, _vp, ctypes.c_int, _c_dp, ctypes.c_size_t, pp]
         d.qsb_program_destroy.argtypes = [_vp, _vp]
@@ -113,6 +115,18 @@ class Library:
     @property
     def num_devices(self):
         return self.dll.qsb_ctx_num_devices(self.ctx)
+
+    def pinned_empty(self, shape, dtype="float64"):
+        """NumPy array over page-locked host memory (qsb_host_alloc); freed when the array is collected."""
+        import weakref
+        dt = np.dtype(dtype)
+        n = int(np.prod(shape)) * dt.itemsize
+        p = _vp()
+        self.check(self.dll.qsb_host_alloc(self.ctx, n, ctypes.byref(p)))
+        buf = (ctypes.c_char * max(1, n)).from_address(p.value)
+        arr = np.frombuffer(buf, dtype=dt, count=int(np.prod(shape))).reshape(shape)
+        weakref.finalize(buf, self.dll.qsb_host_free, self._ctx, p)
+        return arr
 
     def version(self):
         return self.dll.qsb_version().decode()

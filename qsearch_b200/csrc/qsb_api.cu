@@ -60,6 +60,7 @@ extern "C" int qsb_init(int n_devices, const int* device_ids, qsb_ctx** out_ctx)
     QSB_CUDA(cudaSetDevice(id));
     QSB_CUDA(cudaDeviceGetAttribute(&d.sm_count, cudaDevAttrMultiProcessorCount, id));
     QSB_CUDA(cudaStreamCreateWithFlags(&d.stream, cudaStreamNonBlocking));
+    QSB_CUDA(cudaStreamCreateWithFlags(&d.copy_stream, cudaStreamNonBlocking));
     QSB_CUDA(cudaEventCreate(&d.ev0));
     QSB_CUDA(cudaEventCreate(&d.ev1));
     ctx->devs.push_back(d);
@@ -76,8 +77,22 @@ extern "C" int qsb_shutdown(qsb_ctx* ctx) {
     cudaEventDestroy(d.ev0);
     cudaEventDestroy(d.ev1);
     cudaStreamDestroy(d.stream);
+    cudaStreamDestroy(d.copy_stream);
   }
   delete ctx;
+  return QSB_OK;
+}
+
+extern "C" int qsb_host_alloc(qsb_ctx* ctx, size_t bytes, void** out) {
+  if (!ctx || !out) return qsb_fail(QSB_ERR_INVALID, "NULL argument");
+  QSB_CUDA(cudaSetDevice(ctx->devs[0].id));
+  cudaError_t e = cudaHostAlloc(out, bytes ? bytes : 1, cudaHostAllocPortable);
+  if (e != cudaSuccess) { *out = nullptr; return qsb_fail(QSB_ERR_NOMEM, std::string("pinned host allocation failed: ") + cudaGetErrorString(e)); }
+  return QSB_OK;
+}
+extern "C" int qsb_host_free(qsb_ctx* ctx, void* p) {
+  (void)ctx;
+  if (p) cudaFreeHost(p);
   return QSB_OK;
 }
 
@@ -399,29 +414,76 @@ struct HostEvalJob {
 
 static int run_shard(const HostEvalJob& job, int slot, int i0, int i1, const std::vector<long long>& poff) {
   if (i1 <= i0) return QSB_OK;
-  qsb_batch* batch = nullptr;
-  int rc = qsb_batch_create(job.ctx, slot, job.n_programs, job.progs, i1 - i0, job.prog_of_instance + i0, &batch);
-  if (rc) return rc;
-  auto done = [&](int code) { std::string keep = g_err; qsb_batch_destroy(batch); g_err = keep; return code; };
-  if ((rc = qsb_batch_set_params(batch, job.params + poff[i0], (size_t)(poff[i1] - poff[i0])))) return done(rc);
-  if (job.target && (rc = qsb_batch_set_target(batch, job.target))) return done(rc);
-  const size_t NN2 = 2 * ((size_t)1 << (2 * batch->n_qubits));
-  int first = 0;
-  const int n = i1 - i0;
-  while (first < n) {
-    int count = 0;
-    size_t bytes = 0;
-    while (first + count < n) {  // grow the chunk until the output budget is reached (always at least one instance)
-      size_t sa, sb, sc;
-      out_sizes(batch, job.what, first + count, 1, &sa, &sb, &sc);
-      size_t add = (sa + sb + sc) * sizeof(double);
-      if (count > 0 && bytes + add > QSB_CHUNK_BYTES) break;
-      bytes += add; ++count;
+  // two batches = two sets of device output buffers: the kernel of chunk c+1 runs while chunk c is copied to the host
+  qsb_batch* batch[2] = {nullptr, nullptr};
+  cudaEvent_t ev_kernel[2] = {nullptr, nullptr}, ev_copy[2] = {nullptr, nullptr};
+  const QsbDevice& d = job.ctx->devs[slot];
+  auto done = [&](int code) {
+    std::string keep = g_err;
+    cudaStreamSynchronize(d.copy_stream);
+    for (int k = 0; k < 2; ++k) {
+      if (batch[k]) qsb_batch_destroy(batch[k]);
+      if (ev_kernel[k]) cudaEventDestroy(ev_kernel[k]);
+      if (ev_copy[k]) cudaEventDestroy(ev_copy[k]);
     }
-    if ((rc = qsb_batch_run(batch, job.what, first, count, nullptr))) return done(rc);
+    g_err = keep;
+    return code;
+  };
+  int rc;
+  const int n = i1 - i0;
+  // chunk list (output bytes per chunk bounded; always at least one instance per chunk)
+  std::vector<int> starts;
+  {
+    qsb_batch probe;  // only param_off / n_qubits are needed by out_sizes
+    probe.n_qubits = job.progs[0]->n_qubits;
+    probe.param_off.assign(poff.begin() + i0, poff.begin() + i1 + 1);
+    size_t sa, sb, sc;
+    out_sizes(&probe, job.what, 0, n, &sa, &sb, &sc);
+    const size_t total = (sa + sb + sc) * sizeof(double);
+    size_t budget = std::min(QSB_CHUNK_BYTES, std::max<size_t>((size_t)32 << 20, total / 8));
+    if (const char* e = getenv("QSB_CHUNK_BYTES")) { long long v = atoll(e); if (v > 0) budget = (size_t)v; }  // tests
+    int first = 0;
+    while (first < n) {
+      int count = 0;
+      size_t bytes = 0;
+      while (first + count < n) {
+        out_sizes(&probe, job.what, first + count, 1, &sa, &sb, &sc);
+        const size_t add = (sa + sb + sc) * sizeof(double);
+        if (count > 0 && bytes + add > budget) break;
+        bytes += add; ++count;
+      }
+      starts.push_back(first);
+      first += count;
+    }
+    starts.push_back(n);
+  }
+  const int n_chunks = (int)starts.size() - 1;
+  const int n_sets = n_chunks > 1 ? 2 : 1;
+  for (int k = 0; k < n_sets; ++k) {
+    if ((rc = qsb_batch_create(job.ctx, slot, job.n_programs, job.progs, n, job.prog_of_instance + i0, &batch[k]))) return done(rc);
+    if ((rc = qsb_batch_set_params(batch[k], job.params + poff[i0], (size_t)(poff[i1] - poff[i0])))) return done(rc);
+    if (job.target && (rc = qsb_batch_set_target(batch[k], job.target))) return done(rc);
+    if (cudaEventCreateWithFlags(&ev_kernel[k], cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&ev_copy[k], cudaEventDisableTiming) != cudaSuccess)
+      return done(qsb_fail(QSB_ERR_CUDA, "cudaEventCreate failed"));
+  }
+  const size_t NN2 = 2 * ((size_t)1 << (2 * batch[0]->n_qubits));
+#define QSB_R(call) do { cudaError_t _e = (call); if (_e != cudaSuccess) return done(qsb_cuda_fail(_e, #call)); } while (0)
+  auto launch = [&](int c) -> int {
+    const int k = c % n_sets;
+    if (c >= n_sets) { cudaError_t e = cudaStreamWaitEvent(d.stream, ev_copy[k], 0); if (e != cudaSuccess) return qsb_cuda_fail(e, "cudaStreamWaitEvent"); }
+    int r = qsb_batch_run(batch[k], job.what, starts[c], starts[c + 1] - starts[c], nullptr);
+    if (r) return r;
+    cudaError_t e = cudaEventRecord(ev_kernel[k], d.stream);
+    return e == cudaSuccess ? QSB_OK : qsb_cuda_fail(e, "cudaEventRecord");
+  };
+  if ((rc = launch(0))) return done(rc);
+  for (int c = 0; c < n_chunks; ++c) {
+    if (c + 1 < n_chunks && (rc = launch(c + 1))) return done(rc);
+    const int k = c % n_sets, first = starts[c], count = starts[c + 1] - starts[c];
     const long long g0 = i0 + first;  // global instance index of the chunk start
     const long long p0 = poff[g0];
-    double *pa = nullptr, *pb = nullptr, *pc = nullptr;
+    double *pa = nullptr, *pb = nullptr;
     switch (job.what) {
       case QSB_RUN_MATRIX: pa = job.a + g0 * NN2; break;
       case QSB_RUN_DIST: pa = job.a + g0; break;
@@ -429,9 +491,17 @@ static int run_shard(const HostEvalJob& job, int slot, int i0, int i1, const std
       case QSB_RUN_HS: pa = job.a + g0; pb = job.b + p0; break;
       default: break;
     }
-    if ((rc = qsb_batch_fetch(batch, job.what, pa, pb, pc))) return done(rc);
-    first += count;
+    size_t na, nb, nc;
+    out_sizes(batch[k], job.what, first, count, &na, &nb, &nc);
+    QSB_R(cudaStreamWaitEvent(d.copy_stream, ev_kernel[k], 0));
+    if (pa && na) QSB_R(cudaMemcpyAsync(pa, batch[k]->out_a.p, na * sizeof(double), cudaMemcpyDeviceToHost, d.copy_stream));
+    if (pb && nb) QSB_R(cudaMemcpyAsync(pb, batch[k]->out_b.p, nb * sizeof(double), cudaMemcpyDeviceToHost, d.copy_stream));
+    QSB_R(cudaEventRecord(ev_copy[k], d.copy_stream));
   }
+  QSB_R(cudaStreamSynchronize(d.copy_stream));
+  QSB_R(cudaStreamSynchronize(d.stream));
+  QSB_R(cudaGetLastError());
+#undef QSB_R
   return done(QSB_OK);
 }
 

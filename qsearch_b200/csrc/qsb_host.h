@@ -10,7 +10,8 @@
 struct QsbDevice {
   int id = 0;
   int sm_count = 148;
-  cudaStream_t stream = nullptr;
+  cudaStream_t stream = nullptr;       // compute
+  cudaStream_t copy_stream = nullptr;  // device->host copies of the host-buffer calls (overlap with the next chunk)
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
 };
 

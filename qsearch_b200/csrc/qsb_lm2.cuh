@@ -14,46 +14,76 @@
 
 #define QSB_LM_WARPS 8
 
+#ifdef QSB_EMU
+#define QSB_CLOCK() 0ll
+#define QSB_LDCG(p) (*(p))
+static inline void qsb_cluster_sync() { qsb_emu_cluster_sync(); }
+#else
+#define QSB_CLOCK() clock64()
+#define QSB_LDCG(p) __ldcg(p)
+// all threads of all CTAs of the cluster; release/acquire orders the global-memory traffic between them
+__device__ __forceinline__ void qsb_cluster_sync() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\nbarrier.cluster.wait.acquire.aligned;\n" ::: "memory");
+}
+#endif
+#define QSB_LM_MAX_CLUSTER 8
+// phase timers: thread 0 of each CTA accumulates cycles into a.prof (only when profiling was requested)
+#define QSB_PROF_BEGIN() long long _t0 = a.prof ? QSB_CLOCK() : 0ll
+#define QSB_PROF_END(slot) do { if (a.prof && threadIdx.x == 0) atomicAdd((unsigned long long*)&a.prof[slot], (unsigned long long)(QSB_CLOCK() - _t0)); } while (0)
+
 // A[k][l] = sum_m R[k][m] R[l][m] for k, l < rows (both triangles written; ld = rows).  R row-major [rows][K2].
-QSB_DEVICE void qsb_syrk_dmma(const double* R, int rows, int K2, double* A, int warp, int nwarps, int lane) {
+// One warp per TB x TB block of the lower triangle (TB = 8 TW); the rows stream from L2, so bigger blocks mean
+// proportionally fewer bytes per flop.  task0 / ntask_stride: this warp's position among all cooperating warps.
+template <int TW>
+QSB_DEVICE void qsb_syrk_dmma_t(const double* R, int rows, int K2, double* A, int task0, int stride, int lane) {
+  constexpr int TB = 8 * TW;
   const int g = lane >> 2, t = lane & 3;
-  const int nb = (rows + 15) >> 4, ntasks = nb * (nb + 1) / 2;
-  for (int task = warp; task < ntasks; task += nwarps) {
+  const int nb = (rows + TB - 1) / TB, ntasks = nb * (nb + 1) / 2;
+  for (int task = task0; task < ntasks; task += stride) {
     int bk = (int)((sqrt(8.0 * task + 1.0) - 1.0) * 0.5);
     while ((bk + 1) * (bk + 2) / 2 <= task) ++bk;
     while (bk * (bk + 1) / 2 > task) --bk;
     const int bl = task - bk * (bk + 1) / 2;
-    double acc[2][2][2];
-    const double* pa[2];
-    const double* pb[2];
+    double acc[TW][TW][2];
+    const double* pa[TW];
+    const double* pb[TW];
 #pragma unroll
-    for (int i = 0; i < 2; ++i) {
-      int ra = 16 * bk + 8 * i + g, rb = 16 * bl + 8 * i + g;
+    for (int i = 0; i < TW; ++i) {
+      int ra = TB * bk + 8 * i + g, rb = TB * bl + 8 * i + g;
       if (ra > rows - 1) ra = rows - 1;
       if (rb > rows - 1) rb = rows - 1;
       pa[i] = R + (size_t)ra * K2 + t;
       pb[i] = R + (size_t)rb * K2 + t;
 #pragma unroll
-      for (int j = 0; j < 2; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
+      for (int j = 0; j < TW; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
     }
 #pragma unroll 4
     for (int m0 = 0; m0 < K2; m0 += 4) {
-      const double a0 = pa[0][m0], a1 = pa[1][m0], b0 = pb[0][m0], b1 = pb[1][m0];
-      qsb_dmma884(acc[0][0][0], acc[0][0][1], a0, b0);
-      qsb_dmma884(acc[0][1][0], acc[0][1][1], a0, b1);
-      qsb_dmma884(acc[1][0][0], acc[1][0][1], a1, b0);
-      qsb_dmma884(acc[1][1][0], acc[1][1][1], a1, b1);
+      double av[TW], bv[TW];
+#pragma unroll
+      for (int i = 0; i < TW; ++i) { av[i] = QSB_LDCG(pa[i] + m0); bv[i] = QSB_LDCG(pb[i] + m0); }
+#pragma unroll
+      for (int i = 0; i < TW; ++i)
+#pragma unroll
+        for (int j = 0; j < TW; ++j) qsb_dmma884(acc[i][j][0], acc[i][j][1], av[i], bv[j]);
     }
 #pragma unroll
-    for (int i = 0; i < 2; ++i)
+    for (int i = 0; i < TW; ++i)
 #pragma unroll
-      for (int j = 0; j < 2; ++j)
+      for (int j = 0; j < TW; ++j)
 #pragma unroll
         for (int e = 0; e < 2; ++e) {
-          const int k = 16 * bk + 8 * i + g, l = 16 * bl + 8 * j + 2 * t + e;
+          const int k = TB * bk + 8 * i + g, l = TB * bl + 8 * j + 2 * t + e;
           if (k < rows && l < rows) { A[(size_t)k * rows + l] = acc[i][j][e]; A[(size_t)l * rows + k] = acc[i][j][e]; }
         }
   }
+}
+
+// warp = index of this warp among the nwarps cooperating warps (all CTAs of the cluster)
+QSB_DEVICE void qsb_syrk_dmma(const double* R, int rows, int K2, double* A, int warp, int nwarps, int lane) {
+  const int nb32 = (rows + 31) / 32;
+  if (nb32 * (nb32 + 1) / 2 >= 2 * nwarps) qsb_syrk_dmma_t<4>(R, rows, K2, A, warp, nwarps, lane);
+  else qsb_syrk_dmma_t<2>(R, rows, K2, A, warp, nwarps, lane);
 }
 
 // Forward-only sweep on the 8 columns [8 cb, 8 cb + 8) of X = U T^dagger: returns this block's share of
@@ -138,12 +168,310 @@ QSB_DEVICE void qsb_cta_segments(const QsbDevProgram& P, int nseg, int* seg) {
 
 // r -> row P of R, J_r -> rows 0..P-1 (R row-major [(P+1)][2 N^2]); trig must hold the table of the current x
 template <int NQ>
-QSB_DEVICE void qsb_cta_jac(const QsbDevProgram& P, const double* target, const double* trig, const int* seg, double* R) {
+QSB_DEVICE void qsb_cta_jac(const QsbDevProgram& P, const double* target, const double* trig, const int* seg, int rank,
+                            double* R) {
   using G = QsbWarpGeom<NQ>;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int tile = warp % G::WARPS, s = warp / G::WARPS;
+  const int tile = warp % G::WARPS, s = rank * (QSB_LM_WARPS / G::WARPS) + warp / G::WARPS;
   qsb_warp_jac_range<NQ, QSB_RUN_RESID>(P, target, trig, tile, lane, seg[s], seg[s + 1],
                                         R + (size_t)P.n_params * 2 * G::NN, R);
+}
+
+// ---------------------------------------------------------------------------- blocked Cholesky on the tensor cores
+// Factor the augmented damped normal matrix  B = [A + mu diag(d2), g ; g^T, r^T r]  ((P+1) x (P+1), A = J^T J and
+// g = J^T r are rows/columns of the Gram matrix of [J_r ; r]) in the work buffer Lb (ld = rows = P+1):
+//   lower triangle of rows 0..P-1 : L,   upper triangle : L^T (so both solves read contiguous rows),
+//   row P                         : y^T with L y = g  (the forward substitution comes for free).
+// Right-looking, 16-wide panels: diagonal block by one warp in shared memory, panel solve one row per thread,
+// trailing update C -= P P^T as 16x16 DMMA tiles.  Returns false (uniformly) if a pivot is not positive.
+#define QSB_CH_NB 16
+#define QSB_CH_LD 17
+#define QSB_CH_MAXROWS 272  // P + 1 <= 272 (host checks)
+
+struct QsbCholSmem {
+  double D[QSB_CH_NB * QSB_CH_LD];
+  double rinv[QSB_CH_NB];
+  double Pn[QSB_CH_MAXROWS * QSB_CH_LD];
+  int ok;
+};
+
+QSB_DEVICE bool qsb_chol_blocked(const double* A, int rows, const double* d2, double mu, int P, double* Lb, QsbCholSmem* cs) {
+  constexpr int NB = QSB_CH_NB, LD = QSB_CH_LD;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+  const int g = lane >> 2, t = lane & 3;
+  __syncthreads();
+  for (int e = threadIdx.x; e < rows * rows; e += blockDim.x) {
+    const int i = e / rows, j = e - i * rows;
+    if (j <= i) Lb[e] = QSB_LDCG(A + e) + ((i == j && i < P) ? mu * d2[i] : 0.0);
+  }
+  if (threadIdx.x == 0) cs->ok = 1;
+  __syncthreads();
+  for (int kb = 0; kb < P; kb += NB) {
+    const int nbk = (P - kb < NB) ? P - kb : NB;
+    // 1. diagonal block (one warp, shared memory)
+    if (warp == 0) {
+      for (int e = lane; e < NB * NB; e += 32) {
+        const int i = e / NB, j = e % NB;
+        double v = (i == j) ? 1.0 : 0.0;
+        if (i < nbk && j < nbk && j <= i) v = Lb[(size_t)(kb + i) * rows + kb + j];
+        else if (i < nbk && j < nbk) v = 0.0;
+        cs->D[i * LD + j] = v;
+      }
+      __syncwarp();
+      for (int j = 0; j < nbk; ++j) {
+        const double piv = cs->D[j * LD + j];
+        if (!(piv > 0.0) || !(piv < 1e300)) { if (lane == 0) cs->ok = 0; break; }
+        const double s = sqrt(piv), inv = 1.0 / s;
+        __syncwarp();
+        if (lane == j) { cs->D[j * LD + j] = s; cs->rinv[j] = inv; }
+        else if (lane > j && lane < nbk) cs->D[lane * LD + j] *= inv;
+        __syncwarp();
+        if (lane > j && lane < nbk) {
+          const double lij = cs->D[lane * LD + j];
+          for (int k = j + 1; k <= lane; ++k) cs->D[lane * LD + k] = fma(-lij, cs->D[k * LD + j], cs->D[lane * LD + k]);
+        }
+        __syncwarp();
+      }
+      for (int j = nbk + lane; j < NB; j += 32) cs->rinv[j] = 1.0;
+      for (int e = lane; e < nbk * nbk; e += 32) {  // write L and L^T of the block
+        const int i = e / nbk, j = e % nbk;
+        if (j <= i) {
+          const double v = cs->D[i * LD + j];
+          Lb[(size_t)(kb + i) * rows + kb + j] = v;
+          Lb[(size_t)(kb + j) * rows + kb + i] = v;
+        }
+      }
+    }
+    __syncthreads();
+    if (!cs->ok) { __syncthreads(); return false; }
+    // 2. panel: rows below the block, X L_kk^T = A_panel, one row per thread
+    const int R0 = kb + nbk, nrow = rows - R0;
+    for (int ri = threadIdx.x; ri < nrow; ri += blockDim.x) {
+      const int i = R0 + ri;
+      double x[NB];
+      double* src = Lb + (size_t)i * rows + kb;
+#pragma unroll
+      for (int j = 0; j < NB; ++j) x[j] = (j < nbk) ? src[j] : 0.0;
+#pragma unroll
+      for (int j = 0; j < NB; ++j) {
+        double s = x[j];
+#pragma unroll
+        for (int m = 0; m < j; ++m) s = fma(-x[m], cs->D[j * LD + m], s);
+        x[j] = (j < nbk) ? s * cs->rinv[j] : 0.0;
+      }
+#pragma unroll
+      for (int j = 0; j < NB; ++j) {
+        cs->Pn[ri * LD + j] = x[j];
+        if (j < nbk) { src[j] = x[j]; Lb[(size_t)(kb + j) * rows + i] = x[j]; }
+      }
+    }
+    __syncthreads();
+    // 3. trailing update of the rows below R0 (the augmented row P rides along); nothing to do if only row P is left
+    if (R0 < P) {
+      const int nbt = (nrow + 15) >> 4, ntasks = nbt * (nbt + 1) / 2;
+      for (int task = warp; task < ntasks; task += nwarps) {
+        int bi = (int)((sqrt(8.0 * task + 1.0) - 1.0) * 0.5);
+        while ((bi + 1) * (bi + 2) / 2 <= task) ++bi;
+        while (bi * (bi + 1) / 2 > task) --bi;
+        const int bj = task - bi * (bi + 1) / 2;
+        double acc[2][2][2];
+        int ra[2], rb[2];
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+          ra[i] = 16 * bi + 8 * i + g; if (ra[i] > nrow - 1) ra[i] = nrow - 1;
+          rb[i] = 16 * bj + 8 * i + g; if (rb[i] > nrow - 1) rb[i] = nrow - 1;
+        }
+#pragma unroll
+        for (int i = 0; i < 2; ++i)
+#pragma unroll
+          for (int j = 0; j < 2; ++j)
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+              const int r = 16 * bi + 8 * i + g, c = 16 * bj + 8 * j + 2 * t + e;
+              acc[i][j][e] = (r < nrow && c < nrow) ? Lb[(size_t)(R0 + r) * rows + R0 + c] : 0.0;
+            }
+#pragma unroll
+        for (int ks = 0; ks < NB / 4; ++ks) {
+          const double a0 = -cs->Pn[ra[0] * LD + 4 * ks + t], a1 = -cs->Pn[ra[1] * LD + 4 * ks + t];
+          const double b0 = cs->Pn[rb[0] * LD + 4 * ks + t], b1 = cs->Pn[rb[1] * LD + 4 * ks + t];
+          qsb_dmma884(acc[0][0][0], acc[0][0][1], a0, b0);
+          qsb_dmma884(acc[0][1][0], acc[0][1][1], a0, b1);
+          qsb_dmma884(acc[1][0][0], acc[1][0][1], a1, b0);
+          qsb_dmma884(acc[1][1][0], acc[1][1][1], a1, b1);
+        }
+#pragma unroll
+        for (int i = 0; i < 2; ++i)
+#pragma unroll
+          for (int j = 0; j < 2; ++j)
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+              const int r = 16 * bi + 8 * i + g, c = 16 * bj + 8 * j + 2 * t + e;
+              if (r < nrow && c < nrow && c <= r) Lb[(size_t)(R0 + r) * rows + R0 + c] = acc[i][j][e];
+            }
+      }
+    }
+    __syncthreads();
+  }
+  return true;
+}
+
+// h = -(L^T)^{-1} y with y = row P of Lb (see qsb_chol_blocked); one warp, rows of L^T are contiguous in Lb.
+QSB_DEVICE void qsb_chol_back(const double* Lb, int rows, int P, double* h) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  __syncthreads();
+  if (warp == 0) {
+    const double* y = Lb + (size_t)P * rows;
+    for (int j = P - 1; j >= 0; --j) {
+      const double* u = Lb + (size_t)j * rows;  // row j of L^T: u[i] = L[i][j], i >= j
+      double s = 0.0;
+      for (int i = j + 1 + lane; i < P; i += 32) s = fma(u[i], h[i], s);
+      for (int m = 16; m > 0; m >>= 1) s += __shfl_xor_sync(QSB_FULL, s, m);
+      if (lane == 0) h[j] = (-y[j] - s) / u[j];
+      __syncwarp();
+    }
+  }
+  __syncthreads();
+}
+
+// ---------------------------------------------------------------------------- the same factorisation, shared memory
+// Packed lower triangle Ls[i (i+1) / 2 + j] of the augmented matrix (rows = P + 1) entirely in shared memory: no
+// L2 round trips inside the factorisation.  Used whenever it fits (P <= ~220); otherwise qsb_chol_blocked.
+#define QSB_TRI(i, j) ((size_t)(i) * ((i) + 1) / 2 + (j))
+
+QSB_DEVICE bool qsb_chol_packed(const double* A, int rows, const double* d2, double mu, int P, double* Ls, double* rinv, double* rdiag, int* okflag) {
+  constexpr int NB = QSB_CH_NB;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+  const int g = lane >> 2, t = lane & 3;
+  __syncthreads();
+  for (int e = threadIdx.x; e < rows * rows; e += blockDim.x) {
+    const int i = e / rows, j = e - i * rows;
+    if (j <= i) Ls[QSB_TRI(i, j)] = QSB_LDCG(A + e) + ((i == j && i < P) ? mu * d2[i] : 0.0);
+  }
+  if (threadIdx.x == 0) *okflag = 1;
+  __syncthreads();
+  for (int kb = 0; kb < P; kb += NB) {
+    const int nbk = (P - kb < NB) ? P - kb : NB;
+    if (warp == 0) {  // 1. diagonal block: lane = row, the row in registers, columns exchanged by shuffle
+      const int il = lane < nbk ? lane : nbk - 1, i = kb + il;
+      double d[NB];
+#pragma unroll
+      for (int j = 0; j < NB; ++j) d[j] = (j <= il && j < nbk) ? Ls[QSB_TRI(i, kb + j)] : 0.0;
+      bool good = true;
+#pragma unroll
+      for (int j = 0; j < NB; ++j) {
+        if (j < nbk) {
+          const double piv = __shfl_sync(QSB_FULL, d[j], j);
+          if (!(piv > 0.0) || !(piv < 1e300)) { good = false; break; }
+          const double sq = sqrt(piv), inv = 1.0 / sq;
+          if (lane == j) { rinv[j] = inv; rdiag[kb + j] = inv; }
+          d[j] = (lane == j) ? sq : d[j] * inv;
+#pragma unroll
+          for (int k = j + 1; k < NB; ++k) {
+            const double lkj = __shfl_sync(QSB_FULL, d[j], k < nbk ? k : 0);
+            if (k <= il) d[k] = fma(-d[j], lkj, d[k]);
+          }
+        }
+      }
+      if (!good && lane == 0) *okflag = 0;
+      if (lane < nbk) {
+#pragma unroll
+        for (int j = 0; j < NB; ++j) if (j <= lane) Ls[QSB_TRI(i, kb + j)] = d[j];
+      }
+    }
+    __syncthreads();
+    if (!*okflag) { __syncthreads(); return false; }
+    const int R0 = kb + nbk, nrow = rows - R0;
+    for (int ri = threadIdx.x; ri < nrow; ri += blockDim.x) {  // 2. panel, one row per thread
+      double* src = Ls + QSB_TRI(R0 + ri, kb);
+      double x[NB];
+#pragma unroll
+      for (int j = 0; j < NB; ++j) x[j] = (j < nbk) ? src[j] : 0.0;
+#pragma unroll
+      for (int j = 0; j < NB; ++j) {
+        if (j < nbk) {
+          double s = x[j];
+          const double* lj = Ls + QSB_TRI(kb + j, kb);
+#pragma unroll
+          for (int m = 0; m < j; ++m) s = fma(-x[m], lj[m], s);
+          x[j] = s * rinv[j];
+          src[j] = x[j];
+        }
+      }
+    }
+    __syncthreads();
+    if (R0 < P) {  // 3. trailing update, 16x16 DMMA tiles of the lower triangle
+      const int nbt = (nrow + 15) >> 4, ntasks = nbt * (nbt + 1) / 2;
+      for (int task = warp; task < ntasks; task += nwarps) {
+        int bi = (int)((sqrt(8.0 * task + 1.0) - 1.0) * 0.5);
+        while ((bi + 1) * (bi + 2) / 2 <= task) ++bi;
+        while (bi * (bi + 1) / 2 > task) --bi;
+        const int bj = task - bi * (bi + 1) / 2;
+        double acc[2][2][2];
+        const double* pa[2];
+        const double* pb[2];
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+          int ra = 16 * bi + 8 * i + g, rb = 16 * bj + 8 * i + g;
+          if (ra > nrow - 1) ra = nrow - 1;
+          if (rb > nrow - 1) rb = nrow - 1;
+          pa[i] = Ls + QSB_TRI(R0 + ra, kb) + t;
+          pb[i] = Ls + QSB_TRI(R0 + rb, kb) + t;
+        }
+#pragma unroll
+        for (int i = 0; i < 2; ++i)
+#pragma unroll
+          for (int j = 0; j < 2; ++j)
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+              const int r = 16 * bi + 8 * i + g, c = 16 * bj + 8 * j + 2 * t + e;
+              acc[i][j][e] = (r < nrow && c <= r) ? Ls[QSB_TRI(R0 + r, R0 + c)] : 0.0;
+            }
+#pragma unroll
+        for (int ks = 0; ks < NB / 4; ++ks) {
+          const bool in = 4 * ks + t < nbk;
+          const double a0 = in ? -pa[0][4 * ks] : 0.0, a1 = in ? -pa[1][4 * ks] : 0.0;
+          const double b0 = in ? pb[0][4 * ks] : 0.0, b1 = in ? pb[1][4 * ks] : 0.0;
+          qsb_dmma884(acc[0][0][0], acc[0][0][1], a0, b0);
+          qsb_dmma884(acc[0][1][0], acc[0][1][1], a0, b1);
+          qsb_dmma884(acc[1][0][0], acc[1][0][1], a1, b0);
+          qsb_dmma884(acc[1][1][0], acc[1][1][1], a1, b1);
+        }
+        __syncwarp();
+#pragma unroll
+        for (int i = 0; i < 2; ++i)
+#pragma unroll
+          for (int j = 0; j < 2; ++j)
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+              const int r = 16 * bi + 8 * i + g, c = 16 * bj + 8 * j + 2 * t + e;
+              if (r < nrow && c <= r) Ls[QSB_TRI(R0 + r, R0 + c)] = acc[i][j][e];
+            }
+      }
+    }
+    __syncthreads();
+  }
+  return true;
+}
+
+// h = -(L^T)^{-1} y, y = row P of the packed factor.  One warp, column sweep: once h_j is known every lane folds it
+// into its own entries of the right-hand side (row j of L is contiguous), so there is no reduction on the critical path.
+QSB_DEVICE void qsb_chol_back_packed(const double* Ls, int P, const double* rdiag, double* h) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  __syncthreads();
+  if (warp == 0) {
+    const double* y = Ls + QSB_TRI(P, 0);
+    for (int i = lane; i < P; i += 32) h[i] = -y[i];
+    __syncwarp();
+    for (int j = P - 1; j >= 0; --j) {
+      const double* lj = Ls + QSB_TRI(j, 0);
+      const double hj = h[j] * rdiag[j];
+      __syncwarp();
+      if (lane == 0) h[j] = hj;
+      for (int i = lane; i < j; i += 32) h[i] = fma(-lj[i], hj, h[i]);
+      __syncwarp();
+    }
+  }
+  __syncthreads();
 }
 
 template <int NQ>
@@ -161,34 +489,41 @@ QSB_GLOBAL __launch_bounds__(QSB_LM_WARPS * 32) qsb_k_lm2(QsbSolveArgs a) {
   double* wy = wk + a.max_params;
   double* trig = wy + a.max_params;         // 2 * maxP
   double* part = trig + 2 * a.max_params;   // 16
-  int* seg = (int*)(part + 16);             // NSEG + 1
+  int* seg = (int*)(part + 16);             // cluster * NSEG + 1 (<= 72 ints)
+  QsbCholSmem* cs = (QsbCholSmem*)(seg + 72);          // global-memory factorisation (large P)
+  double* Ls = (double*)(seg + 72);                     // or: packed factor in shared memory (a.chol_smem)
+  double* rinv = Ls + (size_t)(a.max_params + 1) * (a.max_params + 2) / 2;
+  int* okflag = (int*)(rinv + QSB_CH_NB);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  double* Rg = a.scratch + (size_t)blockIdx.x * a.scratch_per_cta;
-  for (int inst = blockIdx.x; inst < a.count; inst += gridDim.x) {
+  // a cluster of a.cluster CTAs works on one instance: they split the Jacobian segments and the SYRK blocks, share
+  // R and A through global memory (two cluster barriers per iteration) and repeat the small dense algebra redundantly,
+  // so every CTA takes the same decisions without a broadcast.
+  const int csize = a.cluster, rank = blockIdx.x % csize, cid = blockIdx.x / csize, nclusters = gridDim.x / csize;
+  const int cwarps = csize * QSB_LM_WARPS, cwarp = rank * QSB_LM_WARPS + warp;
+  double* Rg = a.scratch + (size_t)cid * a.scratch_per_cta;
+  for (int inst = cid; inst < a.count; inst += nclusters) {
     const QsbDevProgram prog = a.progs[a.prog_idx[inst]];
     const int P = prog.n_params, rows = P + 1;
     double* A = Rg + (size_t)(a.max_params + 1) * M;
-    double* L = A + (size_t)(a.max_params + 1) * (a.max_params + 1);
+    double* L = A + (size_t)(a.max_params + 1) * (a.max_params + 1) + (size_t)rank * (a.max_params + 1) * (a.max_params + 1);
     const double* x0 = a.x0 + a.param_off[inst];
     const int max_iters = a.max_iters > 0 ? a.max_iters : 100 * (P > 0 ? P : 1);
     __syncthreads();
     for (int k = threadIdx.x; k < P; k += blockDim.x) x[k] = x0[k];
-    qsb_cta_segments(prog, NSEG, seg);
+    qsb_cta_segments(prog, NSEG * csize, seg);
     int iters = 0, status = 0;
     cplx tr;
     double F = qsb_cta_half_norm<NQ>(prog, x, a.target, trig, part, &tr);  // also fills trig for x
     if (P > 0) {
-      qsb_cta_jac<NQ>(prog, a.target, trig, seg, Rg);
+      { QSB_PROF_BEGIN(); qsb_cta_jac<NQ>(prog, a.target, trig, seg, rank, Rg); qsb_cluster_sync(); QSB_PROF_END(0); }
       iters = 1;
-      __syncthreads();
-      qsb_syrk_dmma(Rg, rows, M, A, warp, QSB_LM_WARPS, lane);
-      __syncthreads();
+      { QSB_PROF_BEGIN(); qsb_syrk_dmma(Rg, rows, M, A, cwarp, cwarps, lane); qsb_cluster_sync(); QSB_PROF_END(1); }
       for (int k = threadIdx.x; k < P; k += blockDim.x) {
-        g[k] = A[(size_t)P * rows + k];
-        const double akk = A[(size_t)k * rows + k];
+        g[k] = QSB_LDCG(&A[(size_t)P * rows + k]);
+        const double akk = QSB_LDCG(&A[(size_t)k * rows + k]);
         d2[k] = akk > 0.0 ? akk : 1.0;
       }
-      F = 0.5 * A[(size_t)P * rows + P];
+      F = 0.5 * QSB_LDCG(&A[(size_t)P * rows + P]);
       __syncthreads();
       double mu = 1e-3, nu = 2.0;
       int rejects = 0;
@@ -198,19 +533,24 @@ QSB_GLOBAL __launch_bounds__(QSB_LM_WARPS * 32) qsb_k_lm2(QsbSolveArgs a) {
           double gm = 0.0;
           const double rn = sqrt(2.0 * F);
           for (int k = threadIdx.x; k < P; k += blockDim.x) {
-            const double akk = A[(size_t)k * rows + k];
+            const double akk = QSB_LDCG(&A[(size_t)k * rows + k]);
             if (akk > 0.0) gm = fmax(gm, fabs(g[k]) / (sqrt(akk) * rn));
           }
           gm = qsb_block_max(gm, red);
           if (gm <= a.gtol) { status = 1; break; }
         }
-        if (!qsb_cholesky(A, rows, d2, mu, P, L, wk)) {
+        bool chol_ok;
+        {
+          QSB_PROF_BEGIN();
+          chol_ok = a.chol_smem ? qsb_chol_packed(A, rows, d2, mu, P, Ls, rinv, wk, okflag) : qsb_chol_blocked(A, rows, d2, mu, P, L, cs);
+          QSB_PROF_END(2);
+        }
+        if (!chol_ok) {
           mu *= nu; nu *= 2.0;
           if (++rejects > 60 || mu > 1e30) { status = 5; break; }
           continue;
         }
-        for (int k = threadIdx.x; k < P; k += blockDim.x) wk[k] = -g[k];
-        qsb_chol_solve(L, P, wk, wy, h);
+        { QSB_PROF_BEGIN(); if (a.chol_smem) qsb_chol_back_packed(Ls, P, wk, h); else qsb_chol_back(L, rows, P, h); QSB_PROF_END(3); }
         cplx p1 = cmk(0, 0), p2 = cmk(0, 0);
         for (int k = threadIdx.x; k < P; k += blockDim.x) {
           xn[k] = x[k] + h[k];
@@ -221,7 +561,8 @@ QSB_GLOBAL __launch_bounds__(QSB_LM_WARPS * 32) qsb_k_lm2(QsbSolveArgs a) {
         p1 = qsb_block_sum(p1, red);
         p2 = qsb_block_sum(p2, red);
         const double hnorm = sqrt(p1.x), xnorm = sqrt(p1.y), pred = 0.5 * p2.x;
-        const double Fn = qsb_cta_half_norm<NQ>(prog, xn, a.target, trig, part, &tr);  // trig now belongs to xn
+        double Fn;
+        { QSB_PROF_BEGIN(); Fn = qsb_cta_half_norm<NQ>(prog, xn, a.target, trig, part, &tr); QSB_PROF_END(4); }  // trig now belongs to xn
         const double dF = F - Fn;
         const double rho = (pred > 0.0) ? dF / pred : -1.0;
         if (rho > 1e-4 && Fn == Fn) {
@@ -236,16 +577,14 @@ QSB_GLOBAL __launch_bounds__(QSB_LM_WARPS * 32) qsb_k_lm2(QsbSolveArgs a) {
           if (conv_f) { status = 2; break; }
           if (conv_x) { status = 3; break; }
           if (iters >= max_iters) { status = 0; break; }
-          qsb_cta_jac<NQ>(prog, a.target, trig, seg, Rg);
+          { QSB_PROF_BEGIN(); qsb_cta_jac<NQ>(prog, a.target, trig, seg, rank, Rg); qsb_cluster_sync(); QSB_PROF_END(0); }
           ++iters;
-          __syncthreads();
-          qsb_syrk_dmma(Rg, rows, M, A, warp, QSB_LM_WARPS, lane);
-          __syncthreads();
+          { QSB_PROF_BEGIN(); qsb_syrk_dmma(Rg, rows, M, A, cwarp, cwarps, lane); qsb_cluster_sync(); QSB_PROF_END(1); }
           for (int k = threadIdx.x; k < P; k += blockDim.x) {
-            g[k] = A[(size_t)P * rows + k];
-            d2[k] = fmax(d2[k], A[(size_t)k * rows + k]);
+            g[k] = QSB_LDCG(&A[(size_t)P * rows + k]);
+            d2[k] = fmax(d2[k], QSB_LDCG(&A[(size_t)k * rows + k]));
           }
-          F = 0.5 * A[(size_t)P * rows + P];
+          F = 0.5 * QSB_LDCG(&A[(size_t)P * rows + P]);
           __syncthreads();
           const double q = 2.0 * rho - 1.0;
           mu *= fmax(1.0 / 3.0, 1.0 - q * q * q);
@@ -261,6 +600,7 @@ QSB_GLOBAL __launch_bounds__(QSB_LM_WARPS * 32) qsb_k_lm2(QsbSolveArgs a) {
     qsb_cta_half_norm<NQ>(prog, x, a.target, trig, part, &tr);
     double* ox = a.out_x + a.param_off[inst];
     for (int k = threadIdx.x; k < P; k += blockDim.x) ox[k] = x[k];
+    if (a.prof && threadIdx.x == 0) atomicAdd((unsigned long long*)&a.prof[5], (unsigned long long)iters);
     if (threadIdx.x == 0) {
       a.out_f[inst] = fabs(1.0 - sqrt(tr.x * tr.x + tr.y * tr.y) / N);
       a.out_iters[inst] = iters;
@@ -270,6 +610,9 @@ QSB_GLOBAL __launch_bounds__(QSB_LM_WARPS * 32) qsb_k_lm2(QsbSolveArgs a) {
   }
 }
 
-static inline size_t qsb_lm2_smem_bytes(int max_params) {
-  return 32 * 16 + (size_t)9 * max_params * 8 + 16 * 8 + 16 * 4 + 64;
+static inline size_t qsb_lm2_smem_bytes(int max_params, bool chol_smem) {
+  const size_t base = 32 * 16 + (size_t)9 * max_params * 8 + 16 * 8 + 72 * 4 + 64;
+  const size_t packed = ((size_t)(max_params + 1) * (max_params + 2) / 2 + QSB_CH_NB + 2) * 8;
+  return base + (chol_smem ? packed : sizeof(QsbCholSmem));
 }
+

@@ -9,6 +9,7 @@
 #pragma once
 #include <algorithm>
 #include <atomic>
+#include <barrier>
 #include <cmath>
 #include <cstdint>
 #include <cstdio>
@@ -50,6 +51,7 @@ struct BlockState {
   std::vector<std::vector<uint64_t>> warp_buf, warp_buf2;  // [warp][32]
   unsigned char* smem = nullptr;
   const std::function<void()>* body = nullptr;
+  std::barrier<>* cluster_bar = nullptr;  // shared by the CTAs of one emulated thread-block cluster
 };
 inline BlockState*& cur() { static thread_local BlockState* p = nullptr; return p; }
 extern "C" void qsb_emu_switch(void** save_sp, void* load_sp);
@@ -109,6 +111,7 @@ static inline double atomicAdd(double* p, double v) {
   return old;
 }
 static inline int atomicAdd(int* p, int v) { return __atomic_fetch_add(p, v, __ATOMIC_SEQ_CST); }
+static inline unsigned long long atomicAdd(unsigned long long* p, unsigned long long v) { return __atomic_fetch_add(p, v, __ATOMIC_SEQ_CST); }
 static inline double rsqrt(double x) { return 1.0 / std::sqrt(x); }
 static inline double __longlong_as_double(long long v) { double d; std::memcpy(&d, &v, 8); return d; }
 
@@ -121,7 +124,11 @@ enum { cudaSuccess = 0, cudaErrorInvalidValue = 1 };
 enum cudaMemcpyKind { cudaMemcpyHostToDevice, cudaMemcpyDeviceToHost, cudaMemcpyDeviceToDevice, cudaMemcpyDefault };
 enum { cudaFuncAttributeMaxDynamicSharedMemorySize = 8 };
 enum { cudaDevAttrMultiProcessorCount = 16 };
-static inline cudaError_t cudaGetDeviceCount(int* n) { *n = 1; return 0; }
+static inline cudaError_t cudaGetDeviceCount(int* n) {  // QSB_EMU_DEVICES: pretend to have several GPUs (shard tests)
+  const char* e = std::getenv("QSB_EMU_DEVICES");
+  *n = e ? std::max(1, std::atoi(e)) : 1;
+  return 0;
+}
 static inline cudaError_t cudaSetDevice(int) { return 0; }
 static inline cudaError_t cudaDeviceGetAttribute(int* v, int, int) { *v = 4; return 0; }
 static inline cudaError_t cudaMalloc(void** p, size_t n) { *p = std::malloc(n ? n : 1); return *p ? 0 : 2; }
@@ -130,6 +137,7 @@ static inline cudaError_t cudaMallocHost(void** p, size_t n) { return cudaMalloc
 static inline cudaError_t cudaFreeHost(void* p) { return cudaFree(p); }
 static inline cudaError_t cudaMemcpy(void* d, const void* s, size_t n, cudaMemcpyKind) { std::memcpy(d, s, n); return 0; }
 static inline cudaError_t cudaMemcpyAsync(void* d, const void* s, size_t n, cudaMemcpyKind, cudaStream_t = nullptr) { std::memcpy(d, s, n); return 0; }
+static inline cudaError_t cudaMemset(void* d, int v, size_t n) { std::memset(d, v, n); return 0; }
 static inline cudaError_t cudaMemsetAsync(void* d, int v, size_t n, cudaStream_t = nullptr) { std::memset(d, v, n); return 0; }
 static inline cudaError_t cudaStreamCreate(cudaStream_t* s) { *s = nullptr; return 0; }
 static inline cudaError_t cudaStreamCreateWithFlags(cudaStream_t* s, unsigned) { *s = nullptr; return 0; }
@@ -138,6 +146,11 @@ static inline cudaError_t cudaStreamSynchronize(cudaStream_t) { return 0; }
 static inline cudaError_t cudaDeviceSynchronize() { return 0; }
 static inline cudaError_t cudaEventCreate(cudaEvent_t* e) { *e = new qsb_emu_event(); return 0; }
 static inline cudaError_t cudaEventDestroy(cudaEvent_t e) { delete e; return 0; }
+static inline cudaError_t cudaEventCreateWithFlags(cudaEvent_t* e, unsigned) { *e = new qsb_emu_event(); return 0; }
+static inline cudaError_t cudaStreamWaitEvent(cudaStream_t, cudaEvent_t, unsigned) { return 0; }
+static inline cudaError_t cudaHostAlloc(void** p, size_t n, unsigned) { return cudaMalloc(p, n); }
+#define cudaEventDisableTiming 2
+#define cudaHostAllocPortable 1
 static inline cudaError_t cudaEventRecord(cudaEvent_t e, cudaStream_t = nullptr) { e->t = std::chrono::steady_clock::now(); return 0; }
 static inline cudaError_t cudaEventSynchronize(cudaEvent_t) { return 0; }
 static inline cudaError_t cudaEventElapsedTime(float* ms, cudaEvent_t a, cudaEvent_t b) {
@@ -245,7 +258,38 @@ inline void launch(unsigned grid, unsigned block, size_t smem_bytes, const std::
   for (unsigned w = 0; w < workers; ++w) th.emplace_back(work);
   for (auto& x : th) x.join();
 }
+// Thread-block clusters: every block gets its own OS thread (tests launch few blocks), blocks of one cluster share
+// a std::barrier.  qsb_emu_cluster_sync = block barrier, one fiber waits on the cluster barrier, block barrier.
+inline void launch_cluster(unsigned grid, unsigned block, size_t smem_bytes, unsigned csize, const std::function<void()>& body) {
+  std::vector<std::unique_ptr<std::barrier<>>> bars;
+  for (unsigned c = 0; c < grid / csize; ++c) bars.emplace_back(new std::barrier<>(csize));
+  std::vector<std::thread> th;
+  for (unsigned b = 0; b < grid; ++b)
+    th.emplace_back([&, b] {
+      BlockState st;
+      st.nthreads = block;
+      st.grid = grid;
+      st.fibers.resize(block);
+      st.warp_buf.assign((block + 31) / 32, std::vector<uint64_t>(32, 0));
+      st.warp_buf2 = st.warp_buf;
+      std::vector<unsigned char> sm(smem_bytes + 64);
+      st.smem = (unsigned char*)(((uintptr_t)sm.data() + 63) & ~(uintptr_t)63);
+      st.body = &body;
+      st.cluster_bar = bars[b / csize].get();
+      run_block(st, b);
+      cur() = nullptr;
+    });
+  for (auto& x : th) x.join();
+}
 }  // namespace qsb_emu
+static inline void qsb_emu_cluster_sync() {
+  __syncthreads();
+  auto* st = qsb_emu::cur();
+  if (st->cluster_bar && st->fibers[st->current].tid == 0) st->cluster_bar->arrive_and_wait();
+  __syncthreads();
+}
+#define QSB_LAUNCH_CLUSTER(kernel, grid, block, smem, csize, ...) \
+  qsb_emu::launch_cluster((grid), (block), (smem), (csize), std::function<void()>([&] { kernel(__VA_ARGS__); }))
 #define QSB_DYN_SMEM(name) unsigned char* name = qsb_emu::cur()->smem
 #define QSB_LAUNCH(kernel, grid, block, smem, stream, ...) \
   qsb_emu::launch((grid), (block), (smem), std::function<void()>([&] { kernel(__VA_ARGS__); }))

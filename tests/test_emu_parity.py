@@ -43,3 +43,25 @@ def test_bad_programs_are_rejected():
         lowering.lower(gates.SingleQutritGate())
     with pytest.raises(ValueError):
         lib.eval_matrix([gp], [0], np.zeros(5))
+
+
+def test_chunked_pipelined_host_calls(monkeypatch):
+    """Host-buffer calls stream through several device chunks (two buffer sets, copy overlapping the next kernel):
+    force tiny chunks and compare with the single-chunk result."""
+    from qsearch_b200 import gatesets, lowering, unitaries
+    lib = emulated_library()
+    rng = np.random.default_rng(8)
+    g = gatesets.QubitCNOTRing()
+    c = gatesets.ProductGate(g.initial_layer(3)).appending(g.search_layers(3)[1][0]).appending(g.search_layers(3)[2][0])
+    gp = lowering.lower(c)
+    xs = rng.random((7, c.num_inputs)) * 2 * np.pi
+    poi = np.zeros(7, dtype="int32")
+    T = unitaries.qft(8)
+    ref = lib.eval_residuals_jac([gp], poi, xs, T) + lib.eval_mat_jac([gp], poi, xs) + lib.eval_hs_grad([gp], poi, xs, T)
+    monkeypatch.setenv("QSB_CHUNK_BYTES", str(2 * 64 * 8 * (c.num_inputs + 1) * 2 + 8))  # two instances per chunk
+    got = lib.eval_residuals_jac([gp], poi, xs, T) + lib.eval_mat_jac([gp], poi, xs) + lib.eval_hs_grad([gp], poi, xs, T)
+    for a, b in zip(ref, got):
+        assert np.array_equal(a, b)
+    pinned = lib.pinned_empty((7, 2 * 64))
+    r, _ = lib.eval_residuals_jac([gp], poi, xs, T, out_r=pinned)
+    assert r is pinned and np.array_equal(pinned, ref[0])

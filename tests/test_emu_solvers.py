@@ -116,3 +116,15 @@ def test_drop_in_for_the_reference_compiler(emu):
     opts2 = opts.updated(parallelizer=qsearch.parallelizers.SequentialParallelizer)
     res2 = qsearch.SearchCompiler().compile(opts2)
     assert qsearch.comparison.matrix_distance_squared(ru.qft(4), res2["structure"].matrix(res2["parameters"])) < 1e-10
+
+
+def test_tensor_core_lm_on_three_qubits(emu):
+    """qsb_k_lm2 (segment-parallel DMMA Jacobian + DMMA SYRK) in emulation: reaches a reachable 3-qubit target and
+    reports the distance at the returned parameters."""
+    c, T, rng = _reachable_problem(3, 3, 21)
+    gp = lowering.lower(c)
+    x0 = rng.random((3, gp.n_params)) * 2 * np.pi
+    x, f, iters, status = emu.solve("lm", [gp], np.zeros(3, dtype="int32"), x0, T)
+    assert f.min() < 1e-12
+    for k, xk in enumerate(x.reshape(3, -1)):
+        assert abs(O.matrix_distance_squared(T, O.matrix(c, xk)) - f[k]) < 1e-12
