@@ -275,7 +275,7 @@ def run_ours(args, rank, world, local_rank):
     achieved_tf = (n_inst / (kern_ms * 1e-3)) * F / 1e12
     # what the warp kernel really issues on the FP64 tensor pipe: P complex N^3 products = 8 N^3 P flop per eval
     executed_dmma_tf = (n_inst / (kern_ms * 1e-3)) * 8.0 * (N ** 3) * P / 1e12
-    ncu_traffic = {4: 255877.0, 5: 1075282.0}.get(n)  # dram read+write bytes per eval, profiles/r1/c_ncu_full_resid_n*_warp.txt
+    ncu_traffic = {4: 255786.0, 5: 1075282.0}.get(n)  # dram read+write bytes per eval: profiles/r1/l_ncu_full_resid_n4_warp.txt, c_ncu_full_resid_n5_warp.txt
     line = {
         "metric": "objective+Jacobian evals/sec", "value": value, "unit": "evals/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": kern_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -295,7 +295,7 @@ def run_ours(args, rank, world, local_rank):
                               "second; gate structure lets the kernel execute fewer, so frac can exceed 1. Executed on the tensor pipe: "
                               "8 N^3 P flop per eval (see executed)",
                      "executed": {"dmma_tflops": executed_dmma_tf, "frac_of_dmma_peak": executed_dmma_tf / dmma_peak if dmma_peak else None,
-                                  "ncu_dmma_pipe_active_pct": {4: 53.8, 5: 56.7}.get(n)},
+                                  "ncu_dmma_pipe_active_pct": {4: 57.1, 5: 56.7}.get(n)},
                      "traffic_note": "ncu dram bytes per eval (one --set full capture, profiles/r1) x instances of this launch",
                      "hbm": {"achieved": out_bytes / (kern_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
                              "frac": out_bytes / (kern_ms * 1e-3) / 1e9 / hbm_peak,

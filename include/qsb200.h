@@ -54,7 +54,7 @@ typedef struct qsb_op {
   int32_t q1;        /* target (CNOT), k (CONSTK), else 0 */
   int32_t param_off; /* first parameter of this op within the circuit's parameter vector (param ops) */
   int32_t const_off; /* offset in doubles into the constant pool (CONST1 / CONSTK) */
-  int32_t reserved;
+  int32_t reserved;  /* ignored on input; the library stores the op's gate-table slot here in its own copy */
 } qsb_op;
 
 typedef struct qsb_ctx qsb_ctx;

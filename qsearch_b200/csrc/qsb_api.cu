@@ -172,10 +172,25 @@ extern "C" int qsb_program_create(qsb_ctx* ctx, int n_qubits, int n_ops, const q
       default: break;
     }
   }
+  // gate-table slots: op j owns slots [reserved, reserved + 1 + np): its 2x2 and the np parameter derivatives
+  std::vector<int32_t> slotmap((size_t)std::max(1, n_ops + n_params), -1);
+  {
+    int used = 0;
+    for (int j = 0; j < n_ops; ++j) {
+      qsb_op& o = p->ops[j];
+      const int np = op_params(o.opcode);
+      o.reserved = j + used;
+      if (o.opcode != QSB_OP_CNOT && o.opcode != QSB_OP_CONSTK)
+        for (int w = 0; w <= np; ++w) slotmap[o.reserved + w] = (j << 2) | w;
+      used += np;
+    }
+  }
+  ops = p->ops.data();
   for (auto& d : ctx->devs) {
     qsb_op* dops = nullptr;
     double* dc = nullptr;
     double* dps = nullptr;
+    int32_t* dsm = nullptr;
     QSB_CUDA(cudaSetDevice(d.id));
     QSB_CUDA(cudaMalloc((void**)&dops, sizeof(qsb_op) * std::max(1, n_ops)));
     QSB_CUDA(cudaMalloc((void**)&dc, sizeof(double) * std::max<size_t>(1, const_len)));
@@ -185,7 +200,10 @@ extern "C" int qsb_program_create(qsb_ctx* ctx, int n_qubits, int n_ops, const q
     QSB_CUDA(cudaMemcpy(dps, pscale.data(), sizeof(double) * pscale.size(), cudaMemcpyHostToDevice));
     p->d_ops.push_back(dops);
     p->d_consts.push_back(dc);
+    QSB_CUDA(cudaMalloc((void**)&dsm, sizeof(int32_t) * slotmap.size()));
+    QSB_CUDA(cudaMemcpy(dsm, slotmap.data(), sizeof(int32_t) * slotmap.size(), cudaMemcpyHostToDevice));
     p->d_pscale.push_back(dps);
+    p->d_slotmap.push_back(dsm);
   }
   *out_prog = p;
   return QSB_OK;
@@ -199,6 +217,7 @@ extern "C" int qsb_program_destroy(qsb_ctx* ctx, qsb_program* prog) {
       cudaFree(prog->d_ops[s]);
       cudaFree(prog->d_consts[s]);
       cudaFree(prog->d_pscale[s]);
+      cudaFree(prog->d_slotmap[s]);
     }
   }
   delete prog;
@@ -238,7 +257,7 @@ extern "C" int qsb_batch_create(qsb_ctx* ctx, int slot, int n_programs, const qs
   b->force_generic = ctx->force_generic;
   std::vector<QsbDevProgram> dp(n_programs);
   for (int p = 0; p < n_programs; ++p) {
-    dp[p].ops = progs[p]->d_ops[slot]; dp[p].consts = progs[p]->d_consts[slot]; dp[p].pscale = progs[p]->d_pscale[slot];
+    dp[p].ops = progs[p]->d_ops[slot]; dp[p].consts = progs[p]->d_consts[slot]; dp[p].pscale = progs[p]->d_pscale[slot]; dp[p].slotmap = progs[p]->d_slotmap[slot];
     dp[p].n_ops = progs[p]->n_ops; dp[p].n_params = progs[p]->n_params;
     b->max_ops = std::max(b->max_ops, progs[p]->n_ops);
     b->max_params = std::max(b->max_params, progs[p]->n_params);

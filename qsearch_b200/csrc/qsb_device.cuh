@@ -23,6 +23,8 @@ struct QsbDevProgram {
   const qsb_op* ops;
   const double* consts;
   const double* pscale;  // [n_params]: factor applied to a parameter before its sin/cos (0.5 for half-angle gates)
+  const int32_t* slotmap; // [n_ops + n_params]: gate-table slot -> (op index << 2 | which), -1 for unused slots; the
+                          // slot of op j's matrix is ops[j].reserved, its derivative k sits at reserved + 1 + k
   int n_ops;
   int n_params;
 };

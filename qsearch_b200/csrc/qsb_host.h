@@ -30,6 +30,7 @@ struct qsb_program {
   std::vector<qsb_op*> d_ops;       // per device slot
   std::vector<double*> d_consts;
   std::vector<double*> d_pscale;
+  std::vector<int32_t*> d_slotmap;
 };
 
 struct QsbBuf {

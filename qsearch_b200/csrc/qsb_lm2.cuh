@@ -89,7 +89,7 @@ QSB_DEVICE void qsb_syrk_dmma(const double* R, int rows, int K2, double* A, int 
 // Forward-only sweep on the 8 columns [8 cb, 8 cb + 8) of X = U T^dagger: returns this block's share of
 // |X - I|_F^2 (every lane) and of Tr(X).
 template <int NQ>
-QSB_DEVICE void qsb_warp_forward8(const QsbDevProgram& P, const double* target, const double* trig, int cb, int lane,
+QSB_DEVICE void qsb_warp_forward8(const QsbDevProgram& P, const double* target, const cplx* gtab, int cb, int lane,
                                   double& norm2, cplx& tr) {
   constexpr int N = 1 << NQ, KS = N / 4;
   const int g = lane >> 2, t = lane & 3, c = 8 * cb + g;
@@ -103,7 +103,7 @@ QSB_DEVICE void qsb_warp_forward8(const QsbDevProgram& P, const double* target, 
     const qsb_op op = P.ops[j];
     if (op.opcode == QSB_OP_CNOT) { qsb_cnot<NQ, 1>(X, op.q0, op.q1, lane); continue; }
     cplx m[4];
-    qsb_warp_gate(op, trig, P.consts, m);
+    qsb_warp_gate(op, gtab, 0, m);
     qsb_mix<NQ, 1>(X, op.q0, m, lane);
   }
   double s = 0.0;
@@ -123,10 +123,10 @@ QSB_DEVICE void qsb_warp_forward8(const QsbDevProgram& P, const double* target, 
   norm2 = s; tr = d;
 }
 
-// CTA-wide: (cos, sin) table of x, then F = |U T^dagger - I|_F^2 / 2 and Tr(U T^dagger).  part: >= 3 * (N/8) doubles.
+// CTA-wide: (cos, sin) table and gate table of x, then F = |U T^dagger - I|_F^2 / 2 and Tr(U T^dagger).  part: >= 3 * (N/8) doubles.
 template <int NQ>
 QSB_DEVICE double qsb_cta_half_norm(const QsbDevProgram& P, const double* x, const double* target, double* trig,
-                                    double* part, cplx* tr_out) {
+                                    cplx* gtab, double* part, cplx* tr_out) {
   constexpr int NCB = (1 << NQ) / 8;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   __syncthreads();
@@ -136,9 +136,11 @@ QSB_DEVICE double qsb_cta_half_norm(const QsbDevProgram& P, const double* x, con
     trig[2 * p] = c; trig[2 * p + 1] = s;
   }
   __syncthreads();
+  qsb_fill_gates(P, trig, gtab, threadIdx.x, blockDim.x);
+  __syncthreads();
   if (warp < NCB) {
     double n2; cplx tr;
-    qsb_warp_forward8<NQ>(P, target, trig, warp, lane, n2, tr);
+    qsb_warp_forward8<NQ>(P, target, gtab, warp, lane, n2, tr);
     if (lane == 0) { part[3 * warp] = n2; part[3 * warp + 1] = tr.x; part[3 * warp + 2] = tr.y; }
   }
   __syncthreads();
@@ -166,14 +168,14 @@ QSB_DEVICE void qsb_cta_segments(const QsbDevProgram& P, int nseg, int* seg) {
   }
 }
 
-// r -> row P of R, J_r -> rows 0..P-1 (R row-major [(P+1)][2 N^2]); trig must hold the table of the current x
+// r -> row P of R, J_r -> rows 0..P-1 (R row-major [(P+1)][2 N^2]); gtab must hold the gate table of the current x
 template <int NQ>
-QSB_DEVICE void qsb_cta_jac(const QsbDevProgram& P, const double* target, const double* trig, const int* seg, int rank,
+QSB_DEVICE void qsb_cta_jac(const QsbDevProgram& P, const double* target, const cplx* gtab, const int* seg, int rank,
                             double* R) {
   using G = QsbWarpGeom<NQ>;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int tile = warp % G::WARPS, s = rank * (QSB_LM_WARPS / G::WARPS) + warp / G::WARPS;
-  qsb_warp_jac_range<NQ, QSB_RUN_RESID>(P, target, trig, tile, lane, seg[s], seg[s + 1],
+  qsb_warp_jac_range<NQ, QSB_RUN_RESID>(P, target, gtab, tile, lane, seg[s], seg[s + 1],
                                         R + (size_t)P.n_params * 2 * G::NN, R);
 }
 
@@ -489,7 +491,8 @@ QSB_GLOBAL __launch_bounds__(QSB_LM_WARPS * 32) qsb_k_lm2(QsbSolveArgs a) {
   double* wy = wk + a.max_params;
   double* trig = wy + a.max_params;         // 2 * maxP
   double* part = trig + 2 * a.max_params;   // 16
-  int* seg = (int*)(part + 16);             // cluster * NSEG + 1 (<= 72 ints)
+  cplx* gtab = (cplx*)(part + 16 + (a.max_params & 1));  // [max_ops + max_params][4], 16-byte aligned
+  int* seg = (int*)(gtab + (size_t)4 * (a.max_ops + a.max_params));  // cluster * NSEG + 1 (<= 72 ints)
   QsbCholSmem* cs = (QsbCholSmem*)(seg + 72);          // global-memory factorisation (large P)
   double* Ls = (double*)(seg + 72);                     // or: packed factor in shared memory (a.chol_smem)
   double* rinv = Ls + (size_t)(a.max_params + 1) * (a.max_params + 2) / 2;
@@ -513,9 +516,9 @@ QSB_GLOBAL __launch_bounds__(QSB_LM_WARPS * 32) qsb_k_lm2(QsbSolveArgs a) {
     qsb_cta_segments(prog, NSEG * csize, seg);
     int iters = 0, status = 0;
     cplx tr;
-    double F = qsb_cta_half_norm<NQ>(prog, x, a.target, trig, part, &tr);  // also fills trig for x
+    double F = qsb_cta_half_norm<NQ>(prog, x, a.target, trig, gtab, part, &tr);  // also fills trig for x
     if (P > 0) {
-      { QSB_PROF_BEGIN(); qsb_cta_jac<NQ>(prog, a.target, trig, seg, rank, Rg); qsb_cluster_sync(); QSB_PROF_END(0); }
+      { QSB_PROF_BEGIN(); qsb_cta_jac<NQ>(prog, a.target, gtab, seg, rank, Rg); qsb_cluster_sync(); QSB_PROF_END(0); }
       iters = 1;
       { QSB_PROF_BEGIN(); qsb_syrk_dmma(Rg, rows, M, A, cwarp, cwarps, lane); qsb_cluster_sync(); QSB_PROF_END(1); }
       for (int k = threadIdx.x; k < P; k += blockDim.x) {
@@ -562,7 +565,7 @@ QSB_GLOBAL __launch_bounds__(QSB_LM_WARPS * 32) qsb_k_lm2(QsbSolveArgs a) {
         p2 = qsb_block_sum(p2, red);
         const double hnorm = sqrt(p1.x), xnorm = sqrt(p1.y), pred = 0.5 * p2.x;
         double Fn;
-        { QSB_PROF_BEGIN(); Fn = qsb_cta_half_norm<NQ>(prog, xn, a.target, trig, part, &tr); QSB_PROF_END(4); }  // trig now belongs to xn
+        { QSB_PROF_BEGIN(); Fn = qsb_cta_half_norm<NQ>(prog, xn, a.target, trig, gtab, part, &tr); QSB_PROF_END(4); }  // trig now belongs to xn
         const double dF = F - Fn;
         const double rho = (pred > 0.0) ? dF / pred : -1.0;
         if (rho > 1e-4 && Fn == Fn) {
@@ -577,7 +580,7 @@ QSB_GLOBAL __launch_bounds__(QSB_LM_WARPS * 32) qsb_k_lm2(QsbSolveArgs a) {
           if (conv_f) { status = 2; break; }
           if (conv_x) { status = 3; break; }
           if (iters >= max_iters) { status = 0; break; }
-          { QSB_PROF_BEGIN(); qsb_cta_jac<NQ>(prog, a.target, trig, seg, rank, Rg); qsb_cluster_sync(); QSB_PROF_END(0); }
+          { QSB_PROF_BEGIN(); qsb_cta_jac<NQ>(prog, a.target, gtab, seg, rank, Rg); qsb_cluster_sync(); QSB_PROF_END(0); }
           ++iters;
           { QSB_PROF_BEGIN(); qsb_syrk_dmma(Rg, rows, M, A, cwarp, cwarps, lane); qsb_cluster_sync(); QSB_PROF_END(1); }
           for (int k = threadIdx.x; k < P; k += blockDim.x) {
@@ -597,7 +600,7 @@ QSB_GLOBAL __launch_bounds__(QSB_LM_WARPS * 32) qsb_k_lm2(QsbSolveArgs a) {
       }
     }
     // final distance 1 - |Tr(U T^dagger)| / N at x   (comparison.matrix_distance_squared, comparison.py:8-22)
-    qsb_cta_half_norm<NQ>(prog, x, a.target, trig, part, &tr);
+    qsb_cta_half_norm<NQ>(prog, x, a.target, trig, gtab, part, &tr);
     double* ox = a.out_x + a.param_off[inst];
     for (int k = threadIdx.x; k < P; k += blockDim.x) ox[k] = x[k];
     if (a.prof && threadIdx.x == 0) atomicAdd((unsigned long long*)&a.prof[5], (unsigned long long)iters);
@@ -610,8 +613,8 @@ QSB_GLOBAL __launch_bounds__(QSB_LM_WARPS * 32) qsb_k_lm2(QsbSolveArgs a) {
   }
 }
 
-static inline size_t qsb_lm2_smem_bytes(int max_params, bool chol_smem) {
-  const size_t base = 32 * 16 + (size_t)9 * max_params * 8 + 16 * 8 + 72 * 4 + 64;
+static inline size_t qsb_lm2_smem_bytes(int max_ops, int max_params, bool chol_smem) {
+  const size_t base = 32 * 16 + (size_t)9 * max_params * 8 + 16 * 8 + (size_t)64 * (max_ops + max_params) + 72 * 4 + 80;
   const size_t packed = ((size_t)(max_params + 1) * (max_params + 2) / 2 + QSB_CH_NB + 2) * 8;
   return base + (chol_smem ? packed : sizeof(QsbCholSmem));
 }

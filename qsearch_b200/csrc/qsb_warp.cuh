@@ -181,15 +181,23 @@ QSB_DEVICE void qsb_dmma_product(double (&cr)[TT][TT][2], double (&ci)[TT][TT][2
       yi[nt] = fma(cb.x, pi, fma(cb.y, pr, fma(ca.x, xi, ca.y * xr)));
       ny[nt] = -yi[nt];
     }
+    // term by term over all tiles: two DMMAs into the same accumulator are 2 TT^2 instructions apart
 #pragma unroll
     for (int nt = 0; nt < TT; ++nt)
 #pragma unroll
-      for (int mt = 0; mt < TT; ++mt) {
-        qsb_dmma884(cr[mt][nt][0], cr[mt][nt][1], S.re[ks][mt], yr[nt]);
-        qsb_dmma884(ci[mt][nt][0], ci[mt][nt][1], S.re[ks][mt], yi[nt]);
-        qsb_dmma884(cr[mt][nt][0], cr[mt][nt][1], S.im[ks][mt], ny[nt]);
-        qsb_dmma884(ci[mt][nt][0], ci[mt][nt][1], S.im[ks][mt], yr[nt]);
-      }
+      for (int mt = 0; mt < TT; ++mt) qsb_dmma884(cr[mt][nt][0], cr[mt][nt][1], S.re[ks][mt], yr[nt]);
+#pragma unroll
+    for (int nt = 0; nt < TT; ++nt)
+#pragma unroll
+      for (int mt = 0; mt < TT; ++mt) qsb_dmma884(ci[mt][nt][0], ci[mt][nt][1], S.re[ks][mt], yi[nt]);
+#pragma unroll
+    for (int nt = 0; nt < TT; ++nt)
+#pragma unroll
+      for (int mt = 0; mt < TT; ++mt) qsb_dmma884(cr[mt][nt][0], cr[mt][nt][1], S.im[ks][mt], ny[nt]);
+#pragma unroll
+    for (int nt = 0; nt < TT; ++nt)
+#pragma unroll
+      for (int mt = 0; mt < TT; ++mt) qsb_dmma884(ci[mt][nt][0], ci[mt][nt][1], S.im[ks][mt], yr[nt]);
   }
 }
 
@@ -212,14 +220,30 @@ QSB_DEVICE void qsb_dagger2x2(cplx* g) {
 }
 QSB_DEVICE void qsb_transpose2x2(cplx* g) { const cplx t = g[1]; g[1] = g[2]; g[2] = t; }
 
-// the 2x2 of a one-qubit op; trig holds (cos, sin) of the scaled angle of every parameter, in parameter order
-QSB_DEVICE void qsb_warp_gate(const qsb_op& op, const double* trig, const double* consts, cplx* g) {
-  if (op.opcode == QSB_OP_CONST1) {
-    const double* c = consts + op.const_off;
-    g[0] = cmk(c[0], c[1]); g[1] = cmk(c[2], c[3]); g[2] = cmk(c[4], c[5]); g[3] = cmk(c[6], c[7]);
-  } else {
-    qsb_gate2x2(op.opcode, trig + 2 * op.param_off, 0, g);
+// Gate table: the 2x2 of every one-qubit op and of every parameter derivative of one instance, built once per
+// parameter vector by all cooperating threads (one (op, which) slot per thread and round) and then read as broadcast
+// shared-memory loads, instead of every lane rebuilding the same entries from the sin/cos table at every use.
+QSB_DEVICE void qsb_fill_gates(const QsbDevProgram& P, const double* trig, cplx* gtab, int tid, int nthreads) {
+  const int n_slots = P.n_ops + P.n_params;
+  for (int s = tid; s < n_slots; s += nthreads) {
+    const int code = P.slotmap[s];
+    if (code < 0) continue;
+    const qsb_op op = P.ops[code >> 2];
+    cplx g[4];
+    if (op.opcode == QSB_OP_CONST1) {
+      const double* c = P.consts + op.const_off;
+      g[0] = cmk(c[0], c[1]); g[1] = cmk(c[2], c[3]); g[2] = cmk(c[4], c[5]); g[3] = cmk(c[6], c[7]);
+    } else {
+      qsb_gate2x2(op.opcode, trig + 2 * op.param_off, code & 3, g);
+    }
+    gtab[4 * s] = g[0]; gtab[4 * s + 1] = g[1]; gtab[4 * s + 2] = g[2]; gtab[4 * s + 3] = g[3];
   }
+}
+
+// which = 0: the gate of op; which = 1 + k: its derivative with respect to its k-th parameter
+QSB_DEVICE void qsb_warp_gate(const qsb_op& op, const cplx* gtab, int which, cplx* g) {
+  const cplx* t = gtab + 4 * (op.reserved + which);
+  g[0] = t[0]; g[1] = t[1]; g[2] = t[2]; g[3] = t[3];
 }
 
 // (cos, sin) of the scaled angle of every parameter, in parameter order (one parameter per lane and round)
@@ -236,11 +260,11 @@ QSB_DEVICE void qsb_warp_trig(const QsbDevProgram& P, const double* x, double* t
 // One warp, one tile of one instance, ops [jb, je) of the program (the whole program: jb = 0, je = n_ops).
 // WHAT = QSB_RUN_MATJAC: out_u = U, out_j[k] = J_k, interleaved complex;
 // WHAT = QSB_RUN_RESID: out_u = r, out_j[k] = [Re K_k ; Im K_k] (see qsb_jac_instance in qsb_generic.cuh).
-// trig: (cos, sin) per parameter.  tile = warp-row * WR + warp-col of this warp's block.  A segment [jb, je) first
+// gtab: gate table of this parameter vector (qsb_fill_gates).  tile = warp-row * WR + warp-col of this warp's block.  A segment [jb, je) first
 // builds its own prefix X = g_{je-1} .. g_0 T^dagger and suffix S = g_{M-1} .. g_{je} with structured updates only,
 // so several warps can share the parameters of one instance without exchanging data (used by the LM solver).
 template <int NQ, int WHAT>
-QSB_DEVICE void qsb_warp_jac_range(const QsbDevProgram& P, const double* target, const double* trig, int tile, int lane,
+QSB_DEVICE void qsb_warp_jac_range(const QsbDevProgram& P, const double* target, const cplx* gtab, int tile, int lane,
                                    int jb, int je, double* out_u, double* out_j) {
   using G = QsbWarpGeom<NQ>;
   constexpr int N = G::N, NN = G::NN, KS = G::KS, TT = G::TT;
@@ -265,7 +289,7 @@ QSB_DEVICE void qsb_warp_jac_range(const QsbDevProgram& P, const double* target,
     const qsb_op op = P.ops[j];
     if (op.opcode == QSB_OP_CNOT) { qsb_cnot<NQ, TT>(X, op.q0, op.q1, lane); continue; }
     cplx m[4];
-    qsb_warp_gate(op, trig, P.consts, m);
+    qsb_warp_gate(op, gtab, 0, m);
     qsb_mix<NQ, TT>(X, op.q0, m, lane);
   }
   // suffix of a segment that does not end at the last op: S <- S g_j for j = M-1 .. je
@@ -273,7 +297,7 @@ QSB_DEVICE void qsb_warp_jac_range(const QsbDevProgram& P, const double* target,
     const qsb_op op = P.ops[j];
     if (op.opcode == QSB_OP_CNOT) { qsb_cnot<NQ, TT>(S, op.q0, op.q1, lane); continue; }
     cplx m[4];
-    qsb_warp_gate(op, trig, P.consts, m);
+    qsb_warp_gate(op, gtab, 0, m);
     qsb_transpose2x2(m);
     qsb_mix<NQ, TT>(S, op.q0, m, lane);
   }
@@ -299,7 +323,7 @@ QSB_DEVICE void qsb_warp_jac_range(const QsbDevProgram& P, const double* target,
     const int np = qsb_num_params(op.opcode);
     if (np == 0 && j == jb) break;
     cplx m[4];
-    qsb_warp_gate(op, trig, P.consts, m);
+    qsb_warp_gate(op, gtab, 0, m);
     {
       cplx md[4] = {m[0], m[1], m[2], m[3]};
       qsb_dagger2x2(md);
@@ -307,7 +331,7 @@ QSB_DEVICE void qsb_warp_jac_range(const QsbDevProgram& P, const double* target,
     }
     for (int k = 0; k < np; ++k) {
       cplx dg[4];
-      qsb_gate2x2(op.opcode, trig + 2 * op.param_off, 1 + k, dg);
+      qsb_warp_gate(op, gtab, 1 + k, dg);
       double cr[TT][TT][2], ci[TT][TT][2];
       qsb_product<NQ, TT>(cr, ci, S, X, op.q0, dg, lane);
       double* o = out_j + (size_t)(op.param_off + k) * 2 * NN;
@@ -333,10 +357,12 @@ QSB_DEVICE void qsb_warp_jac_range(const QsbDevProgram& P, const double* target,
 }
 
 template <int NQ, int WHAT>
-QSB_DEVICE void qsb_warp_jac(const QsbDevProgram& P, const double* x, const double* target, double* trig, int tile,
-                             int lane, double* out_u, double* out_j) {
+QSB_DEVICE void qsb_warp_jac(const QsbDevProgram& P, const double* x, const double* target, double* trig, cplx* gtab,
+                             int tile, int lane, double* out_u, double* out_j) {
   qsb_warp_trig(P, x, trig, lane);
-  qsb_warp_jac_range<NQ, WHAT>(P, target, trig, tile, lane, 0, P.n_ops, out_u, out_j);
+  qsb_fill_gates(P, trig, gtab, lane, 32);
+  __syncwarp();
+  qsb_warp_jac_range<NQ, WHAT>(P, target, gtab, tile, lane, 0, P.n_ops, out_u, out_j);
 }
 
 template <int NQ, int WHAT>
@@ -345,14 +371,17 @@ QSB_GLOBAL __launch_bounds__(128) qsb_k_warp_jac(QsbBatchArgs a) {
   constexpr int NN = G::NN;
   QSB_DYN_SMEM(smem_raw);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpb = blockDim.x >> 5;
-  double* trig = (double*)smem_raw + (size_t)warp * 2 * a.max_params;
+  // per warp: gate table [max_ops + max_params][4] complex, then the sin/cos table [2 max_params]
+  const size_t per_warp = (size_t)8 * (a.max_ops + a.max_params) + 2 * a.max_params;
+  cplx* gtab = (cplx*)((double*)smem_raw + (size_t)warp * per_warp);
+  double* trig = (double*)(gtab + (size_t)4 * (a.max_ops + a.max_params));
   const long long p_base = a.param_off[a.first];
   const long long items = (long long)a.count * G::WARPS;
   for (long long it = (long long)blockIdx.x * wpb + warp; it < items; it += (long long)gridDim.x * wpb) {
     const int li = (int)(it / G::WARPS), tile = (int)(it % G::WARPS);
     const int inst = a.first + li;
     const QsbDevProgram P = a.progs[a.prog_idx[inst]];
-    qsb_warp_jac<NQ, WHAT>(P, a.params + a.param_off[inst], a.target, trig, tile, lane,
+    qsb_warp_jac<NQ, WHAT>(P, a.params + a.param_off[inst], a.target, trig, gtab, tile, lane,
                            a.out_a + (size_t)li * 2 * NN, a.out_b + (size_t)(a.param_off[inst] - p_base) * 2 * NN);
   }
 }

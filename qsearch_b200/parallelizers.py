@@ -9,8 +9,17 @@ It runs in-process: no fork after CUDA initialisation (hard
 from . import _lib
 
 
+SM_PER_DEVICE = 148      # B200
+SMS_PER_INSTANCE = 4     # leave a few SMs per (child, start) instance for the solver's thread-block clusters
+MAX_BEAMS = 8
+
+
 def default_num_tasks(opts):
-    """beams = num_tasks // branching_factor (compiler.py:89-93): one beam per visible GPU by default."""
+    """The reference sets num_tasks = number of worker processes and derives beams = num_tasks // branching_factor
+    (parallelizers.py:74, compiler.py:89-93), i.e. it pops as many nodes per expansion as its workers can solve
+    concurrently.  The GPU equivalent of "workers" is SMs: one expansion should fill the visible GPUs with
+    beams x branching x starts instances at a few SMs each (measured on QFT5/Yorktown: 6 beams x 6 children finish
+    in 157 s where 1 beam x 4 starts does not finish in 400 s, profiles/r1/k_qft5_qft4_beams_vs_starts.log)."""
     import math
     try:
         ndev = _lib.get_library().num_devices
@@ -21,7 +30,13 @@ def default_num_tasks(opts):
         bf = max(1, opts.gateset.branching_factor(int(round(math.log2(opts.target.shape[0])))))
     except Exception:
         pass
-    return bf * max(1, ndev)
+    starts = 1
+    try:
+        starts = max(1, int(getattr(opts.solver, "starts", None) or getattr(opts.solver, "num_threads", 1)))
+    except Exception:
+        pass
+    beams = (ndev * SM_PER_DEVICE) // (SMS_PER_INSTANCE * bf * starts)
+    return bf * max(1, min(MAX_BEAMS, beams))
 
 
 class Parallelizer:

@@ -194,3 +194,24 @@ def test_tensor_core_lm_matches_interpreter_lm(lib, monkeypatch):
     x2, f2, it2, st2 = lib2.solve("lm", [gp], poi, x0, T)
     assert f1.min() < 1e-10 and f2.min() < 1e-10
     assert np.abs(f1 - f2).max() < 1e-9
+
+
+def test_two_devices_shard_one_batch():
+    """One context over two GPUs: the library splits the batch into contiguous shards, results are identical."""
+    import ctypes
+    one = _lib.Library(devices=[0])
+    n = ctypes.c_int()
+    one.check(one.dll.qsb_device_count(ctypes.byref(n)))
+    if n.value < 2:
+        pytest.skip("needs two GPUs")
+    two = _lib.Library(devices=[0, 1])
+    circuits, params, targets = workloads.microbench_workload(4, 3, 7)
+    gps = [lowering.lower(c) for c in circuits]
+    poi = np.repeat(np.arange(3, dtype="int32"), 7)
+    flat = params.reshape(len(poi), -1)
+    a = one.eval_residuals_jac(gps, poi, flat, targets["qft"]) + one.eval_hs_grad(gps, poi, flat, targets["qft"])
+    b = two.eval_residuals_jac(gps, poi, flat, targets["qft"]) + two.eval_hs_grad(gps, poi, flat, targets["qft"])
+    for x, y in zip(a, b):
+        assert np.array_equal(x, y)
+    for x, y in zip(one.solve("lm", gps, poi, flat, targets["qft"]), two.solve("lm", gps, poi, flat, targets["qft"])):
+        assert np.allclose(x, y, atol=1e-9)

@@ -39,6 +39,7 @@ def main():
     ap.add_argument("--solver", default="lm")
     ap.add_argument("--min-depth", type=int, default=3)
     ap.add_argument("--timeout", type=float, default=600)
+    ap.add_argument("--beams", type=int, default=-1)
     a = ap.parse_args()
     lib = _lib.get_library()
     print("library:", lib.version(), "devices:", lib.num_devices, flush=True)
@@ -48,6 +49,8 @@ def main():
         for rep in range(a.reps):
             solver = solvers.LeastSquares_Jac_Solver(starts=a.starts) if a.solver == "lm" else solvers.BFGS_Jac_Solver(starts=a.starts)
             opts = q.Options(target=T, gateset=mk_gs(), solver=solver, seed=1000 + rep, timeout=a.timeout)
+            if a.beams > 0:
+                opts.beams = a.beams
             if kind == "leap":
                 opts.min_depth = a.min_depth
             comp = q.LeapCompiler() if kind == "leap" else q.SearchCompiler()
@@ -55,7 +58,7 @@ def main():
             t0 = time.perf_counter()
             res = comp.compile(opts)
             dt = time.perf_counter() - t0
-            print(json.dumps({"case": name, "rep": rep, "solver": a.solver, "starts": a.starts, "wall_s": round(dt, 3),
+            print(json.dumps({"case": name, "rep": rep, "solver": a.solver, "starts": a.starts, "beams": a.beams, "wall_s": round(dt, 3),
                               "cnots": repr(res["structure"]).count("CNOTGate"), "distance": float(res["distance"]),
                               "stats": res["stats"], "launches": lib.launch_count() - l0}), flush=True)
 
