@@ -5,6 +5,7 @@
 #include "qsb_host.h"
 #include "qsb_generic.cuh"
 #include "qsb_warp.cuh"
+#include "qsb_hs_warp.cuh"
 
 struct QsbLaunchShape {
   int threads;
@@ -110,11 +111,35 @@ static int qsb_launch_warp_kernel(const QsbBatchArgs& args, cudaStream_t st, int
 }
 
 static inline bool qsb_warp_path(const qsb_batch* b, int what) {
-  return b->fast_ok && !b->force_generic && b->n_qubits >= 3 && (what == QSB_RUN_MATJAC || what == QSB_RUN_RESID);
+  return b->fast_ok && !b->force_generic && b->n_qubits >= 3 &&
+         (what == QSB_RUN_MATJAC || what == QSB_RUN_RESID || what == QSB_RUN_HS);
+}
+
+template <int NQ>
+static int qsb_launch_warp_hs(const QsbBatchArgs& args, cudaStream_t st, int sm_count) {
+  constexpr int threads = 128, ipc = QsbHsGeom<NQ>::IPC;
+  size_t slot = qsb_hs_slot_doubles(NQ, args.max_ops, args.max_params);
+  slot = (slot + 1) & ~(size_t)1;
+  const size_t smem = ipc * slot * sizeof(double) + 16;
+  if (smem > 200 * 1024) return qsb_fail(QSB_ERR_UNSUPPORTED, "program too long for the warp HS kernel");
+  int rc = qsb_prepare_kernel(qsb_k_warp_hs<NQ>, smem);
+  if (rc) return rc;
+  const int want = (args.count + ipc - 1) / ipc;
+  const int resident = sm_count * qsb_resident_ctas(qsb_k_warp_hs<NQ>, threads, smem);
+  QSB_LAUNCH((qsb_k_warp_hs<NQ>), std::max(1, std::min(want, resident)), threads, smem, st, args);
+  QSB_CUDA(cudaGetLastError());
+  return QSB_OK;
 }
 
 static inline int qsb_launch(qsb_batch* b, int what, const QsbBatchArgs& args, cudaStream_t st, int sm_count) {
   if (!qsb_warp_path(b, what)) return qsb_launch_generic(b, what, args, st, sm_count);
+  if (what == QSB_RUN_HS) {
+    switch (b->n_qubits) {
+      case 3: return qsb_launch_warp_hs<3>(args, st, sm_count);
+      case 4: return qsb_launch_warp_hs<4>(args, st, sm_count);
+      default: return qsb_launch_warp_hs<5>(args, st, sm_count);
+    }
+  }
   const bool mj = what == QSB_RUN_MATJAC;
   switch (b->n_qubits) {
     case 3: return mj ? qsb_launch_warp_kernel<3, QSB_RUN_MATJAC>(args, st, sm_count) : qsb_launch_warp_kernel<3, QSB_RUN_RESID>(args, st, sm_count);

@@ -345,9 +345,19 @@ QSB_DEVICE bool qsb_chol_packed(const double* A, int rows, const double* d2, dou
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
   const int g = lane >> 2, t = lane & 3;
   __syncthreads();
-  for (int e = threadIdx.x; e < rows * rows; e += blockDim.x) {
-    const int i = e / rows, j = e - i * rows;
-    if (j <= i) Ls[QSB_TRI(i, j)] = QSB_LDCG(A + e) + ((i == j && i < P) ? mu * d2[i] : 0.0);
+  // copy in the lower triangle, one row per warp and round; a row's loads (<= 9 per lane) are all issued before the
+  // first store, so the L2 latency is paid once per row, not once per element
+  for (int i = warp; i < rows; i += nwarps) {
+    const double* ar = A + (size_t)i * rows;
+    double* lr = Ls + QSB_TRI(i, 0);
+    double v[9];
+#pragma unroll
+    for (int m = 0; m < 9; ++m) { const int j = lane + 32 * m; v[m] = (j <= i) ? QSB_LDCG(ar + j) : 0.0; }
+#pragma unroll
+    for (int m = 0; m < 9; ++m) {
+      const int j = lane + 32 * m;
+      if (j <= i) lr[j] = v[m] + ((j == i && i < P) ? mu * d2[i] : 0.0);
+    }
   }
   if (threadIdx.x == 0) *okflag = 1;
   __syncthreads();
@@ -493,8 +503,9 @@ QSB_GLOBAL __launch_bounds__(QSB_LM_WARPS * 32) qsb_k_lm2(QsbSolveArgs a) {
   double* part = trig + 2 * a.max_params;   // 16
   cplx* gtab = (cplx*)(part + 16 + (a.max_params & 1));  // [max_ops + max_params][4], 16-byte aligned
   int* seg = (int*)(gtab + (size_t)4 * (a.max_ops + a.max_params));  // cluster * NSEG + 1 (<= 72 ints)
-  QsbCholSmem* cs = (QsbCholSmem*)(seg + 72);          // global-memory factorisation (large P)
-  double* Ls = (double*)(seg + 72);                     // or: packed factor in shared memory (a.chol_smem)
+  qsb_op* sops = (qsb_op*)(seg + 72);                                 // the program's ops, staged once per instance
+  QsbCholSmem* cs = (QsbCholSmem*)(sops + a.max_ops);  // global-memory factorisation (large P)
+  double* Ls = (double*)(sops + a.max_ops);             // or: packed factor in shared memory (a.chol_smem)
   double* rinv = Ls + (size_t)(a.max_params + 1) * (a.max_params + 2) / 2;
   int* okflag = (int*)(rinv + QSB_CH_NB);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -505,8 +516,11 @@ QSB_GLOBAL __launch_bounds__(QSB_LM_WARPS * 32) qsb_k_lm2(QsbSolveArgs a) {
   const int cwarps = csize * QSB_LM_WARPS, cwarp = rank * QSB_LM_WARPS + warp;
   double* Rg = a.scratch + (size_t)cid * a.scratch_per_cta;
   for (int inst = cid; inst < a.count; inst += nclusters) {
-    const QsbDevProgram prog = a.progs[a.prog_idx[inst]];
+    QsbDevProgram prog = a.progs[a.prog_idx[inst]];
     const int P = prog.n_params, rows = P + 1;
+    __syncthreads();
+    for (int e = threadIdx.x; e < prog.n_ops * 6; e += blockDim.x) ((int32_t*)sops)[e] = ((const int32_t*)prog.ops)[e];
+    prog.ops = sops;  // every sweep of this solve reads the ops from shared memory
     double* A = Rg + (size_t)(a.max_params + 1) * M;
     double* L = A + (size_t)(a.max_params + 1) * (a.max_params + 1) + (size_t)rank * (a.max_params + 1) * (a.max_params + 1);
     const double* x0 = a.x0 + a.param_off[inst];
@@ -614,7 +628,7 @@ QSB_GLOBAL __launch_bounds__(QSB_LM_WARPS * 32) qsb_k_lm2(QsbSolveArgs a) {
 }
 
 static inline size_t qsb_lm2_smem_bytes(int max_ops, int max_params, bool chol_smem) {
-  const size_t base = 32 * 16 + (size_t)9 * max_params * 8 + 16 * 8 + (size_t)64 * (max_ops + max_params) + 72 * 4 + 80;
+  const size_t base = 32 * 16 + (size_t)9 * max_params * 8 + 16 * 8 + (size_t)64 * (max_ops + max_params) + 72 * 4 + (size_t)24 * max_ops + 88;
   const size_t packed = ((size_t)(max_params + 1) * (max_params + 2) / 2 + QSB_CH_NB + 2) * 8;
   return base + (chol_smem ? packed : sizeof(QsbCholSmem));
 }

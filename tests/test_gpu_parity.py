@@ -167,7 +167,7 @@ def test_warp_kernels_match_interpreter(lib, n):
         b.set_params(params.reshape(len(poi), -1))
         b.set_target(targets["haar"] if "haar" in targets else targets["qft"])
         res = []
-        for what in (_lib.RUN_MATJAC, _lib.RUN_RESID):
+        for what in (_lib.RUN_MATJAC, _lib.RUN_RESID, _lib.RUN_HS):
             b.run(what)
             res.extend(x for x in b.fetch() if x is not None)
         out[kind] = res
