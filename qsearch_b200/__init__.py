@@ -6,7 +6,7 @@ reference-shaped Backend / Solver / Parallelizer / Compiler classes on top of it
 does not touch CUDA (fork-safe); the library is loaded on first use and its absence is a hard error.
 """
 from . import unitaries, gates, gatesets, lowering, options, backends, objectives, solvers, parallelizers, heuristics  # noqa: F401
-from . import compiler, leap_compiler, defaults, utils  # noqa: F401
+from . import compiler, leap_compiler, defaults, utils, post_processing  # noqa: F401
 from .options import Options  # noqa: F401
 from .compiler import SearchCompiler  # noqa: F401
 from .leap_compiler import LeapCompiler  # noqa: F401

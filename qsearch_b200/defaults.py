@@ -18,6 +18,7 @@ standard_defaults = {
     "stdout_enabled": False,
     "log_file": None,
     "seed": None,
+    "reoptimize_size": 7,  # window of LEAPReoptimizing_PostProcessor as used by examples/leap_qft4.py:15
 }
 
 

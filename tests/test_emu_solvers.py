@@ -128,3 +128,24 @@ def test_tensor_core_lm_on_three_qubits(emu):
     assert f.min() < 1e-12
     for k, xk in enumerate(x.reshape(3, -1)):
         assert abs(O.matrix_distance_squared(T, O.matrix(c, xk)) - f[k]) < 1e-12
+
+
+def test_leap_reoptimizing_post_processor(emu):
+    """post_processing.py:108-295 on the batched solver: a deliberately padded 2-qubit LEAP-style result gets shorter
+    and still implements the target."""
+    from qsearch_b200 import post_processing
+    T = unitaries.qft(4)
+    g = gatesets.QubitCNOTLinear()
+    circ = gates.ProductGate(g.initial_layer(2))
+    for _ in range(6):  # qft(4) needs 3 CNOTs; build a 6-layer circuit and solve it
+        circ = circ.appending(g.search_layers(2)[0][0])
+    opts = q.Options(target=T, seed=4)
+    opts.set_defaults(**q.defaults.standard_defaults)
+    opts.set_smart_defaults(**q.defaults.standard_smart_defaults)
+    res = solvers.LeastSquares_Jac_Solver(starts=4).solve_batch([circ], opts)
+    assert res.distance[0] < 1e-10
+    padded = {"structure": circ, "parameters": res.x[0], "cut_depths": [0, 3, 6]}
+    out = post_processing.LEAPReoptimizing_PostProcessor().post_process_circuit(padded, q.Options(target=T, seed=4, reoptimize_size=4))
+    n_after = repr(out["structure"]).count("CNOTGate")
+    assert n_after < 6
+    assert O.matrix_distance_squared(T, O.matrix(out["structure"], out["parameters"])) < 1e-10

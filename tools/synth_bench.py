@@ -40,6 +40,7 @@ def main():
     ap.add_argument("--min-depth", type=int, default=3)
     ap.add_argument("--timeout", type=float, default=600)
     ap.add_argument("--beams", type=int, default=-1)
+    ap.add_argument("--reopt", type=int, default=0, help="run LEAPReoptimizing_PostProcessor with this window size on LEAP results")
     a = ap.parse_args()
     lib = _lib.get_library()
     print("library:", lib.version(), "devices:", lib.num_devices, flush=True)
@@ -58,9 +59,17 @@ def main():
             t0 = time.perf_counter()
             res = comp.compile(opts)
             dt = time.perf_counter() - t0
+            extra = {}
+            if kind == "leap" and a.reopt > 0:
+                t1 = time.perf_counter()
+                post = q.post_processing.LEAPReoptimizing_PostProcessor().post_process_circuit(
+                    res, opts.updated(reoptimize_size=a.reopt, timeout=a.timeout))
+                extra = {"reopt_window": a.reopt, "reopt_wall_s": round(time.perf_counter() - t1, 3),
+                         "cnots_before": repr(res["structure"]).count("CNOTGate"), "reopt_stats": post.get("stats")}
+                res = dict(res, structure=post["structure"], parameters=post["parameters"], distance=post.get("distance", res["distance"]))
             print(json.dumps({"case": name, "rep": rep, "solver": a.solver, "starts": a.starts, "beams": a.beams, "wall_s": round(dt, 3),
                               "cnots": repr(res["structure"]).count("CNOTGate"), "distance": float(res["distance"]),
-                              "stats": res["stats"], "launches": lib.launch_count() - l0}), flush=True)
+                              "stats": res["stats"], "launches": lib.launch_count() - l0, **extra}), flush=True)
 
 
 if __name__ == "__main__":
