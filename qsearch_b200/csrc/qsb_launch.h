@@ -82,6 +82,8 @@ static inline int qsb_launch_generic(qsb_batch* b, int what, const QsbBatchArgs&
 
 // ---------------------------------------------------------------------------- warp (register / DMMA) kernels
 // 4 warps per CTA, one instance tile per warp, grid = SMs x resident CTAs (persistent warps stride over the items).
+#define QSB_WARP_NOFIT 1  // internal: the program's tables do not fit the warp kernel's shared memory -> use the interpreter
+
 template <class K>
 static inline int qsb_resident_ctas(K kernel, int threads, size_t smem) {
 #ifdef QSB_EMU
@@ -98,7 +100,7 @@ template <int NQ, int WHAT>
 static int qsb_launch_warp_kernel(const QsbBatchArgs& args, cudaStream_t st, int sm_count) {
   constexpr int threads = 128, wpb = threads / 32;
   const size_t smem = (size_t)wpb * (8 * (size_t)(args.max_ops + args.max_params) + 2 * (size_t)args.max_params) * sizeof(double) + 16;
-  if (smem > 200 * 1024) return qsb_fail(QSB_ERR_UNSUPPORTED, "too many parameters for the warp kernels");
+  if (smem > 200 * 1024) return QSB_WARP_NOFIT;
   int rc = qsb_prepare_kernel(qsb_k_warp_jac<NQ, WHAT>, smem);
   if (rc) return rc;
   const long long items = (long long)args.count * QsbWarpGeom<NQ>::WARPS;
@@ -121,7 +123,7 @@ static int qsb_launch_warp_hs(const QsbBatchArgs& args, cudaStream_t st, int sm_
   size_t slot = qsb_hs_slot_doubles(NQ, args.max_ops, args.max_params);
   slot = (slot + 1) & ~(size_t)1;
   const size_t smem = ipc * slot * sizeof(double) + 16;
-  if (smem > 200 * 1024) return qsb_fail(QSB_ERR_UNSUPPORTED, "program too long for the warp HS kernel");
+  if (smem > 200 * 1024) return QSB_WARP_NOFIT;
   int rc = qsb_prepare_kernel(qsb_k_warp_hs<NQ>, smem);
   if (rc) return rc;
   const int want = (args.count + ipc - 1) / ipc;
@@ -131,8 +133,7 @@ static int qsb_launch_warp_hs(const QsbBatchArgs& args, cudaStream_t st, int sm_
   return QSB_OK;
 }
 
-static inline int qsb_launch(qsb_batch* b, int what, const QsbBatchArgs& args, cudaStream_t st, int sm_count) {
-  if (!qsb_warp_path(b, what)) return qsb_launch_generic(b, what, args, st, sm_count);
+static inline int qsb_launch_warp(qsb_batch* b, int what, const QsbBatchArgs& args, cudaStream_t st, int sm_count) {
   if (what == QSB_RUN_HS) {
     switch (b->n_qubits) {
       case 3: return qsb_launch_warp_hs<3>(args, st, sm_count);
@@ -146,4 +147,12 @@ static inline int qsb_launch(qsb_batch* b, int what, const QsbBatchArgs& args, c
     case 4: return mj ? qsb_launch_warp_kernel<4, QSB_RUN_MATJAC>(args, st, sm_count) : qsb_launch_warp_kernel<4, QSB_RUN_RESID>(args, st, sm_count);
     default: return mj ? qsb_launch_warp_kernel<5, QSB_RUN_MATJAC>(args, st, sm_count) : qsb_launch_warp_kernel<5, QSB_RUN_RESID>(args, st, sm_count);
   }
+}
+
+static inline int qsb_launch(qsb_batch* b, int what, const QsbBatchArgs& args, cudaStream_t st, int sm_count) {
+  if (qsb_warp_path(b, what)) {
+    const int rc = qsb_launch_warp(b, what, args, st, sm_count);
+    if (rc != QSB_WARP_NOFIT) return rc;
+  }
+  return qsb_launch_generic(b, what, args, st, sm_count);
 }

@@ -28,7 +28,7 @@ def main():
     circuits, params, targets = workloads.microbench_workload(a.qubits, n_circ, n_vec)
     gps = [lowering.lower(c) for c in circuits]
     poi = np.repeat(np.arange(n_circ, dtype="int32"), n_vec)
-    lib = _lib.Library(devices=[0])
+    lib = _lib.Library(path=os.environ.get("QSB_LIB_PATH"), devices=[0])  # QSB_LIB_PATH: A/B builds of the library
     b = lib.batch(gps, poi)
     b.set_params(params.reshape(len(poi), -1))
     b.set_target(targets["qft"])
