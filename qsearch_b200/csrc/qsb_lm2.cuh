@@ -340,7 +340,10 @@ QSB_DEVICE void qsb_chol_back(const double* Lb, int rows, int P, double* h) {
 // L2 round trips inside the factorisation.  Used whenever it fits (P <= ~220); otherwise qsb_chol_blocked.
 #define QSB_TRI(i, j) ((size_t)(i) * ((i) + 1) / 2 + (j))
 
-QSB_DEVICE bool qsb_chol_packed(const double* A, int rows, const double* d2, double mu, int P, double* Ls, double* rinv, double* rdiag, int* okflag) {
+QSB_DEVICE bool qsb_chol_packed(const double* A, int rows, const double* d2, double mu, int P, double* Ls, double* rinv, double* rdiag, int* okflag,
+                                long long* prof) {
+#define QSB_CH_T(slot) do { if (prof && threadIdx.x == 0) { const long long _n = QSB_CLOCK(); atomicAdd((unsigned long long*)&prof[slot], (unsigned long long)(_n - _tc)); _tc = _n; } } while (0)
+  long long _tc = prof ? QSB_CLOCK() : 0ll;
   constexpr int NB = QSB_CH_NB;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
   const int g = lane >> 2, t = lane & 3;
@@ -361,6 +364,7 @@ QSB_DEVICE bool qsb_chol_packed(const double* A, int rows, const double* d2, dou
   }
   if (threadIdx.x == 0) *okflag = 1;
   __syncthreads();
+  QSB_CH_T(6);
   for (int kb = 0; kb < P; kb += NB) {
     const int nbk = (P - kb < NB) ? P - kb : NB;
     if (warp == 0) {  // 1. diagonal block: lane = row, the row in registers, columns exchanged by shuffle
@@ -374,7 +378,7 @@ QSB_DEVICE bool qsb_chol_packed(const double* A, int rows, const double* d2, dou
         if (j < nbk) {
           const double piv = __shfl_sync(QSB_FULL, d[j], j);
           if (!(piv > 0.0) || !(piv < 1e300)) { good = false; break; }
-          const double sq = sqrt(piv), inv = 1.0 / sq;
+          const double inv = rsqrt(piv), sq = piv * inv;  // one reciprocal-square-root sequence instead of sqrt + divide
           if (lane == j) { rinv[j] = inv; rdiag[kb + j] = inv; }
           d[j] = (lane == j) ? sq : d[j] * inv;
 #pragma unroll
@@ -391,6 +395,7 @@ QSB_DEVICE bool qsb_chol_packed(const double* A, int rows, const double* d2, dou
       }
     }
     __syncthreads();
+    QSB_CH_T(7);
     if (!*okflag) { __syncthreads(); return false; }
     const int R0 = kb + nbk, nrow = rows - R0;
     for (int ri = threadIdx.x; ri < nrow; ri += blockDim.x) {  // 2. panel, one row per thread
@@ -411,6 +416,7 @@ QSB_DEVICE bool qsb_chol_packed(const double* A, int rows, const double* d2, dou
       }
     }
     __syncthreads();
+    QSB_CH_T(8);
     if (R0 < P) {  // 3. trailing update, 16x16 DMMA tiles of the lower triangle
       const int nbt = (nrow + 15) >> 4, ntasks = nbt * (nbt + 1) / 2;
       for (int task = warp; task < ntasks; task += nwarps) {
@@ -461,8 +467,10 @@ QSB_DEVICE bool qsb_chol_packed(const double* A, int rows, const double* d2, dou
       }
     }
     __syncthreads();
+    QSB_CH_T(9);
   }
   return true;
+#undef QSB_CH_T
 }
 
 // h = -(L^T)^{-1} y, y = row P of the packed factor.  One warp, column sweep: once h_j is known every lane folds it
@@ -559,7 +567,7 @@ QSB_GLOBAL __launch_bounds__(QSB_LM_WARPS * 32) qsb_k_lm2(QsbSolveArgs a) {
         bool chol_ok;
         {
           QSB_PROF_BEGIN();
-          chol_ok = a.chol_smem ? qsb_chol_packed(A, rows, d2, mu, P, Ls, rinv, wk, okflag) : qsb_chol_blocked(A, rows, d2, mu, P, L, cs);
+          chol_ok = a.chol_smem ? qsb_chol_packed(A, rows, d2, mu, P, Ls, rinv, wk, okflag, a.prof) : qsb_chol_blocked(A, rows, d2, mu, P, L, cs);
           QSB_PROF_END(2);
         }
         if (!chol_ok) {

@@ -30,7 +30,7 @@ struct QsbSolveArgs {
   int32_t* out_status;
   int cluster;      // qsb_k_lm2: CTAs per instance (thread-block cluster size; 1 in the interpreter kernels)
   int chol_smem;    // qsb_k_lm2: packed Cholesky factor in shared memory (fits) or in global scratch
-  long long* prof;  // optional [8] cycle counters (QSB_LM_PROFILE=1): jac, syrk, cholesky, solve, trial, iterations
+  long long* prof;  // optional [12] cycle counters (QSB_LM_PROFILE=1): jac, syrk, cholesky, solve, trial, iterations
 };
 
 QSB_DEVICE double qsb_block_max(double v, cplx* red) {

@@ -91,3 +91,35 @@ def test_emulated_warp_kernels_match_interpreter():
         for a, g in zip(out[0], out[1]):
             assert a.shape == g.shape and np.abs(a - g).max() < 1e-13
         assert any(not np.array_equal(a, g) for a, g in zip(out[0], out[1]))  # two different code paths did run
+
+
+def test_edge_cases_constants_empty_and_mixed_batches():
+    """Programs without parameters (constants + CNOT) through every entry point including the solvers, an empty
+    batch, and one ragged batch mixing three structures (one of them with a constant leaf and a ZXZXZ gate)."""
+    from oracle import qs_oracle as O
+    from qsearch_b200 import gates, gatesets, lowering, unitaries
+    lib = emulated_library()
+    c = gates.KroneckerGate(gates.SXGate(), gates.CNOTGate())
+    gp = lowering.lower(c)
+    assert gp.n_params == 0
+    Uo, T = O.matrix(c, []), unitaries.qft(8)
+    none = np.zeros(0)
+    assert np.abs(lib.eval_matrix([gp], [0], none)[0] - Uo).max() < 1e-15
+    U2, J = lib.eval_mat_jac([gp], [0], none)
+    assert np.abs(U2[0] - Uo).max() < 1e-15 and J.shape == (0, 8, 8)
+    r, Jr = lib.eval_residuals_jac([gp], [0], none, T)
+    f, g = lib.eval_hs_grad([gp], [0], none, T)
+    assert np.abs(r[0] - O.matrix_residuals(T, Uo)).max() < 1e-15 and Jr.shape == (0, 128) and g.shape == (0,)
+    assert abs(f[0] - O.matrix_distance_squared(T, Uo)) < 1e-15
+    for method in ("lm", "lbfgs"):
+        x, ff, it, st = lib.solve(method, [gp], [0], none, T)
+        assert x.size == 0 and abs(ff[0] - f[0]) < 1e-15
+    assert lib.eval_matrix([gp], np.zeros(0, dtype="int32"), none).shape == (0, 8, 8)
+    g4 = gatesets.QubitCNOTRing()
+    c1 = gates.ProductGate(g4.initial_layer(4))
+    c2 = c1.appending(g4.search_layers(4)[3][0])
+    c3 = gates.KroneckerGate(gates.SXGate(), gates.U3Gate(), gates.IdentityGate(), gates.ZXZXZGate())
+    rng = np.random.default_rng(0)
+    circuits, counts = [c1, c2, c3], (1, 2, 2)
+    assert _parity.check_against_oracle(lib, circuits, [rng.random((k, z.num_inputs)) * 2 * np.pi for k, z in zip(counts, circuits)],
+                                        unitaries.qft(16)) == 5
