@@ -248,6 +248,10 @@ def run_ours(args, rank, world, local_rank):
     for _ in range(2):
         batch.run(_lib.RUN_HS, timed=True)
     hs_ms = min(batch.run(_lib.RUN_HS, timed=True) for _ in range(3))
+    # LM-system form (r'r, J_r'r, J_r'J_r per instance; J_r stays in L2) on a quarter of the instances
+    n_sys = max(1, n_inst // 4)
+    batch.run(_lib.RUN_LMSYS, count=n_sys, timed=True)
+    sys_ms = min(batch.run(_lib.RUN_LMSYS, count=n_sys, timed=True) for _ in range(2))
     batch.close()
 
     # -- end to end through the host-buffer C-ABI call ------------------------------------------------------
@@ -302,6 +306,9 @@ def run_ours(args, rank, world, local_rank):
                              "bytes_per_eval": out_bytes / n_inst}},
         "hs_form": {"value": world * n_inst / (hs_ms * 1e-3), "unit": "evals/s", "ms_per_step": hs_ms,
                     "e2e_value": world * n_inst / t_hs_e2e, "algorithmic_flop_per_eval": flops_hs(n, G, P)},
+        "lm_system_form": {"value": world * n_sys / (sys_ms * 1e-3), "unit": "evals/s", "instances": n_sys,
+                           "what": "r'r, J_r'r, J_r'J_r per instance (QSB_RUN_LMSYS: DMMA Jacobian + DMMA SYRK, J_r never written to HBM)",
+                           "algorithmic_flop_per_eval": F + 2 * 2 * N * N * (P + 1) * (P + 1)},
         "parity_max_abs_err": worst,
     }
     if cpu is not None:

@@ -68,7 +68,8 @@ enum qsb_what {
   QSB_RUN_HS = 3,     /* f, grad f               (comparison.matrix_distance_squared_jac :37)           */
   QSB_RUN_RESID = 4,  /* r, J_r                  (comparison.matrix_residuals :57 / _residuals_jac :66) */
   QSB_RUN_DIST = 5,   /* f only                  (comparison.matrix_distance_squared :8)                */
-  QSB_RUN_LMSYS = 6   /* r'r, J_r'J_r, J_r'r     (what a Levenberg-Marquardt step consumes; J_r never stored) */
+  QSB_RUN_LMSYS = 6   /* r'r, J_r'J_r, J_r'r     (what a Levenberg-Marquardt step consumes; J_r stays in L2).
+                         Device-resident batches only; one-qubit-leaf + CNOT programs on 3..5 qubits. */
 };
 
 /* ---- context ------------------------------------------------------------------------------------------ */

@@ -11,6 +11,7 @@
 #include "qsb_host.h"
 #include "qsb_generic.cuh"
 #include "qsb_warp.cuh"
+#include "qsb_lm2.cuh"
 #include "qsb_launch.h"
 
 // ---------------------------------------------------------------------------- errors
@@ -295,7 +296,7 @@ extern "C" int qsb_batch_destroy(qsb_batch* b) {
   if (!b) return QSB_OK;
   cudaSetDevice(b->ctx->devs[b->slot].id);
   cudaStreamSynchronize(b->ctx->devs[b->slot].stream);
-  cudaFree(b->d_progs); cudaFree(b->d_prog_idx); cudaFree(b->d_param_off); cudaFree(b->d_params); cudaFree(b->d_target);
+  cudaFree(b->d_progs); cudaFree(b->d_prog_idx); cudaFree(b->d_param_off); cudaFree(b->d_sq_off); cudaFree(b->d_params); cudaFree(b->d_target);
   cudaFree(b->out_a.p); cudaFree(b->out_b.p); cudaFree(b->out_c.p); cudaFree(b->solver_scratch);
   delete b;
   return QSB_OK;
@@ -404,6 +405,48 @@ extern "C" int qsb_batch_fetch(qsb_batch* b, int what, double* a, double* bb, do
   return QSB_OK;
 }
 
+// QSB_RUN_LMSYS: tensor-core kernels only (one-qubit leaves + CNOT, 3..5 qubits)
+template <int NQ>
+static int qsb_launch_lmsys_nq(qsb_batch* b, const QsbBatchArgs& args, cudaStream_t st, int sm_count) {
+  const size_t NN = (size_t)1 << (2 * NQ), maxP = (size_t)args.max_params;
+  const size_t smem = qsb_lmsys_smem_bytes(args.max_ops, args.max_params);
+  if (smem > 200 * 1024) return qsb_fail(QSB_ERR_UNSUPPORTED, "program too long for QSB_RUN_LMSYS");
+  int rc = qsb_prepare_kernel(qsb_k_lmsys<NQ>, smem);
+  if (rc) return rc;
+  const int threads = QSB_LM_WARPS * 32;
+  const int grid = std::max(1, std::min(args.count, sm_count * qsb_resident_ctas(qsb_k_lmsys<NQ>, threads, smem)));
+  size_t per_cta = (maxP + 1) * 2 * NN + (maxP + 1) * (maxP + 1);
+  per_cta = (per_cta + 1) & ~(size_t)1;
+  const size_t need = (size_t)grid * per_cta * sizeof(double);
+  if (need > b->solver_scratch_bytes) {
+    if (b->solver_scratch) cudaFree(b->solver_scratch);
+    b->solver_scratch = nullptr; b->solver_scratch_bytes = 0;
+    if (cudaMalloc(&b->solver_scratch, need) != cudaSuccess) return qsb_fail(QSB_ERR_NOMEM, "device allocation of the LM-system scratch failed");
+    b->solver_scratch_bytes = need;
+  }
+  if (!b->d_sq_off) {
+    std::vector<long long> sq((size_t)b->n_instances + 1);
+    long long off = 0;
+    for (int i = 0; i < b->n_instances; ++i) { sq[i] = off; const long long p = b->param_off[i + 1] - b->param_off[i]; off += p * p; }
+    sq[b->n_instances] = off;
+    QSB_CUDA(cudaMalloc((void**)&b->d_sq_off, sizeof(long long) * sq.size()));
+    QSB_CUDA(cudaMemcpy(b->d_sq_off, sq.data(), sizeof(long long) * sq.size(), cudaMemcpyHostToDevice));
+  }
+  QSB_LAUNCH((qsb_k_lmsys<NQ>), grid, threads, smem, st, args, (double*)b->solver_scratch, per_cta, (const long long*)b->d_sq_off);
+  QSB_CUDA(cudaGetLastError());
+  return QSB_OK;
+}
+
+static int qsb_launch_lmsys(qsb_batch* b, const QsbBatchArgs& args, cudaStream_t st, int sm_count) {
+  if (!b->fast_ok || b->n_qubits < 3)
+    return qsb_fail(QSB_ERR_UNSUPPORTED, "QSB_RUN_LMSYS needs a one-qubit-leaf + CNOT program on 3..5 qubits");
+  switch (b->n_qubits) {
+    case 3: return qsb_launch_lmsys_nq<3>(b, args, st, sm_count);
+    case 4: return qsb_launch_lmsys_nq<4>(b, args, st, sm_count);
+    default: return qsb_launch_lmsys_nq<5>(b, args, st, sm_count);
+  }
+}
+
 int qsb_batch_enqueue(qsb_batch* b, int what, int first, int count) {
   const QsbDevice& d = b->ctx->devs[b->slot];
   QsbBatchArgs args;
@@ -411,7 +454,7 @@ int qsb_batch_enqueue(qsb_batch* b, int what, int first, int count) {
   args.target = b->d_target; args.first = first; args.count = count; args.max_ops = b->max_ops;
   args.max_params = std::max(1, b->max_params);
   args.out_a = (double*)b->out_a.p; args.out_b = (double*)b->out_b.p; args.out_c = (double*)b->out_c.p;
-  int rc = qsb_launch(b, what, args, d.stream, d.sm_count);
+  int rc = (what == QSB_RUN_LMSYS) ? qsb_launch_lmsys(b, args, d.stream, d.sm_count) : qsb_launch(b, what, args, d.stream, d.sm_count);
   if (rc == QSB_OK) {
     std::lock_guard<std::mutex> g(b->ctx->mu);
     b->ctx->launches += 1;

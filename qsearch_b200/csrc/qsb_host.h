@@ -50,6 +50,7 @@ struct qsb_batch {
   QsbDevProgram* d_progs = nullptr;
   int32_t* d_prog_idx = nullptr;
   long long* d_param_off = nullptr;
+  long long* d_sq_off = nullptr;     // prefix sums of P_i^2 (QSB_RUN_LMSYS output offsets), built on first use
   double* d_params = nullptr;
   double* d_target = nullptr;
   QsbBuf out_a, out_b, out_c;  // grown on demand

@@ -641,3 +641,46 @@ static inline size_t qsb_lm2_smem_bytes(int max_ops, int max_params, bool chol_s
   return base + (chol_smem ? packed : sizeof(QsbCholSmem));
 }
 
+
+// ---------------------------------------------------------------------------- QSB_RUN_LMSYS
+// What one Levenberg-Marquardt step consumes, for every instance of a batch: r^T r, g = J_r^T r and A = J_r^T J_r,
+// with J_r only ever written to a per-CTA slab that is immediately re-read by the SYRK (it stays in L2; nothing of
+// size 2 N^2 P goes to HBM or to the host).  One CTA of QSB_LM_WARPS warps per instance, same phases as qsb_k_lm2.
+// out_a[inst] = r^T r, out_b[param_off ..] = g, out_c[sum P_i^2 ..] = A (row-major P x P).
+template <int NQ>
+QSB_GLOBAL __launch_bounds__(QSB_LM_WARPS * 32) qsb_k_lmsys(QsbBatchArgs a, double* scratch, size_t scratch_per_cta,
+                                                            const long long* sq_off) {
+  using G = QsbWarpGeom<NQ>;
+  constexpr int M = 2 * G::NN, NSEG = QSB_LM_WARPS / G::WARPS;
+  QSB_DYN_SMEM(smem_raw);
+  double* trig = (double*)smem_raw;                       // 2 * maxP
+  double* part = trig + 2 * a.max_params;                 // 16
+  cplx* gtab = (cplx*)(part + 16);
+  int* seg = (int*)(gtab + (size_t)4 * (a.max_ops + a.max_params));
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  double* Rg = scratch + (size_t)blockIdx.x * scratch_per_cta;
+  const long long p_base = a.param_off[a.first], s_base = sq_off[a.first];
+  for (int li = blockIdx.x; li < a.count; li += gridDim.x) {
+    const int inst = a.first + li;
+    const QsbDevProgram prog = a.progs[a.prog_idx[inst]];
+    const int P = prog.n_params, rows = P + 1;
+    double* A = Rg + (size_t)(a.max_params + 1) * M;
+    __syncthreads();
+    qsb_cta_segments(prog, NSEG, seg);
+    cplx tr;
+    qsb_cta_half_norm<NQ>(prog, a.params + a.param_off[inst], a.target, trig, gtab, part, &tr);  // trig + gate table
+    qsb_cta_jac<NQ>(prog, a.target, gtab, seg, 0, Rg);
+    __syncthreads();
+    qsb_syrk_dmma(Rg, rows, M, A, warp, QSB_LM_WARPS, lane);
+    __syncthreads();
+    double* og = a.out_b + (a.param_off[inst] - p_base);
+    double* oA = a.out_c + (sq_off[inst] - s_base);
+    for (int k = threadIdx.x; k < P; k += blockDim.x) og[k] = A[(size_t)P * rows + k];
+    for (int e = threadIdx.x; e < P * P; e += blockDim.x) oA[e] = A[(size_t)(e / P) * rows + (e % P)];
+    if (threadIdx.x == 0) a.out_a[li] = A[(size_t)P * rows + P];
+  }
+}
+
+static inline size_t qsb_lmsys_smem_bytes(int max_ops, int max_params) {
+  return ((size_t)2 * max_params + 16 + 8 * (size_t)(max_ops + max_params)) * 8 + 16 * 4 + 64;
+}

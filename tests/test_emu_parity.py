@@ -123,3 +123,28 @@ def test_edge_cases_constants_empty_and_mixed_batches():
     circuits, counts = [c1, c2, c3], (1, 2, 2)
     assert _parity.check_against_oracle(lib, circuits, [rng.random((k, z.num_inputs)) * 2 * np.pi for k, z in zip(counts, circuits)],
                                         unitaries.qft(16)) == 5
+
+
+def test_lm_system_run_kind():
+    """QSB_RUN_LMSYS (r'r, J_r'r, J_r'J_r per instance, J_r never leaving the device) against the oracle."""
+    from oracle import qs_oracle as O
+    from qsearch_b200 import _lib, lowering, workloads
+    lib = emulated_library()
+    circuits, params, targets = workloads.microbench_workload(3, 2, 2, depth=3)
+    gps = [lowering.lower(c) for c in circuits]
+    poi = np.repeat(np.arange(2, dtype="int32"), 2)
+    T = targets["haar"]
+    b = lib.batch(gps, poi)
+    b.set_params(params.reshape(len(poi), -1))
+    b.set_target(T)
+    b.run(_lib.RUN_LMSYS)
+    rr, g, A = b.fetch()
+    b.close()
+    P = gps[0].n_params
+    for i in range(len(poi)):
+        x = params.reshape(len(poi), -1)[i]
+        U, J = O.mat_jac(circuits[poi[i]], x)
+        r, Jr = O.matrix_residuals(T, U), O.matrix_residuals_jac(T, U, J)
+        assert abs(rr[i] - r @ r) < 1e-12
+        assert np.abs(g[i * P:(i + 1) * P] - Jr.T @ r).max() < 1e-12
+        assert np.abs(A[i * P * P:(i + 1) * P * P].reshape(P, P) - Jr.T @ Jr).max() < 1e-12

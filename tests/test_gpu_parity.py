@@ -215,3 +215,26 @@ def test_two_devices_shard_one_batch():
         assert np.array_equal(x, y)
     for x, y in zip(one.solve("lm", gps, poi, flat, targets["qft"]), two.solve("lm", gps, poi, flat, targets["qft"])):
         assert np.allclose(x, y, atol=1e-9)
+
+
+@pytest.mark.parametrize("n", [3, 4, 5])
+def test_lm_system_run_kind(lib, n):
+    """QSB_RUN_LMSYS on the device: r'r, J_r'r and J_r'J_r per instance against the oracle."""
+    circuits, params, targets = workloads.microbench_workload(n, 3, 2, depth=5)
+    gps = [lowering.lower(c) for c in circuits]
+    poi = np.repeat(np.arange(3, dtype="int32"), 2)
+    T = targets["haar"]
+    flat = params.reshape(len(poi), -1)
+    b = lib.batch(gps, poi)
+    b.set_params(flat)
+    b.set_target(T)
+    b.run(_lib.RUN_LMSYS)
+    rr, g, A = b.fetch()
+    b.close()
+    P = gps[0].n_params
+    for i in range(len(poi)):
+        U, J = O.mat_jac(circuits[poi[i]], flat[i])
+        r, Jr = O.matrix_residuals(T, U), O.matrix_residuals_jac(T, U, J)
+        assert abs(rr[i] - r @ r) < 1e-11
+        assert np.abs(g[i * P:(i + 1) * P] - Jr.T @ r).max() < 1e-11
+        assert np.abs(A[i * P * P:(i + 1) * P * P].reshape(P, P) - Jr.T @ Jr).max() < 1e-11
