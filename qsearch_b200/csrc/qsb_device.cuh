@@ -8,10 +8,12 @@
 #ifdef QSB_EMU
 // tests/emu/cuda_emu.h is force-included by the test build (g++ -include ...)
 #define QSB_DEVICE static inline
+#define QSB_HOST_DEVICE static inline
 #define QSB_GLOBAL static void
 #else
 #include <cuda_runtime.h>
 #define QSB_DEVICE __device__ __forceinline__
+#define QSB_HOST_DEVICE __host__ __device__ static inline
 #define QSB_GLOBAL __global__ void
 #define QSB_DYN_SMEM(name) extern __shared__ __align__(16) unsigned char name[]
 #define QSB_LAUNCH(kernel, grid, block, smem, stream, ...) kernel<<<(grid), (block), (smem), (stream)>>>(__VA_ARGS__)

@@ -99,7 +99,7 @@ static inline int qsb_resident_ctas(K kernel, int threads, size_t smem) {
 template <int NQ, int WHAT>
 static int qsb_launch_warp_kernel(const QsbBatchArgs& args, cudaStream_t st, int sm_count) {
   constexpr int threads = 128, wpb = threads / 32;
-  const size_t smem = (size_t)wpb * (8 * (size_t)(args.max_ops + args.max_params) + 2 * (size_t)args.max_params) * sizeof(double) + 16;
+  const size_t smem = (size_t)wpb * qsb_warp_jac_smem_doubles(args.max_ops, args.max_params) * sizeof(double) + 16;
   if (smem > 200 * 1024) return QSB_WARP_NOFIT;
   int rc = qsb_prepare_kernel(qsb_k_warp_jac<NQ, WHAT>, smem);
   if (rc) return rc;

@@ -136,7 +136,7 @@ QSB_DEVICE double qsb_cta_half_norm(const QsbDevProgram& P, const double* x, con
     trig[2 * p] = c; trig[2 * p + 1] = s;
   }
   __syncthreads();
-  qsb_fill_gates(P, trig, gtab, threadIdx.x, blockDim.x);
+  qsb_fill_gates(P, trig, gtab, threadIdx.x, blockDim.x, true);  // rank-one derivative slots: qsb_cta_jac reads this table
   __syncthreads();
   if (warp < NCB) {
     double n2; cplx tr;
@@ -169,13 +169,14 @@ QSB_DEVICE void qsb_cta_segments(const QsbDevProgram& P, int nseg, int* seg) {
 }
 
 // r -> row P of R, J_r -> rows 0..P-1 (R row-major [(P+1)][2 N^2]); gtab must hold the gate table of the current x
+// wtiles: QSB_LM_WARPS * QSB_WTILE_DOUBLES of shared memory (16-byte aligned)
 template <int NQ>
-QSB_DEVICE void qsb_cta_jac(const QsbDevProgram& P, const double* target, const cplx* gtab, const int* seg, int rank,
-                            double* R) {
+QSB_DEVICE void qsb_cta_jac(const QsbDevProgram& P, const double* target, const cplx* gtab, double* wtiles, const int* seg,
+                            int rank, double* R) {
   using G = QsbWarpGeom<NQ>;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int tile = warp % G::WARPS, s = rank * (QSB_LM_WARPS / G::WARPS) + warp / G::WARPS;
-  qsb_warp_jac_range<NQ, QSB_RUN_RESID>(P, target, gtab, tile, lane, seg[s], seg[s + 1],
+  qsb_warp_jac_range<NQ, QSB_RUN_RESID>(P, target, gtab, wtiles + (size_t)warp * QSB_WTILE_DOUBLES, tile, lane, seg[s], seg[s + 1],
                                         R + (size_t)P.n_params * 2 * G::NN, R);
 }
 
@@ -513,7 +514,9 @@ QSB_GLOBAL __launch_bounds__(QSB_LM_WARPS * 32) qsb_k_lm2(QsbSolveArgs a) {
   int* seg = (int*)(gtab + (size_t)4 * (a.max_ops + a.max_params));  // cluster * NSEG + 1 (<= 72 ints)
   qsb_op* sops = (qsb_op*)(seg + 72);                                 // the program's ops, staged once per instance
   QsbCholSmem* cs = (QsbCholSmem*)(sops + a.max_ops);  // global-memory factorisation (large P)
-  double* Ls = (double*)(sops + a.max_ops);             // or: packed factor in shared memory (a.chol_smem)
+  double* Ls = (double*)(sops + a.max_ops);             // or: packed factor in shared memory (a.chol_smem); during the
+                                                        // Jacobian phase the same bytes are the warps' W tiles
+  double* wtiles = (double*)(((uintptr_t)Ls + 15) & ~(uintptr_t)15);
   double* rinv = Ls + (size_t)(a.max_params + 1) * (a.max_params + 2) / 2;
   int* okflag = (int*)(rinv + QSB_CH_NB);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -540,7 +543,7 @@ QSB_GLOBAL __launch_bounds__(QSB_LM_WARPS * 32) qsb_k_lm2(QsbSolveArgs a) {
     cplx tr;
     double F = qsb_cta_half_norm<NQ>(prog, x, a.target, trig, gtab, part, &tr);  // also fills trig for x
     if (P > 0) {
-      { QSB_PROF_BEGIN(); qsb_cta_jac<NQ>(prog, a.target, gtab, seg, rank, Rg); qsb_cluster_sync(); QSB_PROF_END(0); }
+      { QSB_PROF_BEGIN(); qsb_cta_jac<NQ>(prog, a.target, gtab, wtiles, seg, rank, Rg); qsb_cluster_sync(); QSB_PROF_END(0); }
       iters = 1;
       { QSB_PROF_BEGIN(); qsb_syrk_dmma(Rg, rows, M, A, cwarp, cwarps, lane); qsb_cluster_sync(); QSB_PROF_END(1); }
       for (int k = threadIdx.x; k < P; k += blockDim.x) {
@@ -602,7 +605,7 @@ QSB_GLOBAL __launch_bounds__(QSB_LM_WARPS * 32) qsb_k_lm2(QsbSolveArgs a) {
           if (conv_f) { status = 2; break; }
           if (conv_x) { status = 3; break; }
           if (iters >= max_iters) { status = 0; break; }
-          { QSB_PROF_BEGIN(); qsb_cta_jac<NQ>(prog, a.target, gtab, seg, rank, Rg); qsb_cluster_sync(); QSB_PROF_END(0); }
+          { QSB_PROF_BEGIN(); qsb_cta_jac<NQ>(prog, a.target, gtab, wtiles, seg, rank, Rg); qsb_cluster_sync(); QSB_PROF_END(0); }
           ++iters;
           { QSB_PROF_BEGIN(); qsb_syrk_dmma(Rg, rows, M, A, cwarp, cwarps, lane); qsb_cluster_sync(); QSB_PROF_END(1); }
           for (int k = threadIdx.x; k < P; k += blockDim.x) {
@@ -638,7 +641,8 @@ QSB_GLOBAL __launch_bounds__(QSB_LM_WARPS * 32) qsb_k_lm2(QsbSolveArgs a) {
 static inline size_t qsb_lm2_smem_bytes(int max_ops, int max_params, bool chol_smem) {
   const size_t base = 32 * 16 + (size_t)9 * max_params * 8 + 16 * 8 + (size_t)64 * (max_ops + max_params) + 72 * 4 + (size_t)24 * max_ops + 88;
   const size_t packed = ((size_t)(max_params + 1) * (max_params + 2) / 2 + QSB_CH_NB + 2) * 8;
-  return base + (chol_smem ? packed : sizeof(QsbCholSmem));
+  const size_t wtiles = (size_t)QSB_LM_WARPS * QSB_WTILE_DOUBLES * 8 + 16;
+  return base + std::max(chol_smem ? packed : sizeof(QsbCholSmem), wtiles);
 }
 
 
@@ -656,7 +660,8 @@ QSB_GLOBAL __launch_bounds__(QSB_LM_WARPS * 32) qsb_k_lmsys(QsbBatchArgs a, doub
   double* trig = (double*)smem_raw;                       // 2 * maxP
   double* part = trig + 2 * a.max_params;                 // 16
   cplx* gtab = (cplx*)(part + 16);
-  int* seg = (int*)(gtab + (size_t)4 * (a.max_ops + a.max_params));
+  double* wtiles = (double*)(gtab + (size_t)4 * (a.max_ops + a.max_params));
+  int* seg = (int*)(wtiles + (size_t)QSB_LM_WARPS * QSB_WTILE_DOUBLES);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   double* Rg = scratch + (size_t)blockIdx.x * scratch_per_cta;
   const long long p_base = a.param_off[a.first], s_base = sq_off[a.first];
@@ -669,7 +674,7 @@ QSB_GLOBAL __launch_bounds__(QSB_LM_WARPS * 32) qsb_k_lmsys(QsbBatchArgs a, doub
     qsb_cta_segments(prog, NSEG, seg);
     cplx tr;
     qsb_cta_half_norm<NQ>(prog, a.params + a.param_off[inst], a.target, trig, gtab, part, &tr);  // trig + gate table
-    qsb_cta_jac<NQ>(prog, a.target, gtab, seg, 0, Rg);
+    qsb_cta_jac<NQ>(prog, a.target, gtab, wtiles, seg, 0, Rg);
     __syncthreads();
     qsb_syrk_dmma(Rg, rows, M, A, warp, QSB_LM_WARPS, lane);
     __syncthreads();
@@ -682,5 +687,5 @@ QSB_GLOBAL __launch_bounds__(QSB_LM_WARPS * 32) qsb_k_lmsys(QsbBatchArgs a, doub
 }
 
 static inline size_t qsb_lmsys_smem_bytes(int max_ops, int max_params) {
-  return ((size_t)2 * max_params + 16 + 8 * (size_t)(max_ops + max_params)) * 8 + 16 * 4 + 64;
+  return ((size_t)2 * max_params + 16 + 8 * (size_t)(max_ops + max_params) + (size_t)QSB_LM_WARPS * QSB_WTILE_DOUBLES) * 8 + 16 * 4 + 64;
 }

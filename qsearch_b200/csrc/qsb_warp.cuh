@@ -220,10 +220,49 @@ QSB_DEVICE void qsb_dagger2x2(cplx* g) {
 }
 QSB_DEVICE void qsb_transpose2x2(cplx* g) { const cplx t = g[1]; g[1] = g[2]; g[2] = t; }
 
+// ---------------------------------------------------------------------------- rank-one form of the derivatives
+// Every parameter derivative of the one-qubit leaves is  dg = c g + a b^T  with c = -i/2 (generator-type parameters:
+// g^dagger dg has the eigenvalues +-i/2) or c = 0 (phase-type parameters: dg is one row or one column of g times i).
+// Then  K = S (dg (x) I) X = c V + (S a)(b^T X),  V = S (g (x) I) X = U T^dagger the same for every parameter, and
+// (S a)[:, kappa] = a0 S[:, k0] + a1 S[:, k1],  (b^T X)[kappa, :] = b0 X[k0, :] + b1 X[k1, :]  contract over HALF
+// the index range (kappa = k without the bit of the gate's qubit): half the tensor-core work of a dense product.
+QSB_DEVICE bool qsb_deriv_has_v(int opcode, int k) {
+  switch (opcode) {
+    case QSB_OP_RX: case QSB_OP_RY: case QSB_OP_RZ: case QSB_OP_XZXZ: case QSB_OP_ZXZXZ: return true;
+    case QSB_OP_U3: return k == 0;
+    default: return false;  // U1, U2, U3 phi / lambda
+  }
+}
+
+// dg -> {rho, (row, has_v), b0, b1}: the remainder R = dg - c g is rank one up to rounding; factored around its largest
+// entry it is a b^T with b^T = the pivot row of R and a = (1, rho) (pivot row 0: row = 0) or (rho, 1) (row = 1)
+QSB_DEVICE void qsb_rank_one(const cplx* g, bool has_v, cplx* d) {
+  cplx r[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) r[i] = has_v ? cmk(d[i].x - 0.5 * g[i].y, d[i].y + 0.5 * g[i].x) : d[i];  // R = dg + (i/2) g
+  int piv = 0;
+  double best = -1.0;
+  cplx pv = r[0];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const double m = r[i].x * r[i].x + r[i].y * r[i].y;
+    if (m > best) { best = m; piv = i; pv = r[i]; }
+  }
+  const bool row1 = piv >= 2;                                                  // pivot row
+  const cplx ot = piv == 0 ? r[2] : piv == 1 ? r[3] : piv == 2 ? r[0] : r[1];  // same column, other row
+  const double inv = best > 0.0 ? 1.0 / best : 0.0;
+  const cplx ratio = cmk((ot.x * pv.x + ot.y * pv.y) * inv, (ot.y * pv.x - ot.x * pv.y) * inv);  // ot / pv
+  const cplx b0 = row1 ? r[2] : r[0], b1 = row1 ? r[3] : r[1];
+  d[0] = ratio; d[1] = cmk(row1 ? 1.0 : 0.0, has_v ? 1.0 : 0.0);
+  d[2] = b0; d[3] = b1;
+}
+
 // Gate table: the 2x2 of every one-qubit op and of every parameter derivative of one instance, built once per
 // parameter vector by all cooperating threads (one (op, which) slot per thread and round) and then read as broadcast
 // shared-memory loads, instead of every lane rebuilding the same entries from the sin/cos table at every use.
-QSB_DEVICE void qsb_fill_gates(const QsbDevProgram& P, const double* trig, cplx* gtab, int tid, int nthreads) {
+// rank1: derivative slots hold the rank-one form above (qsb_rank_one) instead of the 2x2 itself.
+QSB_DEVICE void qsb_fill_gates(const QsbDevProgram& P, const double* trig, cplx* gtab, int tid, int nthreads,
+                               bool rank1 = false) {
   const int n_slots = P.n_ops + P.n_params;
   for (int s = tid; s < n_slots; s += nthreads) {
     const int code = P.slotmap[s];
@@ -235,6 +274,11 @@ QSB_DEVICE void qsb_fill_gates(const QsbDevProgram& P, const double* trig, cplx*
       g[0] = cmk(c[0], c[1]); g[1] = cmk(c[2], c[3]); g[2] = cmk(c[4], c[5]); g[3] = cmk(c[6], c[7]);
     } else {
       qsb_gate2x2(op.opcode, trig + 2 * op.param_off, code & 3, g);
+      if (rank1 && (code & 3) != 0) {
+        cplx g0[4];
+        qsb_gate2x2(op.opcode, trig + 2 * op.param_off, 0, g0);
+        qsb_rank_one(g0, qsb_deriv_has_v(op.opcode, (code & 3) - 1), g);
+      }
     }
     gtab[4 * s] = g[0]; gtab[4 * s + 1] = g[1]; gtab[4 * s + 2] = g[2]; gtab[4 * s + 3] = g[3];
   }
@@ -257,112 +301,345 @@ QSB_DEVICE void qsb_warp_trig(const QsbDevProgram& P, const double* x, double* t
   __syncwarp();
 }
 
+// ---------------------------------------------------------------------------- dynamic layout of the contracted index
+// The contracted index k only has to be laid out the SAME way in X (rows) and S (columns), so the kernel is free to
+// move the bit of the qubit it is about to work on from a lane position (0..1) into a k-step position (>= 2), where the
+// partner element is in the same thread.  One exchange = one __shfl_xor of half the fragment; afterwards every mix, CNOT
+// and half-size product on that qubit is thread-local.  pos/log: nibble l of pos = physical bit of logical bit l,
+// nibble p of log = logical bit at physical bit p; mru/mru2: the k-step positions used last (not evicted).
+struct QsbKLayout {
+  unsigned pos, log;
+  int mru, mru2;
+};
+QSB_DEVICE int qsb_nib(unsigned w, int i) { return (int)((w >> (4 * i)) & 7u); }
+QSB_DEVICE unsigned qsb_nib_set(unsigned w, int i, int v) { return (w & ~(15u << (4 * i))) | ((unsigned)v << (4 * i)); }
+
+// exchange lane bit lbit with k-step bit KB of a fragment
+template <int KS, int TT, int KB>
+QSB_DEVICE void qsb_swap_bits(QsbFrag<KS, TT>& F, int lbit, int lane) {
+  const bool hi = (lane >> lbit) & 1;
+  const int mask = 1 << lbit;
+#pragma unroll
+  for (int ks = 0; ks < KS; ++ks) {
+    if (ks & KB) continue;
+#pragma unroll
+    for (int o = 0; o < TT; ++o) {
+      const double sr = hi ? F.re[ks][o] : F.re[ks | KB][o], si = hi ? F.im[ks][o] : F.im[ks | KB][o];
+      const double rr = __shfl_xor_sync(QSB_FULL, sr, mask), ri = __shfl_xor_sync(QSB_FULL, si, mask);
+      if (hi) { F.re[ks][o] = rr; F.im[ks][o] = ri; }
+      else { F.re[ks | KB][o] = rr; F.im[ks | KB][o] = ri; }
+    }
+  }
+}
+
+// make the logical bit lb a k-step bit of both fragments; returns its k-step mask (1, 2 or 4)
+template <int NQ, int TT, bool WITH_S>
+QSB_DEVICE int qsb_bring_in(QsbFrag<(1 << NQ) / 4, TT>& X, QsbFrag<(1 << NQ) / 4, TT>& S, QsbKLayout& L, int lb, int lane) {
+  constexpr int KS = (1 << NQ) / 4;
+  int p = qsb_nib(L.pos, lb);
+  if (p < 2) {
+    int v = 2;
+    if (NQ == 4) v = (L.mru == 2) ? 3 : 2;
+    if (NQ == 5) { while (v == L.mru || v == L.mru2) ++v; }
+    switch (v) {
+      case 2: qsb_swap_bits<KS, TT, 1>(X, p, lane); if (WITH_S) qsb_swap_bits<KS, TT, 1>(S, p, lane); break;
+      case 3: if (NQ >= 4) { qsb_swap_bits<KS, TT, (NQ >= 4 ? 2 : 1)>(X, p, lane); if (WITH_S) qsb_swap_bits<KS, TT, (NQ >= 4 ? 2 : 1)>(S, p, lane); } break;
+      default: if (NQ >= 5) { qsb_swap_bits<KS, TT, (NQ >= 5 ? 4 : 1)>(X, p, lane); if (WITH_S) qsb_swap_bits<KS, TT, (NQ >= 5 ? 4 : 1)>(S, p, lane); } break;
+    }
+    const int lv = qsb_nib(L.log, v);
+    L.pos = qsb_nib_set(qsb_nib_set(L.pos, lb, v), lv, p);
+    L.log = qsb_nib_set(qsb_nib_set(L.log, v, lb), p, lv);
+    p = v;
+  }
+  if (p != L.mru) { L.mru2 = L.mru; L.mru = p; }
+  return 1 << (p - 2);
+}
+
+template <int NQ, int TT>
+QSB_DEVICE void qsb_mix_slot(QsbFrag<(1 << NQ) / 4, TT>& F, int kb, const cplx* m) {
+  constexpr int KS = (1 << NQ) / 4;
+  switch (kb) {
+    case 1: qsb_mix_thread<KS, TT, 1>(F, m); break;
+    case 2: if (NQ >= 4) qsb_mix_thread<KS, TT, (NQ >= 4 ? 2 : 1)>(F, m); break;
+    default: if (NQ >= 5) qsb_mix_thread<KS, TT, (NQ >= 5 ? 4 : 1)>(F, m); break;
+  }
+}
+
+// CNOT whose target bit sits at k-step mask kb; the control bit at physical position cp (lane or k-step bit)
+template <int NQ, int TT>
+QSB_DEVICE void qsb_cnot_slot(QsbFrag<(1 << NQ) / 4, TT>& F, int kb, int cp, int lane) {
+  constexpr int KS = (1 << NQ) / 4;
+  switch (kb) {
+    case 1: qsb_cnot_thread<KS, TT, 1>(F, cp, lane); break;
+    case 2: if (NQ >= 4) qsb_cnot_thread<KS, TT, (NQ >= 4 ? 2 : 1)>(F, cp, lane); break;
+    default: if (NQ >= 5) qsb_cnot_thread<KS, TT, (NQ >= 5 ? 4 : 1)>(F, cp, lane); break;
+  }
+}
+
+// acc += (S a)(b^T X) over the half index range; ab = {rho, (row, has_v), b0, b1} as written by qsb_rank_one
+template <int KS, int TT, int KB>
+QSB_DEVICE void qsb_dmma_half(double (&cr)[TT][TT][2], double (&ci)[TT][TT][2], const QsbFrag<KS, TT>& S,
+                              const QsbFrag<KS, TT>& X, const cplx* ab) {
+  const cplx rho = ab[0], b0 = ab[2], b1 = ab[3];
+  const bool row1 = ab[1].x != 0.0;  // the same for the whole warp
+#pragma unroll
+  for (int ks = 0; ks < KS; ++ks) {
+    if (ks & KB) continue;
+    double sr[TT], si[TT], yr[TT], yi[TT];
+    if (row1) {  // a = (rho, 1)
+#pragma unroll
+      for (int o = 0; o < TT; ++o) {
+        sr[o] = fma(rho.x, S.re[ks][o], fma(-rho.y, S.im[ks][o], S.re[ks | KB][o]));
+        si[o] = fma(rho.x, S.im[ks][o], fma(rho.y, S.re[ks][o], S.im[ks | KB][o]));
+      }
+    } else {  // a = (1, rho)
+#pragma unroll
+      for (int o = 0; o < TT; ++o) {
+        sr[o] = fma(rho.x, S.re[ks | KB][o], fma(-rho.y, S.im[ks | KB][o], S.re[ks][o]));
+        si[o] = fma(rho.x, S.im[ks | KB][o], fma(rho.y, S.re[ks | KB][o], S.im[ks][o]));
+      }
+    }
+#pragma unroll
+    for (int o = 0; o < TT; ++o) {
+      yr[o] = fma(b1.x, X.re[ks | KB][o], fma(-b1.y, X.im[ks | KB][o], fma(b0.x, X.re[ks][o], -b0.y * X.im[ks][o])));
+      yi[o] = fma(b1.x, X.im[ks | KB][o], fma(b1.y, X.re[ks | KB][o], fma(b0.x, X.im[ks][o], b0.y * X.re[ks][o])));
+    }
+    // term by term over all tiles: two DMMAs into the same accumulator are 2 TT^2 instructions apart
+#pragma unroll
+    for (int nt = 0; nt < TT; ++nt)
+#pragma unroll
+      for (int mt = 0; mt < TT; ++mt) qsb_dmma884(cr[mt][nt][0], cr[mt][nt][1], sr[mt], yr[nt]);
+#pragma unroll
+    for (int nt = 0; nt < TT; ++nt)
+#pragma unroll
+      for (int mt = 0; mt < TT; ++mt) qsb_dmma884(ci[mt][nt][0], ci[mt][nt][1], sr[mt], yi[nt]);
+#pragma unroll
+    for (int nt = 0; nt < TT; ++nt)
+#pragma unroll
+      for (int mt = 0; mt < TT; ++mt) qsb_dmma884(cr[mt][nt][0], cr[mt][nt][1], si[mt], -yi[nt]);
+#pragma unroll
+    for (int nt = 0; nt < TT; ++nt)
+#pragma unroll
+      for (int mt = 0; mt < TT; ++mt) qsb_dmma884(ci[mt][nt][0], ci[mt][nt][1], si[mt], yr[nt]);
+  }
+}
+
+// V = S X (dense, all k-steps)
+template <int KS, int TT>
+QSB_DEVICE void qsb_dmma_full(double (&cr)[TT][TT][2], double (&ci)[TT][TT][2], const QsbFrag<KS, TT>& S,
+                              const QsbFrag<KS, TT>& X) {
+#pragma unroll
+  for (int a = 0; a < TT; ++a)
+#pragma unroll
+    for (int b = 0; b < TT; ++b) { cr[a][b][0] = cr[a][b][1] = ci[a][b][0] = ci[a][b][1] = 0.0; }
+#pragma unroll
+  for (int ks = 0; ks < KS; ++ks) {
+#pragma unroll
+    for (int nt = 0; nt < TT; ++nt)
+#pragma unroll
+      for (int mt = 0; mt < TT; ++mt) qsb_dmma884(cr[mt][nt][0], cr[mt][nt][1], S.re[ks][mt], X.re[ks][nt]);
+#pragma unroll
+    for (int nt = 0; nt < TT; ++nt)
+#pragma unroll
+      for (int mt = 0; mt < TT; ++mt) qsb_dmma884(ci[mt][nt][0], ci[mt][nt][1], S.re[ks][mt], X.im[ks][nt]);
+#pragma unroll
+    for (int nt = 0; nt < TT; ++nt)
+#pragma unroll
+      for (int mt = 0; mt < TT; ++mt) qsb_dmma884(cr[mt][nt][0], cr[mt][nt][1], S.im[ks][mt], -X.im[ks][nt]);
+#pragma unroll
+    for (int nt = 0; nt < TT; ++nt)
+#pragma unroll
+      for (int mt = 0; mt < TT; ++mt) qsb_dmma884(ci[mt][nt][0], ci[mt][nt][1], S.im[ks][mt], X.re[ks][nt]);
+  }
+}
+
+// One parameterised (or constant) one-qubit op of the backward sweep whose qubit sits at k-step bit KB:
+// X <- g^dagger X (peel), K_k = c V + (S a_k)(b_k^T X) for its parameters, S <- S g.
+template <int NQ, int WHAT, int KB>
+QSB_DEVICE void qsb_jac_op(QsbFrag<(1 << NQ) / 4, QsbWarpGeom<NQ>::TT>& X, QsbFrag<(1 << NQ) / 4, QsbWarpGeom<NQ>::TT>& S,
+                           const qsb_op& op, int np, const cplx* gtab, const double* wtile, int r0, int c0, int lane,
+                           bool update_s, double* oj) {
+  using G = QsbWarpGeom<NQ>;
+  constexpr int N = G::N, NN = G::NN, KS = G::KS, TT = G::TT;
+  const int g = lane >> 2, t = lane & 3;
+  cplx m[4];
+  qsb_warp_gate(op, gtab, 0, m);
+  {
+    cplx md[4] = {m[0], m[1], m[2], m[3]};
+    qsb_dagger2x2(md);
+    qsb_mix_thread<KS, TT, KB>(X, md);  // X = R_j T^dagger
+  }
+  for (int k = 0; k < np; ++k) {
+    double cr[TT][TT][2], ci[TT][TT][2];
+    const cplx* ab = gtab + 4 * (op.reserved + 1 + k);
+    if (ab[1].y != 0.0) {  // generator-type parameter: start from W = -i/2 V
+      const double2* w2 = reinterpret_cast<const double2*>(wtile);
+#pragma unroll
+      for (int mt = 0; mt < TT; ++mt)
+#pragma unroll
+        for (int nt = 0; nt < TT; ++nt) {
+          const int i = (mt * TT + nt) * 2;
+          const double2 a = w2[i * 32 + lane], b = w2[(i + 1) * 32 + lane];
+          cr[mt][nt][0] = a.x; cr[mt][nt][1] = a.y; ci[mt][nt][0] = b.x; ci[mt][nt][1] = b.y;
+        }
+    } else {
+#pragma unroll
+      for (int mt = 0; mt < TT; ++mt)
+#pragma unroll
+        for (int nt = 0; nt < TT; ++nt) { cr[mt][nt][0] = cr[mt][nt][1] = ci[mt][nt][0] = ci[mt][nt][1] = 0.0; }
+    }
+    qsb_dmma_half<KS, TT, KB>(cr, ci, S, X, ab);
+    double* o = oj + (size_t)k * 2 * NN;
+#pragma unroll
+    for (int mt = 0; mt < TT; ++mt)
+#pragma unroll
+      for (int nt = 0; nt < TT; ++nt) {
+        const int e = (r0 + 8 * mt + g) * N + c0 + 8 * nt + 2 * t;
+        if (WHAT == QSB_RUN_MATJAC) {
+          *reinterpret_cast<double2*>(o + 2 * e) = make_double2(cr[mt][nt][0], ci[mt][nt][0]);
+          *reinterpret_cast<double2*>(o + 2 * e + 2) = make_double2(cr[mt][nt][1], ci[mt][nt][1]);
+        } else {
+          *reinterpret_cast<double2*>(o + e) = make_double2(cr[mt][nt][0], cr[mt][nt][1]);
+          *reinterpret_cast<double2*>(o + NN + e) = make_double2(ci[mt][nt][0], ci[mt][nt][1]);
+        }
+      }
+  }
+  if (update_s) {
+    qsb_transpose2x2(m);
+    qsb_mix_thread<KS, TT, KB>(S, m);  // S <- S g_j
+  }
+}
+
+// doubles of per-warp shared memory qsb_warp_jac_range needs for W = -i/2 V (one C-fragment tile, re and im)
+#define QSB_WTILE_DOUBLES 512
+
 // One warp, one tile of one instance, ops [jb, je) of the program (the whole program: jb = 0, je = n_ops).
 // WHAT = QSB_RUN_MATJAC: out_u = U, out_j[k] = J_k, interleaved complex;
 // WHAT = QSB_RUN_RESID: out_u = r, out_j[k] = [Re K_k ; Im K_k] (see qsb_jac_instance in qsb_generic.cuh).
-// gtab: gate table of this parameter vector (qsb_fill_gates).  tile = warp-row * WR + warp-col of this warp's block.  A segment [jb, je) first
-// builds its own prefix X = g_{je-1} .. g_0 T^dagger and suffix S = g_{M-1} .. g_{je} with structured updates only,
-// so several warps can share the parameters of one instance without exchanging data (used by the LM solver).
+// gtab: gate table of this parameter vector (qsb_fill_gates with rank1 = true); wtile: QSB_WTILE_DOUBLES of this warp's
+// shared memory; tile = warp-row * WR + warp-col of this warp's block.  A segment [jb, je) first builds its own prefix
+// X = g_{je-1} .. g_0 T^dagger and suffix S = g_{M-1} .. g_{je} with structured updates only, so several warps can
+// share the parameters of one instance without exchanging data (used by the LM solver).  The segment that ends at the
+// last op writes out_u (every tile its own block of it).
 template <int NQ, int WHAT>
-QSB_DEVICE void qsb_warp_jac_range(const QsbDevProgram& P, const double* target, const cplx* gtab, int tile, int lane,
-                                   int jb, int je, double* out_u, double* out_j) {
+QSB_DEVICE void qsb_warp_jac_range(const QsbDevProgram& P, const double* target, const cplx* gtab, double* wtile, int tile,
+                                   int lane, int jb, int je, double* out_u, double* out_j) {
   using G = QsbWarpGeom<NQ>;
   constexpr int N = G::N, NN = G::NN, KS = G::KS, TT = G::TT;
   const int g = lane >> 2, t = lane & 3;
   const int r0 = (tile / G::WR) * 8 * TT, c0 = (tile % G::WR) * 8 * TT;
   QsbFrag<KS, TT> X, S;
+  QsbKLayout L;
+  L.pos = L.log = 0x43210u;
+  L.mru = -1; L.mru2 = -1;
 #pragma unroll
   for (int ks = 0; ks < KS; ++ks)
 #pragma unroll
     for (int o = 0; o < TT; ++o) {
-      const int k = 4 * ks + t, c = c0 + 8 * o + g, r = r0 + 8 * o + g;
+      const int k = 4 * ks + t, c = c0 + 8 * o + g;
       if (WHAT == QSB_RUN_RESID) {  // X = T^dagger
         const double2 tv = *reinterpret_cast<const double2*>(target + 2 * (c * N + k));
         X.re[ks][o] = tv.x; X.im[ks][o] = -tv.y;
       } else {
         X.re[ks][o] = (k == c) ? 1.0 : 0.0; X.im[ks][o] = 0.0;
       }
-      S.re[ks][o] = (k == r) ? 1.0 : 0.0; S.im[ks][o] = 0.0;
     }
-  // forward sweep: X <- g_j X for the ops below je
+  // forward sweep: X <- g_j X for the ops below je (S does not exist yet: only X is exchanged)
   for (int j = 0; j < je; ++j) {
     const qsb_op op = P.ops[j];
-    if (op.opcode == QSB_OP_CNOT) { qsb_cnot<NQ, TT>(X, op.q0, op.q1, lane); continue; }
+    if (op.opcode == QSB_OP_CNOT) {
+      const int kb = qsb_bring_in<NQ, TT, false>(X, S, L, NQ - 1 - op.q1, lane);
+      qsb_cnot_slot<NQ, TT>(X, kb, qsb_nib(L.pos, NQ - 1 - op.q0), lane);
+      continue;
+    }
     cplx m[4];
     qsb_warp_gate(op, gtab, 0, m);
-    qsb_mix<NQ, TT>(X, op.q0, m, lane);
+    const int kb = qsb_bring_in<NQ, TT, false>(X, S, L, NQ - 1 - op.q0, lane);
+    qsb_mix_slot<NQ, TT>(X, kb, m);
+  }
+  // S = the warp's row block of the identity in the layout the forward sweep left behind
+#pragma unroll
+  for (int ks = 0; ks < KS; ++ks) {
+    const int kp = 4 * ks + t;
+    int kl = 0;
+#pragma unroll
+    for (int b = 0; b < NQ; ++b) kl |= ((kp >> b) & 1) << qsb_nib(L.log, b);
+#pragma unroll
+    for (int o = 0; o < TT; ++o) { S.re[ks][o] = (kl == r0 + 8 * o + g) ? 1.0 : 0.0; S.im[ks][o] = 0.0; }
   }
   // suffix of a segment that does not end at the last op: S <- S g_j for j = M-1 .. je
   for (int j = P.n_ops - 1; j >= je; --j) {
     const qsb_op op = P.ops[j];
-    if (op.opcode == QSB_OP_CNOT) { qsb_cnot<NQ, TT>(S, op.q0, op.q1, lane); continue; }
+    if (op.opcode == QSB_OP_CNOT) {
+      const int kb = qsb_bring_in<NQ, TT, true>(X, S, L, NQ - 1 - op.q1, lane);
+      qsb_cnot_slot<NQ, TT>(S, kb, qsb_nib(L.pos, NQ - 1 - op.q0), lane);
+      continue;
+    }
     cplx m[4];
     qsb_warp_gate(op, gtab, 0, m);
     qsb_transpose2x2(m);
-    qsb_mix<NQ, TT>(S, op.q0, m, lane);
+    const int kb = qsb_bring_in<NQ, TT, true>(X, S, L, NQ - 1 - op.q0, lane);
+    qsb_mix_slot<NQ, TT>(S, kb, m);
   }
-  if (r0 == 0 && je == P.n_ops) {  // the warps of the first block row write U T^dagger (their column block of it)
+  {  // V = S X = U T^dagger (this warp's tile of it): output of the last segment, and W = -i/2 V for the derivatives
+    double vr[TT][TT][2], vi[TT][TT][2];
+    qsb_dmma_full<KS, TT>(vr, vi, S, X);
+    double2* w2 = reinterpret_cast<double2*>(wtile);
 #pragma unroll
-    for (int ks = 0; ks < KS; ++ks)
+    for (int mt = 0; mt < TT; ++mt)
 #pragma unroll
-      for (int o = 0; o < TT; ++o) {
-        const int k = 4 * ks + t, c = c0 + 8 * o + g, e = k * N + c;
-        if (WHAT == QSB_RUN_MATJAC) *reinterpret_cast<double2*>(out_u + 2 * e) = make_double2(X.re[ks][o], X.im[ks][o]);
-        else { out_u[e] = X.re[ks][o] - (k == c ? 1.0 : 0.0); out_u[NN + e] = X.im[ks][o]; }
+      for (int nt = 0; nt < TT; ++nt) {
+        const int i = (mt * TT + nt) * 2;
+        w2[i * 32 + lane] = make_double2(0.5 * vi[mt][nt][0], 0.5 * vi[mt][nt][1]);
+        w2[(i + 1) * 32 + lane] = make_double2(-0.5 * vr[mt][nt][0], -0.5 * vr[mt][nt][1]);
+        if (je == P.n_ops) {
+          const int r = r0 + 8 * mt + g, c = c0 + 8 * nt + 2 * t, e = r * N + c;
+          if (WHAT == QSB_RUN_MATJAC) {
+            *reinterpret_cast<double2*>(out_u + 2 * e) = make_double2(vr[mt][nt][0], vi[mt][nt][0]);
+            *reinterpret_cast<double2*>(out_u + 2 * e + 2) = make_double2(vr[mt][nt][1], vi[mt][nt][1]);
+          } else {
+            *reinterpret_cast<double2*>(out_u + e) = make_double2(vr[mt][nt][0] - (r == c ? 1.0 : 0.0), vr[mt][nt][1] - (r == c + 1 ? 1.0 : 0.0));
+            *reinterpret_cast<double2*>(out_u + NN + e) = make_double2(vi[mt][nt][0], vi[mt][nt][1]);
+          }
+        }
       }
+    __syncwarp();
   }
   // backward sweep over the segment
   for (int j = je - 1; j >= jb; --j) {
     const qsb_op op = P.ops[j];
     if (op.opcode == QSB_OP_CNOT) {
       if (j == jb) break;
-      qsb_cnot<NQ, TT>(X, op.q0, op.q1, lane);
-      qsb_cnot<NQ, TT>(S, op.q0, op.q1, lane);
+      const int kb = qsb_bring_in<NQ, TT, true>(X, S, L, NQ - 1 - op.q1, lane);
+      const int cp = qsb_nib(L.pos, NQ - 1 - op.q0);
+      qsb_cnot_slot<NQ, TT>(X, kb, cp, lane);
+      qsb_cnot_slot<NQ, TT>(S, kb, cp, lane);
       continue;
     }
     const int np = qsb_num_params(op.opcode);
     if (np == 0 && j == jb) break;
-    cplx m[4];
-    qsb_warp_gate(op, gtab, 0, m);
-    {
-      cplx md[4] = {m[0], m[1], m[2], m[3]};
-      qsb_dagger2x2(md);
-      qsb_mix<NQ, TT>(X, op.q0, md, lane);  // X = R_j T^dagger
-    }
-    for (int k = 0; k < np; ++k) {
-      cplx dg[4];
-      qsb_warp_gate(op, gtab, 1 + k, dg);
-      double cr[TT][TT][2], ci[TT][TT][2];
-      qsb_product<NQ, TT>(cr, ci, S, X, op.q0, dg, lane);
-      double* o = out_j + (size_t)(op.param_off + k) * 2 * NN;
-#pragma unroll
-      for (int mt = 0; mt < TT; ++mt)
-#pragma unroll
-        for (int nt = 0; nt < TT; ++nt) {
-          const int e = (r0 + 8 * mt + g) * N + c0 + 8 * nt + 2 * t;
-          if (WHAT == QSB_RUN_MATJAC) {
-            *reinterpret_cast<double2*>(o + 2 * e) = make_double2(cr[mt][nt][0], ci[mt][nt][0]);
-            *reinterpret_cast<double2*>(o + 2 * e + 2) = make_double2(cr[mt][nt][1], ci[mt][nt][1]);
-          } else {
-            *reinterpret_cast<double2*>(o + e) = make_double2(cr[mt][nt][0], cr[mt][nt][1]);
-            *reinterpret_cast<double2*>(o + NN + e) = make_double2(ci[mt][nt][0], ci[mt][nt][1]);
-          }
-        }
-    }
-    if (j > jb) {
-      qsb_transpose2x2(m);
-      qsb_mix<NQ, TT>(S, op.q0, m, lane);  // S <- S g_j
+    const int kb = qsb_bring_in<NQ, TT, true>(X, S, L, NQ - 1 - op.q0, lane);
+    double* oj = out_j + (size_t)op.param_off * 2 * NN;
+    switch (kb) {  // one dispatch per op: everything below is straight-line code for that k-step bit
+      case 1: qsb_jac_op<NQ, WHAT, 1>(X, S, op, np, gtab, wtile, r0, c0, lane, j > jb, oj); break;
+      case 2: if (NQ >= 4) qsb_jac_op<NQ, WHAT, (NQ >= 4 ? 2 : 1)>(X, S, op, np, gtab, wtile, r0, c0, lane, j > jb, oj); break;
+      default: if (NQ >= 5) qsb_jac_op<NQ, WHAT, (NQ >= 5 ? 4 : 1)>(X, S, op, np, gtab, wtile, r0, c0, lane, j > jb, oj); break;
     }
   }
 }
 
 template <int NQ, int WHAT>
 QSB_DEVICE void qsb_warp_jac(const QsbDevProgram& P, const double* x, const double* target, double* trig, cplx* gtab,
-                             int tile, int lane, double* out_u, double* out_j) {
+                             double* wtile, int tile, int lane, double* out_u, double* out_j) {
   qsb_warp_trig(P, x, trig, lane);
-  qsb_fill_gates(P, trig, gtab, lane, 32);
+  qsb_fill_gates(P, trig, gtab, lane, 32, true);
   __syncwarp();
-  qsb_warp_jac_range<NQ, WHAT>(P, target, gtab, tile, lane, 0, P.n_ops, out_u, out_j);
+  qsb_warp_jac_range<NQ, WHAT>(P, target, gtab, wtile, tile, lane, 0, P.n_ops, out_u, out_j);
+}
+
+// doubles of shared memory per warp of qsb_k_warp_jac
+QSB_HOST_DEVICE size_t qsb_warp_jac_smem_doubles(int max_ops, int max_params) {
+  return QSB_WTILE_DOUBLES + (size_t)8 * (max_ops + max_params) + 2 * (size_t)(max_params + (max_params & 1)) + 3 * (size_t)(max_ops + (max_ops & 1));
 }
 
 template <int NQ, int WHAT>
@@ -371,17 +648,29 @@ QSB_GLOBAL __launch_bounds__(128) qsb_k_warp_jac(QsbBatchArgs a) {
   constexpr int NN = G::NN;
   QSB_DYN_SMEM(smem_raw);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpb = blockDim.x >> 5;
-  // per warp: gate table [max_ops + max_params][4] complex, then the sin/cos table [2 max_params]
-  const size_t per_warp = (size_t)8 * (a.max_ops + a.max_params) + 2 * a.max_params;
-  cplx* gtab = (cplx*)((double*)smem_raw + (size_t)warp * per_warp);
+  // per warp: W tile, gate table [max_ops + max_params][4] complex, the sin/cos table [2 max_params], and the ops of the
+  // program the warp worked on last (every sweep decodes them; from shared memory that is a short-latency load)
+  const size_t per_warp = qsb_warp_jac_smem_doubles(a.max_ops, a.max_params);
+  double* wtile = (double*)smem_raw + (size_t)warp * per_warp;
+  cplx* gtab = (cplx*)(wtile + QSB_WTILE_DOUBLES);
   double* trig = (double*)(gtab + (size_t)4 * (a.max_ops + a.max_params));
+  qsb_op* sops = (qsb_op*)(trig + 2 * (size_t)(a.max_params + (a.max_params & 1)));
+  int staged = -1;
   const long long p_base = a.param_off[a.first];
   const long long items = (long long)a.count * G::WARPS;
   for (long long it = (long long)blockIdx.x * wpb + warp; it < items; it += (long long)gridDim.x * wpb) {
     const int li = (int)(it / G::WARPS), tile = (int)(it % G::WARPS);
     const int inst = a.first + li;
-    const QsbDevProgram P = a.progs[a.prog_idx[inst]];
-    qsb_warp_jac<NQ, WHAT>(P, a.params + a.param_off[inst], a.target, trig, gtab, tile, lane,
+    const int pi = a.prog_idx[inst];
+    QsbDevProgram P = a.progs[pi];
+    if (pi != staged) {
+      __syncwarp();
+      for (int e = lane; e < P.n_ops * 6; e += 32) ((int32_t*)sops)[e] = ((const int32_t*)P.ops)[e];
+      staged = pi;
+      __syncwarp();
+    }
+    P.ops = sops;
+    qsb_warp_jac<NQ, WHAT>(P, a.params + a.param_off[inst], a.target, trig, gtab, wtile, tile, lane,
                            a.out_a + (size_t)li * 2 * NN, a.out_b + (size_t)(a.param_off[inst] - p_base) * 2 * NN);
   }
 }

@@ -77,3 +77,40 @@ def check_against_oracle(lib, circuits, xs_per_circuit, T, tol=TOL):
         assert np.abs(Jr[k:k + P].T - O.matrix_residuals_jac(T, Uo, list(Jo))).max() < tol
         k += P
     return len(poi)
+
+
+def all_leaf_circuit(n):
+    """Every parameterised one-qubit leaf, a constant leaf and CNOTs in both directions on n qubits."""
+    from qsearch_b200 import gates
+    leaves = [gates.XGate(), gates.YGate(), gates.ZGate(), gates.U1Gate(), gates.U2Gate(), gates.U3Gate(), gates.XZXZGate(),
+              gates.ZXZXZGate(), gates.SXGate()]
+    layers = []
+    for s0 in range(0, len(leaves), n):
+        row = leaves[s0:s0 + n]
+        row += [gates.IdentityGate()] * (n - len(row))
+        layers.append(gates.KroneckerGate(*row))
+        q = (s0 // n) % (n - 1)
+        layers.append(gates.NonadjacentCNOTGate(n, q, q + 1) if s0 % 2 == 0 else gates.NonadjacentCNOTGate(n, q + 1, q))
+    layers.append(gates.KroneckerGate(*leaves[:n][::-1]))
+    return gates.ProductGate(*layers)
+
+
+def check_every_leaf_type(lib, n, tol=TOL):
+    """mat_jac and the residual Jacobian of all_leaf_circuit(n) against the oracle, including all-zero angles."""
+    from qsearch_b200 import unitaries
+    rng = np.random.default_rng(11)
+    c = all_leaf_circuit(n)
+    gp = lowering.lower(c)
+    P = c.num_inputs
+    xs = rng.random((3, P)) * 2 * np.pi
+    xs[2, :] = 0.0  # degenerate angles: sin = 0 in every gate
+    T = unitaries.qft(1 << n)
+    poi = np.zeros(3, dtype="int32")
+    U, J = lib.eval_mat_jac([gp], poi, xs)
+    r, Jr = lib.eval_residuals_jac([gp], poi, xs, T)
+    for i in range(3):
+        Uo, Jo = O.mat_jac(c, xs[i])
+        assert np.abs(U[i] - Uo).max() < tol
+        assert np.abs(J[i * P:(i + 1) * P] - np.array(Jo)).max() < tol
+        assert np.abs(r[i] - O.matrix_residuals(T, Uo)).max() < tol
+        assert np.abs(Jr[i * P:(i + 1) * P].T - O.matrix_residuals_jac(T, Uo, Jo)).max() < tol

@@ -148,3 +148,10 @@ def test_lm_system_run_kind():
         assert abs(rr[i] - r @ r) < 1e-12
         assert np.abs(g[i * P:(i + 1) * P] - Jr.T @ r).max() < 1e-12
         assert np.abs(A[i * P * P:(i + 1) * P * P].reshape(P, P) - Jr.T @ Jr).max() < 1e-12
+
+
+def test_every_leaf_type_through_the_warp_kernels():
+    """Rank-one derivative forms (generator-type and phase-type parameters) of all leaves against the oracle, n = 3, 4."""
+    lib = emulated_library()
+    for n in (3, 4):
+        _parity.check_every_leaf_type(lib, n)

@@ -66,6 +66,13 @@ def test_finite_difference(lib, gate):
         assert np.abs(fd - J).sum(axis=(1, 2)).max() < 1e-7
 
 
+@pytest.mark.parametrize("n", [3, 4, 5])
+def test_every_leaf_type_through_the_warp_kernels(lib, n):
+    """All parameterised leaves (generator-type and phase-type derivatives), a constant leaf and CNOTs in both
+    directions through the register/DMMA kernels, including all-zero angles."""
+    _parity.check_every_leaf_type(lib, n)
+
+
 @pytest.mark.parametrize("n", [2, 3, 4, 5])
 def test_ragged_batches_against_oracle(lib, n):
     rng = np.random.default_rng(100 + n)
