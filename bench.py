@@ -277,9 +277,10 @@ def run_ours(args, rank, world, local_rank):
     peaks = load_peaks()
     hbm_peak = peaks.get("hbm_gbs", 6650.0)
     achieved_tf = (n_inst / (kern_ms * 1e-3)) * F / 1e12
-    # what the warp kernel really issues on the FP64 tensor pipe: P complex N^3 products = 8 N^3 P flop per eval
-    executed_dmma_tf = (n_inst / (kern_ms * 1e-3)) * 8.0 * (N ** 3) * P / 1e12
-    ncu_traffic = {4: 255786.0, 5: 1075282.0}.get(n)  # dram read+write bytes per eval: profiles/r1/l_ncu_full_resid_n4_warp.txt, c_ncu_full_resid_n5_warp.txt
+    # what the warp kernel really issues on the FP64 tensor pipe: P half-size complex products (N x N/2 x N, rank-one form
+    # of the derivative) + one dense product for U T^dagger = (4 P + 8) N^3 flop per eval
+    executed_dmma_tf = (n_inst / (kern_ms * 1e-3)) * (4.0 * P + 8.0) * (N ** 3) / 1e12
+    ncu_traffic = {4: 255639.0, 5: 1068130.0}.get(n)  # dram read+write bytes per eval: profiles/r1/u_ncu_full_resid_n{4,5}_warp.txt
     line = {
         "metric": "objective+Jacobian evals/sec", "value": value, "unit": "evals/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": kern_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -297,9 +298,10 @@ def run_ours(args, rank, world, local_rank):
                      "dfma_peak": fp64_peak,
                      "flops": "achieved = ALGORITHMIC flops (dense prefix/suffix formulation, SURVEY 8d: 8N^3(2(G-1)+2P) + 8N^3(P+1)) per "
                               "second; gate structure lets the kernel execute fewer, so frac can exceed 1. Executed on the tensor pipe: "
-                              "8 N^3 P flop per eval (see executed)",
+                              "(4 P + 8) N^3 flop per eval (see executed); DFMA work shares the same FP64 pipe",
                      "executed": {"dmma_tflops": executed_dmma_tf, "frac_of_dmma_peak": executed_dmma_tf / dmma_peak if dmma_peak else None,
-                                  "ncu_dmma_pipe_active_pct": {4: 57.1, 5: 56.7}.get(n)},
+                                  "ncu_dmma_pipe_active_pct": {4: 45.2, 5: 47.7}.get(n),
+                                  "ncu_fp64_dfma_pipe_active_pct": {4: 22.1, 5: 22.7}.get(n)},
                      "traffic_note": "ncu dram bytes per eval (one --set full capture, profiles/r1) x instances of this launch",
                      "hbm": {"achieved": out_bytes / (kern_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
                              "frac": out_bytes / (kern_ms * 1e-3) / 1e9 / hbm_peak,
