@@ -17,10 +17,12 @@
 #ifdef QSB_EMU
 #define QSB_CLOCK() 0ll
 #define QSB_LDCG(p) (*(p))
+#define QSB_LDCG2(p) (*reinterpret_cast<const double2*>(p))
 static inline void qsb_cluster_sync() { qsb_emu_cluster_sync(); }
 #else
 #define QSB_CLOCK() clock64()
 #define QSB_LDCG(p) __ldcg(p)
+#define QSB_LDCG2(p) __ldcg(reinterpret_cast<const double2*>(p))
 // all threads of all CTAs of the cluster; release/acquire orders the global-memory traffic between them
 __device__ __forceinline__ void qsb_cluster_sync() {
   asm volatile("barrier.cluster.arrive.release.aligned;\nbarrier.cluster.wait.acquire.aligned;\n" ::: "memory");
@@ -34,16 +36,20 @@ __device__ __forceinline__ void qsb_cluster_sync() {
 // A[k][l] = sum_m R[k][m] R[l][m] for k, l < rows (both triangles written; ld = rows).  R row-major [rows][K2].
 // One warp per TB x TB block of the lower triangle (TB = 8 TW); the rows stream from L2, so bigger blocks mean
 // proportionally fewer bytes per flop.  task0 / ntask_stride: this warp's position among all cooperating warps.
+// KSPLIT = 2: a block's contraction is cut in two halves done by two warps that ADD their results into a zeroed A (two
+// addends: the sum does not depend on which lands first, so the result stays deterministic).
 template <int TW>
-QSB_DEVICE void qsb_syrk_dmma_t(const double* R, int rows, int K2, double* A, int task0, int stride, int lane) {
+QSB_DEVICE void qsb_syrk_dmma_t(const double* R, int rows, int K2, double* A, int task0, int stride, int lane, int ksplit) {
   constexpr int TB = 8 * TW;
   const int g = lane >> 2, t = lane & 3;
-  const int nb = (rows + TB - 1) / TB, ntasks = nb * (nb + 1) / 2;
+  const int nb = (rows + TB - 1) / TB, ntasks = nb * (nb + 1) / 2 * ksplit;
+  const int klen = K2 / ksplit;
   for (int task = task0; task < ntasks; task += stride) {
-    int bk = (int)((sqrt(8.0 * task + 1.0) - 1.0) * 0.5);
-    while ((bk + 1) * (bk + 2) / 2 <= task) ++bk;
-    while (bk * (bk + 1) / 2 > task) --bk;
-    const int bl = task - bk * (bk + 1) / 2;
+    const int tile = task / ksplit, kbeg = (task % ksplit) * klen;
+    int bk = (int)((sqrt(8.0 * tile + 1.0) - 1.0) * 0.5);
+    while ((bk + 1) * (bk + 2) / 2 <= tile) ++bk;
+    while (bk * (bk + 1) / 2 > tile) --bk;
+    const int bl = tile - bk * (bk + 1) / 2;
     double acc[TW][TW][2];
     const double* pa[TW];
     const double* pb[TW];
@@ -52,20 +58,31 @@ QSB_DEVICE void qsb_syrk_dmma_t(const double* R, int rows, int K2, double* A, in
       int ra = TB * bk + 8 * i + g, rb = TB * bl + 8 * i + g;
       if (ra > rows - 1) ra = rows - 1;
       if (rb > rows - 1) rb = rows - 1;
-      pa[i] = R + (size_t)ra * K2 + t;
-      pb[i] = R + (size_t)rb * K2 + t;
+      pa[i] = R + (size_t)ra * K2 + kbeg + 4 * t;
+      pb[i] = R + (size_t)rb * K2 + kbeg + 4 * t;
 #pragma unroll
       for (int j = 0; j < TW; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
     }
-#pragma unroll 4
-    for (int m0 = 0; m0 < K2; m0 += 4) {
-      double av[TW], bv[TW];
+    // The order of the contracted index is free as long as both operands agree: lane t takes the 4 consecutive columns
+    // 16 u + 4 t .. + 3 of a 16-column chunk (two 16-byte loads) and feeds them to 4 successive DMMAs, instead of one
+    // 8-byte load per DMMA.
+#pragma unroll 2
+    for (int m0 = 0; m0 < klen; m0 += 16) {
+      double2 av[TW][2], bv[TW][2];
 #pragma unroll
-      for (int i = 0; i < TW; ++i) { av[i] = QSB_LDCG(pa[i] + m0); bv[i] = QSB_LDCG(pb[i] + m0); }
+      for (int i = 0; i < TW; ++i) {
+        av[i][0] = QSB_LDCG2(pa[i] + m0); av[i][1] = QSB_LDCG2(pa[i] + m0 + 2);
+        bv[i][0] = QSB_LDCG2(pb[i] + m0); bv[i][1] = QSB_LDCG2(pb[i] + m0 + 2);
+      }
 #pragma unroll
-      for (int i = 0; i < TW; ++i)
+      for (int s4 = 0; s4 < 4; ++s4)
 #pragma unroll
-        for (int j = 0; j < TW; ++j) qsb_dmma884(acc[i][j][0], acc[i][j][1], av[i], bv[j]);
+        for (int i = 0; i < TW; ++i)
+#pragma unroll
+          for (int j = 0; j < TW; ++j) {
+            const double x = (s4 & 1) ? av[i][s4 >> 1].y : av[i][s4 >> 1].x, y = (s4 & 1) ? bv[j][s4 >> 1].y : bv[j][s4 >> 1].x;
+            qsb_dmma884(acc[i][j][0], acc[i][j][1], x, y);
+          }
     }
 #pragma unroll
     for (int i = 0; i < TW; ++i)
@@ -74,16 +91,39 @@ QSB_DEVICE void qsb_syrk_dmma_t(const double* R, int rows, int K2, double* A, in
 #pragma unroll
         for (int e = 0; e < 2; ++e) {
           const int k = TB * bk + 8 * i + g, l = TB * bl + 8 * j + 2 * t + e;
-          if (k < rows && l < rows) { A[(size_t)k * rows + l] = acc[i][j][e]; A[(size_t)l * rows + k] = acc[i][j][e]; }
+          if (k < rows && l < rows) {
+            if (ksplit == 1) { A[(size_t)k * rows + l] = acc[i][j][e]; A[(size_t)l * rows + k] = acc[i][j][e]; }
+            else {
+              atomicAdd(&A[(size_t)k * rows + l], acc[i][j][e]);
+              if (bk != bl) atomicAdd(&A[(size_t)l * rows + k], acc[i][j][e]);  // a diagonal block holds both triangles itself
+            }
+          }
         }
   }
 }
 
-// warp = index of this warp among the nwarps cooperating warps (all CTAs of the cluster)
+// Block size (16 or 32) and K-split (1 or 2) that finish soonest on nwarps warps: rounds x DMMAs per round, 16-wide
+// blocks charged 1.5x for their doubled L2 bytes per flop.  Returns tw | ksplit << 8.
+QSB_DEVICE int qsb_syrk_plan(int rows, int nwarps) {
+  int best = 0;
+  long long best_cost = 0;
+  for (int c = 0; c < 4; ++c) {
+    const int tw = (c & 1) ? 4 : 2, ks = (c & 2) ? 2 : 1;
+    const int nb = (rows + 8 * tw - 1) / (8 * tw);
+    const long long tasks = (long long)nb * (nb + 1) / 2 * ks, rounds = (tasks + nwarps - 1) / nwarps;
+    const long long cost = rounds * (tw * tw) * (tw == 2 ? 3 : 2) / ks * 8 + (ks == 2 ? 1 : 0);
+    if (c == 0 || cost < best_cost) { best_cost = cost; best = tw | (ks << 8); }
+  }
+  return best;
+}
+QSB_DEVICE bool qsb_syrk_needs_zero(int rows, int nwarps) { return (qsb_syrk_plan(rows, nwarps) >> 8) == 2; }
+
+// warp = index of this warp among the nwarps cooperating warps (all CTAs of the cluster).  When the plan splits K the
+// caller must have zeroed A (qsb_syrk_needs_zero) and made that visible to all cooperating warps.
 QSB_DEVICE void qsb_syrk_dmma(const double* R, int rows, int K2, double* A, int warp, int nwarps, int lane) {
-  const int nb32 = (rows + 31) / 32;
-  if (nb32 * (nb32 + 1) / 2 >= 2 * nwarps) qsb_syrk_dmma_t<4>(R, rows, K2, A, warp, nwarps, lane);
-  else qsb_syrk_dmma_t<2>(R, rows, K2, A, warp, nwarps, lane);
+  const int plan = qsb_syrk_plan(rows, nwarps), ks = plan >> 8;
+  if ((plan & 255) == 4) qsb_syrk_dmma_t<4>(R, rows, K2, A, warp, nwarps, lane, ks);
+  else qsb_syrk_dmma_t<2>(R, rows, K2, A, warp, nwarps, lane, ks);
 }
 
 // Forward-only sweep on the 8 columns [8 cb, 8 cb + 8) of X = U T^dagger: returns this block's share of
@@ -351,16 +391,24 @@ QSB_DEVICE bool qsb_chol_packed(const double* A, int rows, const double* d2, dou
   __syncthreads();
   // copy in the lower triangle, one row per warp and round; a row's loads (<= 9 per lane) are all issued before the
   // first store, so the L2 latency is paid once per row, not once per element
-  for (int i = warp; i < rows; i += nwarps) {
-    const double* ar = A + (size_t)i * rows;
-    double* lr = Ls + QSB_TRI(i, 0);
-    double v[9];
-#pragma unroll
-    for (int m = 0; m < 9; ++m) { const int j = lane + 32 * m; v[m] = (j <= i) ? QSB_LDCG(ar + j) : 0.0; }
+  for (int i0 = 2 * warp; i0 < rows; i0 += 2 * nwarps) {  // two rows per warp and round: up to 18 loads in flight per lane
+    const int i1 = (i0 + 1 < rows) ? i0 + 1 : i0;
+    const double* ar0 = A + (size_t)i0 * rows;
+    const double* ar1 = A + (size_t)i1 * rows;
+    double v0[9], v1[9];
 #pragma unroll
     for (int m = 0; m < 9; ++m) {
       const int j = lane + 32 * m;
-      if (j <= i) lr[j] = v[m] + ((j == i && i < P) ? mu * d2[i] : 0.0);
+      v0[m] = (j <= i0) ? QSB_LDCG(ar0 + j) : 0.0;
+      v1[m] = (j <= i1) ? QSB_LDCG(ar1 + j) : 0.0;
+    }
+    double* lr0 = Ls + QSB_TRI(i0, 0);
+    double* lr1 = Ls + QSB_TRI(i1, 0);
+#pragma unroll
+    for (int m = 0; m < 9; ++m) {
+      const int j = lane + 32 * m;
+      if (j <= i0) lr0[j] = v0[m] + ((j == i0 && i0 < P) ? mu * d2[i0] : 0.0);
+      if (j <= i1 && i1 != i0) lr1[j] = v1[m] + ((j == i1 && i1 < P) ? mu * d2[i1] : 0.0);
     }
   }
   if (threadIdx.x == 0) *okflag = 1;
@@ -369,25 +417,22 @@ QSB_DEVICE bool qsb_chol_packed(const double* A, int rows, const double* d2, dou
   for (int kb = 0; kb < P; kb += NB) {
     const int nbk = (P - kb < NB) ? P - kb : NB;
     if (warp == 0) {  // 1. diagonal block: lane = row, the row in registers, columns exchanged by shuffle
-      const int il = lane < nbk ? lane : nbk - 1, i = kb + il;
+      // A short block is padded with identity rows, and the entries above the diagonal are left to hold garbage that
+      // nothing reads, so the 16 column steps are straight-line code: broadcast, rsqrt, 15 - j shuffle + FMA pairs.
+      const int i = kb + lane;
       double d[NB];
 #pragma unroll
-      for (int j = 0; j < NB; ++j) d[j] = (j <= il && j < nbk) ? Ls[QSB_TRI(i, kb + j)] : 0.0;
+      for (int j = 0; j < NB; ++j) d[j] = (lane < nbk && j <= lane) ? Ls[QSB_TRI(i, kb + j)] : ((j == lane) ? 1.0 : 0.0);
       bool good = true;
 #pragma unroll
       for (int j = 0; j < NB; ++j) {
-        if (j < nbk) {
-          const double piv = __shfl_sync(QSB_FULL, d[j], j);
-          if (!(piv > 0.0) || !(piv < 1e300)) { good = false; break; }
-          const double inv = rsqrt(piv), sq = piv * inv;  // one reciprocal-square-root sequence instead of sqrt + divide
-          if (lane == j) { rinv[j] = inv; rdiag[kb + j] = inv; }
-          d[j] = (lane == j) ? sq : d[j] * inv;
+        const double piv = __shfl_sync(QSB_FULL, d[j], j);
+        if (!(piv > 0.0) || !(piv < 1e300)) { good = false; break; }
+        const double inv = rsqrt(piv);  // one reciprocal-square-root sequence instead of sqrt + divide
+        if (lane == j && j < nbk) { rinv[j] = inv; rdiag[kb + j] = inv; }
+        d[j] = (lane == j) ? piv * inv : d[j] * inv;
 #pragma unroll
-          for (int k = j + 1; k < NB; ++k) {
-            const double lkj = __shfl_sync(QSB_FULL, d[j], k < nbk ? k : 0);
-            if (k <= il) d[k] = fma(-d[j], lkj, d[k]);
-          }
-        }
+        for (int k = j + 1; k < NB; ++k) d[k] = fma(-d[j], __shfl_sync(QSB_FULL, d[j], k), d[k]);
       }
       if (!good && lane == 0) *okflag = 0;
       if (lane < nbk) {
@@ -404,15 +449,16 @@ QSB_DEVICE bool qsb_chol_packed(const double* A, int rows, const double* d2, dou
       double x[NB];
 #pragma unroll
       for (int j = 0; j < NB; ++j) x[j] = (j < nbk) ? src[j] : 0.0;
+      // column-oriented substitution: once x[j] is final it is folded into all later entries (independent FMAs), the
+      // same operations on every x[k] in the same order as the row-oriented form, without its serial chain
 #pragma unroll
       for (int j = 0; j < NB; ++j) {
         if (j < nbk) {
-          double s = x[j];
-          const double* lj = Ls + QSB_TRI(kb + j, kb);
-#pragma unroll
-          for (int m = 0; m < j; ++m) s = fma(-x[m], lj[m], s);
-          x[j] = s * rinv[j];
+          x[j] *= rinv[j];
           src[j] = x[j];
+#pragma unroll
+          for (int k = j + 1; k < NB; ++k)
+            if (k < nbk) x[k] = fma(-x[j], Ls[QSB_TRI(kb + k, kb + j)], x[k]);
         }
       }
     }
@@ -480,16 +526,37 @@ QSB_DEVICE void qsb_chol_back_packed(const double* Ls, int P, const double* rdia
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   __syncthreads();
   if (warp == 0) {
+    // the right-hand side lives in registers (lane l owns rows l, l + 32, ...): a step is one multiply, one shuffle
+    // broadcast and one FMA per owned row; the factor's row j is read from shared memory off the critical path
+    constexpr int NR = (QSB_CH_MAXROWS + 31) / 32;
     const double* y = Ls + QSB_TRI(P, 0);
-    for (int i = lane; i < P; i += 32) h[i] = -y[i];
-    __syncwarp();
-    for (int j = P - 1; j >= 0; --j) {
-      const double* lj = Ls + QSB_TRI(j, 0);
-      const double hj = h[j] * rdiag[j];
-      __syncwarp();
-      if (lane == 0) h[j] = hj;
-      for (int i = lane; i < j; i += 32) h[i] = fma(-lj[i], hj, h[i]);
-      __syncwarp();
+    double hr[NR], rd[NR];
+#pragma unroll
+    for (int b = 0; b < NR; ++b) {
+      const int i = 32 * b + lane;
+      hr[b] = (i < P) ? -y[i] : 0.0;
+      rd[b] = (i < P) ? rdiag[i] : 0.0;
+    }
+#pragma unroll
+    for (int b = NR - 1; b >= 0; --b) {
+      if (32 * b < P) {
+        const int jhi = (P - 1 < 32 * b + 31) ? P - 1 : 32 * b + 31;
+        for (int j = jhi; j >= 32 * b; --j) {
+          const double hj = __shfl_sync(QSB_FULL, hr[b] * rd[b], j & 31);
+          if (lane == (j & 31)) hr[b] = hj;
+          const double* lj = Ls + QSB_TRI(j, 0);
+#pragma unroll
+          for (int c = 0; c <= b; ++c) {
+            const int i = 32 * c + lane;
+            if (i < j) hr[c] = fma(-lj[i], hj, hr[c]);
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int b = 0; b < NR; ++b) {
+      const int i = 32 * b + lane;
+      if (i < P) h[i] = hr[b];
     }
   }
   __syncthreads();
@@ -532,8 +599,14 @@ QSB_GLOBAL __launch_bounds__(QSB_LM_WARPS * 32) qsb_k_lm2(QsbSolveArgs a) {
     __syncthreads();
     for (int e = threadIdx.x; e < prog.n_ops * 6; e += blockDim.x) ((int32_t*)sops)[e] = ((const int32_t*)prog.ops)[e];
     prog.ops = sops;  // every sweep of this solve reads the ops from shared memory
-    double* A = Rg + (size_t)(a.max_params + 1) * M;
-    double* L = A + (size_t)(a.max_params + 1) * (a.max_params + 1) + (size_t)rank * (a.max_params + 1) * (a.max_params + 1);
+    // two Gram buffers used alternately: the one the next SYRK adds into is zeroed during the Jacobian phase, when no
+    // CTA of the cluster can still be reading it (they all passed the barriers of the evaluation before)
+    double* Abuf = Rg + (size_t)(a.max_params + 1) * M;
+    const size_t asz = (size_t)(a.max_params + 1) * (a.max_params + 1);
+    double* A = Abuf;
+    double* L = Abuf + 2 * asz + (size_t)rank * asz;
+    const bool kzero = qsb_syrk_needs_zero(rows, cwarps);
+    if (kzero && csize > 1) qsb_cluster_sync();  // nobody is still reading the previous instance's Gram matrix
     const double* x0 = a.x0 + a.param_off[inst];
     const int max_iters = a.max_iters > 0 ? a.max_iters : 100 * (P > 0 ? P : 1);
     __syncthreads();
@@ -543,7 +616,11 @@ QSB_GLOBAL __launch_bounds__(QSB_LM_WARPS * 32) qsb_k_lm2(QsbSolveArgs a) {
     cplx tr;
     double F = qsb_cta_half_norm<NQ>(prog, x, a.target, trig, gtab, part, &tr);  // also fills trig for x
     if (P > 0) {
-      { QSB_PROF_BEGIN(); qsb_cta_jac<NQ>(prog, a.target, gtab, wtiles, seg, rank, Rg); qsb_cluster_sync(); QSB_PROF_END(0); }
+      {
+        QSB_PROF_BEGIN();
+        if (kzero) for (int e = rank * blockDim.x + threadIdx.x; e < rows * rows; e += csize * blockDim.x) A[e] = 0.0;
+        qsb_cta_jac<NQ>(prog, a.target, gtab, wtiles, seg, rank, Rg); qsb_cluster_sync(); QSB_PROF_END(0);
+      }
       iters = 1;
       { QSB_PROF_BEGIN(); qsb_syrk_dmma(Rg, rows, M, A, cwarp, cwarps, lane); qsb_cluster_sync(); QSB_PROF_END(1); }
       for (int k = threadIdx.x; k < P; k += blockDim.x) {
@@ -605,7 +682,12 @@ QSB_GLOBAL __launch_bounds__(QSB_LM_WARPS * 32) qsb_k_lm2(QsbSolveArgs a) {
           if (conv_f) { status = 2; break; }
           if (conv_x) { status = 3; break; }
           if (iters >= max_iters) { status = 0; break; }
-          { QSB_PROF_BEGIN(); qsb_cta_jac<NQ>(prog, a.target, gtab, wtiles, seg, rank, Rg); qsb_cluster_sync(); QSB_PROF_END(0); }
+          {
+            QSB_PROF_BEGIN();
+            A = Abuf + (size_t)(iters & 1) * asz;
+            if (kzero) for (int e = rank * blockDim.x + threadIdx.x; e < rows * rows; e += csize * blockDim.x) A[e] = 0.0;
+            qsb_cta_jac<NQ>(prog, a.target, gtab, wtiles, seg, rank, Rg); qsb_cluster_sync(); QSB_PROF_END(0);
+          }
           ++iters;
           { QSB_PROF_BEGIN(); qsb_syrk_dmma(Rg, rows, M, A, cwarp, cwarps, lane); qsb_cluster_sync(); QSB_PROF_END(1); }
           for (int k = threadIdx.x; k < P; k += blockDim.x) {
@@ -674,6 +756,7 @@ QSB_GLOBAL __launch_bounds__(QSB_LM_WARPS * 32) qsb_k_lmsys(QsbBatchArgs a, doub
     qsb_cta_segments(prog, NSEG, seg);
     cplx tr;
     qsb_cta_half_norm<NQ>(prog, a.params + a.param_off[inst], a.target, trig, gtab, part, &tr);  // trig + gate table
+    if (qsb_syrk_needs_zero(rows, QSB_LM_WARPS)) for (int e = threadIdx.x; e < rows * rows; e += blockDim.x) A[e] = 0.0;
     qsb_cta_jac<NQ>(prog, a.target, gtab, wtiles, seg, 0, Rg);
     __syncthreads();
     qsb_syrk_dmma(Rg, rows, M, A, warp, QSB_LM_WARPS, lane);
