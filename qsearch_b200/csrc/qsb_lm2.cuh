@@ -449,28 +449,25 @@ QSB_DEVICE bool qsb_chol_packed(const double* A, int rows, const double* d2, dou
       double x[NB];
 #pragma unroll
       for (int j = 0; j < NB; ++j) x[j] = (j < nbk) ? src[j] : 0.0;
-      // column-oriented substitution: once x[j] is final it is folded into all later entries (independent FMAs), the
-      // same operations on every x[k] in the same order as the row-oriented form, without its serial chain
 #pragma unroll
       for (int j = 0; j < NB; ++j) {
         if (j < nbk) {
-          x[j] *= rinv[j];
-          src[j] = x[j];
+          double s = x[j];
+          const double* lj = Ls + QSB_TRI(kb + j, kb);
 #pragma unroll
-          for (int k = j + 1; k < NB; ++k)
-            if (k < nbk) x[k] = fma(-x[j], Ls[QSB_TRI(kb + k, kb + j)], x[k]);
+          for (int m = 0; m < j; ++m) s = fma(-x[m], lj[m], s);
+          x[j] = s * rinv[j];
+          src[j] = x[j];
         }
       }
     }
     __syncthreads();
     QSB_CH_T(8);
-    if (R0 < P) {  // 3. trailing update, 16x16 DMMA tiles of the lower triangle
-      const int nbt = (nrow + 15) >> 4, ntasks = nbt * (nbt + 1) / 2;
-      for (int task = warp; task < ntasks; task += nwarps) {
-        int bi = (int)((sqrt(8.0 * task + 1.0) - 1.0) * 0.5);
-        while ((bi + 1) * (bi + 2) / 2 <= task) ++bi;
-        while (bi * (bi + 1) / 2 > task) --bi;
-        const int bj = task - bi * (bi + 1) / 2;
+    if (R0 < P) {  // 3. trailing update, 16x16 DMMA tiles of the lower triangle, dealt round-robin to the warps
+      const int nbt = (nrow + 15) >> 4;
+      int bi = 0, bj = 0;
+      for (int skip = warp; skip > 0; --skip) { if (++bj > bi) { ++bi; bj = 0; } }
+      for (; bi < nbt;) {
         double acc[2][2][2];
         const double* pa[2];
         const double* pb[2];
@@ -511,6 +508,7 @@ QSB_DEVICE bool qsb_chol_packed(const double* A, int rows, const double* d2, dou
               const int r = 16 * bi + 8 * i + g, c = 16 * bj + 8 * j + 2 * t + e;
               if (r < nrow && c <= r) Ls[QSB_TRI(R0 + r, R0 + c)] = acc[i][j][e];
             }
+        for (int skip = nwarps; skip > 0; --skip) { if (++bj > bi) { ++bi; bj = 0; } }
       }
     }
     __syncthreads();
