@@ -381,6 +381,79 @@ QSB_DEVICE void qsb_chol_back(const double* Lb, int rows, int P, double* h) {
 // L2 round trips inside the factorisation.  Used whenever it fits (P <= ~220); otherwise qsb_chol_blocked.
 #define QSB_TRI(i, j) ((size_t)(i) * ((i) + 1) / 2 + (j))
 
+// diagonal block [kb, kb + nbk) of the packed factor: one warp, lane = row, the row in registers, columns exchanged by
+// shuffle.  A short block is padded with identity rows, and the entries above the diagonal are left to hold garbage
+// that nothing reads, so the 16 column steps are straight-line code: broadcast, rsqrt, 15 - j shuffle + FMA pairs.
+QSB_DEVICE void qsb_chp_diag(double* Ls, int kb, int nbk, double* rinv, double* rdiag, int* okflag, int lane) {
+  constexpr int NB = QSB_CH_NB;
+  const int i = kb + lane;
+  double d[NB];
+#pragma unroll
+  for (int j = 0; j < NB; ++j) d[j] = (lane < nbk && j <= lane) ? Ls[QSB_TRI(i, kb + j)] : ((j == lane) ? 1.0 : 0.0);
+  bool good = true;
+#pragma unroll
+  for (int j = 0; j < NB; ++j) {
+    const double piv = __shfl_sync(QSB_FULL, d[j], j);
+    if (!(piv > 0.0) || !(piv < 1e300)) { good = false; break; }
+    const double inv = rsqrt(piv);  // one reciprocal-square-root sequence instead of sqrt + divide
+    if (lane == j && j < nbk) { rinv[j] = inv; rdiag[kb + j] = inv; }
+    d[j] = (lane == j) ? piv * inv : d[j] * inv;
+#pragma unroll
+    for (int k = j + 1; k < NB; ++k) d[k] = fma(-d[j], __shfl_sync(QSB_FULL, d[j], k), d[k]);
+  }
+  if (!good && lane == 0) *okflag = 0;
+  if (lane < nbk) {
+#pragma unroll
+    for (int j = 0; j < NB; ++j) if (j <= lane) Ls[QSB_TRI(i, kb + j)] = d[j];
+  }
+}
+
+// one 16x16 tile (bi, bj) of the trailing update C -= P P^T behind panel [kb, kb + nbk); the trailing matrix starts at R0
+QSB_DEVICE void qsb_chp_tile(double* Ls, int R0, int kb, int nbk, int nrow, int bi, int bj, int lane) {
+  constexpr int NB = QSB_CH_NB;
+  const int g = lane >> 2, t = lane & 3;
+  double acc[2][2][2];
+  const double* pa[2];
+  const double* pb[2];
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    int ra = 16 * bi + 8 * i + g, rb = 16 * bj + 8 * i + g;
+    if (ra > nrow - 1) ra = nrow - 1;
+    if (rb > nrow - 1) rb = nrow - 1;
+    pa[i] = Ls + QSB_TRI(R0 + ra, kb) + t;
+    pb[i] = Ls + QSB_TRI(R0 + rb, kb) + t;
+  }
+#pragma unroll
+  for (int i = 0; i < 2; ++i)
+#pragma unroll
+    for (int j = 0; j < 2; ++j)
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        const int r = 16 * bi + 8 * i + g, c = 16 * bj + 8 * j + 2 * t + e;
+        acc[i][j][e] = (r < nrow && c <= r) ? Ls[QSB_TRI(R0 + r, R0 + c)] : 0.0;
+      }
+#pragma unroll
+  for (int ks = 0; ks < NB / 4; ++ks) {
+    const bool in = 4 * ks + t < nbk;
+    const double a0 = in ? -pa[0][4 * ks] : 0.0, a1 = in ? -pa[1][4 * ks] : 0.0;
+    const double b0 = in ? pb[0][4 * ks] : 0.0, b1 = in ? pb[1][4 * ks] : 0.0;
+    qsb_dmma884(acc[0][0][0], acc[0][0][1], a0, b0);
+    qsb_dmma884(acc[0][1][0], acc[0][1][1], a0, b1);
+    qsb_dmma884(acc[1][0][0], acc[1][0][1], a1, b0);
+    qsb_dmma884(acc[1][1][0], acc[1][1][1], a1, b1);
+  }
+  __syncwarp();
+#pragma unroll
+  for (int i = 0; i < 2; ++i)
+#pragma unroll
+    for (int j = 0; j < 2; ++j)
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        const int r = 16 * bi + 8 * i + g, c = 16 * bj + 8 * j + 2 * t + e;
+        if (r < nrow && c <= r) Ls[QSB_TRI(R0 + r, R0 + c)] = acc[i][j][e];
+      }
+}
+
 QSB_DEVICE bool qsb_chol_packed(const double* A, int rows, const double* d2, double mu, int P, double* Ls, double* rinv, double* rdiag, int* okflag,
                                 long long* prof) {
 #define QSB_CH_T(slot) do { if (prof && threadIdx.x == 0) { const long long _n = QSB_CLOCK(); atomicAdd((unsigned long long*)&prof[slot], (unsigned long long)(_n - _tc)); _tc = _n; } } while (0)
@@ -414,34 +487,14 @@ QSB_DEVICE bool qsb_chol_packed(const double* A, int rows, const double* d2, dou
   if (threadIdx.x == 0) *okflag = 1;
   __syncthreads();
   QSB_CH_T(6);
+  // Look-ahead: the diagonal block of panel k+1 is factored by warp 0 while the other warps finish the trailing update of
+  // panel k (only the first block column of the trailing matrix has to be done before that), so the serial column chain
+  // of the diagonal block is hidden behind tensor-core work except for the very first block.
+  if (warp == 0) qsb_chp_diag(Ls, 0, (P < NB) ? P : NB, rinv, rdiag, okflag, lane);
+  __syncthreads();
+  QSB_CH_T(7);
   for (int kb = 0; kb < P; kb += NB) {
     const int nbk = (P - kb < NB) ? P - kb : NB;
-    if (warp == 0) {  // 1. diagonal block: lane = row, the row in registers, columns exchanged by shuffle
-      // A short block is padded with identity rows, and the entries above the diagonal are left to hold garbage that
-      // nothing reads, so the 16 column steps are straight-line code: broadcast, rsqrt, 15 - j shuffle + FMA pairs.
-      const int i = kb + lane;
-      double d[NB];
-#pragma unroll
-      for (int j = 0; j < NB; ++j) d[j] = (lane < nbk && j <= lane) ? Ls[QSB_TRI(i, kb + j)] : ((j == lane) ? 1.0 : 0.0);
-      bool good = true;
-#pragma unroll
-      for (int j = 0; j < NB; ++j) {
-        const double piv = __shfl_sync(QSB_FULL, d[j], j);
-        if (!(piv > 0.0) || !(piv < 1e300)) { good = false; break; }
-        const double inv = rsqrt(piv);  // one reciprocal-square-root sequence instead of sqrt + divide
-        if (lane == j && j < nbk) { rinv[j] = inv; rdiag[kb + j] = inv; }
-        d[j] = (lane == j) ? piv * inv : d[j] * inv;
-#pragma unroll
-        for (int k = j + 1; k < NB; ++k) d[k] = fma(-d[j], __shfl_sync(QSB_FULL, d[j], k), d[k]);
-      }
-      if (!good && lane == 0) *okflag = 0;
-      if (lane < nbk) {
-#pragma unroll
-        for (int j = 0; j < NB; ++j) if (j <= lane) Ls[QSB_TRI(i, kb + j)] = d[j];
-      }
-    }
-    __syncthreads();
-    QSB_CH_T(7);
     if (!*okflag) { __syncthreads(); return false; }
     const int R0 = kb + nbk, nrow = rows - R0;
     for (int ri = threadIdx.x; ri < nrow; ri += blockDim.x) {  // 2. panel, one row per thread
@@ -463,57 +516,26 @@ QSB_DEVICE bool qsb_chol_packed(const double* A, int rows, const double* d2, dou
     }
     __syncthreads();
     QSB_CH_T(8);
-    if (R0 < P) {  // 3. trailing update, 16x16 DMMA tiles of the lower triangle, dealt round-robin to the warps
+    if (R0 < P) {  // 3. trailing update, 16x16 DMMA tiles of the lower triangle
       const int nbt = (nrow + 15) >> 4;
-      int bi = 0, bj = 0;
-      for (int skip = warp; skip > 0; --skip) { if (++bj > bi) { ++bi; bj = 0; } }
-      for (; bi < nbt;) {
-        double acc[2][2][2];
-        const double* pa[2];
-        const double* pb[2];
-#pragma unroll
-        for (int i = 0; i < 2; ++i) {
-          int ra = 16 * bi + 8 * i + g, rb = 16 * bj + 8 * i + g;
-          if (ra > nrow - 1) ra = nrow - 1;
-          if (rb > nrow - 1) rb = nrow - 1;
-          pa[i] = Ls + QSB_TRI(R0 + ra, kb) + t;
-          pb[i] = Ls + QSB_TRI(R0 + rb, kb) + t;
+      for (int bi = warp; bi < nbt; bi += nwarps) qsb_chp_tile(Ls, R0, kb, nbk, nrow, bi, 0, lane);  // 3a. first block column
+      __syncthreads();
+      const int nbk1 = (P - R0 < NB) ? P - R0 : NB;
+      if (warp == 0) qsb_chp_diag(Ls, R0, nbk1, rinv, rdiag, okflag, lane);  // 3b. next diagonal block ...
+      if (warp != 0 || nwarps == 1) {                                         // ... under the rest of the update
+        const int nw = (nwarps == 1) ? 1 : nwarps - 1, w = (nwarps == 1) ? 0 : warp - 1;
+        int bi = 1, bj = 1;
+        for (int skip = w; skip > 0; --skip) { if (++bj > bi) { ++bi; bj = 1; } }
+        while (bi < nbt) {
+          qsb_chp_tile(Ls, R0, kb, nbk, nrow, bi, bj, lane);
+          for (int skip = nw; skip > 0; --skip) { if (++bj > bi) { ++bi; bj = 1; } }
         }
-#pragma unroll
-        for (int i = 0; i < 2; ++i)
-#pragma unroll
-          for (int j = 0; j < 2; ++j)
-#pragma unroll
-            for (int e = 0; e < 2; ++e) {
-              const int r = 16 * bi + 8 * i + g, c = 16 * bj + 8 * j + 2 * t + e;
-              acc[i][j][e] = (r < nrow && c <= r) ? Ls[QSB_TRI(R0 + r, R0 + c)] : 0.0;
-            }
-#pragma unroll
-        for (int ks = 0; ks < NB / 4; ++ks) {
-          const bool in = 4 * ks + t < nbk;
-          const double a0 = in ? -pa[0][4 * ks] : 0.0, a1 = in ? -pa[1][4 * ks] : 0.0;
-          const double b0 = in ? pb[0][4 * ks] : 0.0, b1 = in ? pb[1][4 * ks] : 0.0;
-          qsb_dmma884(acc[0][0][0], acc[0][0][1], a0, b0);
-          qsb_dmma884(acc[0][1][0], acc[0][1][1], a0, b1);
-          qsb_dmma884(acc[1][0][0], acc[1][0][1], a1, b0);
-          qsb_dmma884(acc[1][1][0], acc[1][1][1], a1, b1);
-        }
-        __syncwarp();
-#pragma unroll
-        for (int i = 0; i < 2; ++i)
-#pragma unroll
-          for (int j = 0; j < 2; ++j)
-#pragma unroll
-            for (int e = 0; e < 2; ++e) {
-              const int r = 16 * bi + 8 * i + g, c = 16 * bj + 8 * j + 2 * t + e;
-              if (r < nrow && c <= r) Ls[QSB_TRI(R0 + r, R0 + c)] = acc[i][j][e];
-            }
-        for (int skip = nwarps; skip > 0; --skip) { if (++bj > bi) { ++bi; bj = 0; } }
       }
+      __syncthreads();
     }
-    __syncthreads();
     QSB_CH_T(9);
   }
+  if (!*okflag) { __syncthreads(); return false; }
   return true;
 #undef QSB_CH_T
 }
