@@ -36,6 +36,7 @@ def case(n, depth, n_children, starts, seed, gateset):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--method", default="lm")
+    ap.add_argument("--only", default=None, help="run only the case with this name (for ncu captures)")
     a = ap.parse_args()
     lib = _lib.get_library()
     cases = [("n3 d6 2x4", 3, 6, 2, 4, gatesets.QubitCNOTLinear()),
@@ -46,6 +47,8 @@ def main():
              ("n5 d30 6x4", 5, 30, 6, 4, gatesets.QubitCNOTAdjacencyList(YORKTOWN)),
              ("n5 d30 6x24", 5, 30, 6, 24, gatesets.QubitCNOTAdjacencyList(YORKTOWN))]
     for name, n, depth, nc, starts, gs in cases:
+        if a.only and name != a.only:
+            continue
         gps, poi, x0 = case(n, depth, nc, starts, 5, gs)
         T = unitaries.qft(1 << n)
         lib.solve(a.method, gps[:1], poi[:1] * 0, x0[:gps[0].n_params], T)  # warm-up (module load, allocations)
