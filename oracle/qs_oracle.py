@@ -198,6 +198,19 @@ def matrix_residuals_jac(T, M, J):  # comparison.py:66-72 ; returns shape (2N^2,
     return rows.T
 
 
+# ----------------------------------------------------------------------------- state preparation objective
+def distance_with_initial_state(stateA, stateB, A, B):  # comparison.py:114-115
+    return np.abs(1 - np.abs(np.vdot(A @ stateA, B @ stateB)))
+
+
+def distance_with_initial_state_jac(stateA, stateB, A, B, J):  # comparison.py:117-123
+    si = A @ stateA
+    s = np.vdot(si, B @ stateB)
+    vu = np.array([np.vdot(si, K @ stateB) for K in J])
+    g = -(s.real * vu.real + s.imag * vu.imag) / np.abs(s) if len(J) else np.zeros(0)
+    return 1 - np.abs(s), g
+
+
 # ----------------------------------------------------------------------------- the timed units
 def eval_lm(gate, T, x):
     """One LM-form objective+Jacobian evaluation: r in R^{2N^2}, J_r in R^{2N^2 x P} (a8+a11+a12)."""

@@ -29,6 +29,14 @@ class Compiler:
         raise NotImplementedError
 
 
+def _require_target(options):
+    """``target`` is required (compiler.py:62); a state-preparation Options object supplies it as a smart default
+    (defaults.py:80-81,128) - the reference's Project passes ``options.target`` explicitly, same effect."""
+    if "target_state" in options and "target" in options:
+        options.target = options.target
+    options.make_required("target")
+
+
 def _qudits_of(options):
     U = options.unitary_preprocessor(options.target) if "unitary_preprocessor" in options else options.target
     d = options.gateset.d
@@ -67,7 +75,7 @@ class SearchCompiler(Compiler):
 
     def compile(self, options=None):
         options = self.options.updated(options) if options is not None else self.options.copy()
-        options.make_required("target")
+        _require_target(options)
         logger, h, weight_limit = options.logger, options.heuristic, options.weight_limit
         start = timer()
         n = _qudits_of(options)

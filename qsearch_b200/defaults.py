@@ -1,5 +1,7 @@
 """Default option values of the search (reference: qsearch/defaults.py:89-122), with the GPU classes in the
 slots the reference fills with its CPU ones."""
+import numpy as np
+
 from . import backends, gatesets, heuristics, objectives, parallelizers, solvers, utils
 
 standard_defaults = {
@@ -37,3 +39,19 @@ standard_smart_defaults = {
     "heuristic": default_heuristic,
     "logger": default_logger,
 }
+
+
+# state preparation (reference: qsearch/defaults.py:75-81,124-130): Options(target_state=..., defaults=stateprep_defaults,
+# smart_defaults=stateprep_smart_defaults)
+def stateprep_initial_state(options):
+    v = np.zeros(np.asarray(options.target_state).shape, dtype="complex128")
+    v[0] = 1
+    return v
+
+
+def stateprep_target(options):
+    return np.eye(np.asarray(options.target_state).shape[0], dtype="complex128")
+
+
+stateprep_defaults = {"objective": objectives.StateprepObjective()}
+stateprep_smart_defaults = {"target": stateprep_target, "initial_state": stateprep_initial_state}

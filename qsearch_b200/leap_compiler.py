@@ -10,7 +10,7 @@ from timeit import default_timer as timer
 
 import numpy as np
 
-from .compiler import Compiler, _better, _frontier, _qudits_of, _solve_root
+from .compiler import Compiler, _better, _frontier, _qudits_of, _require_target, _solve_root
 from .gates import ProductGate
 
 
@@ -30,7 +30,7 @@ class SubCompiler(Compiler):
 
     def compile(self, options=None):
         options = self.options.updated(options) if options is not None else self.options.copy()
-        options.make_required("target")
+        _require_target(options)
         logger, h, depth_limit = options.logger, options.heuristic, options.weight_limit
         n = _qudits_of(options)
         gateset = options.gateset
@@ -88,7 +88,7 @@ class LeapCompiler(Compiler):
 
     def compile(self, options=None):
         options = self.options.updated(options) if options is not None else self.options.copy()
-        options.make_required("target")
+        _require_target(options)
         logger = options.logger
         start = timer()
         n = _qudits_of(options)

@@ -12,8 +12,14 @@ from .backends import program_for
 
 
 class Objective:
+    has_residuals = True  # False: gen_error_residuals* return None, so default_solver avoids least squares (solvers.py:51-52)
+
     def gen_eval_func(self, circuit, options):
         return self.gen_error_func(circuit, options)
+
+    def device_target(self, options):
+        """The N x N complex matrix the device kernels contract the circuit unitary with."""
+        return np.ascontiguousarray(options.target, dtype="complex128")
 
     def __eq__(self, other):
         return type(self) == type(other)
@@ -59,6 +65,51 @@ class MatrixDistanceObjective(Objective):
     # batched form used by the search loop: distances of many (circuit, parameters) pairs in one launch
     def eval_batch(self, circuits, parameter_vectors, options):
         gps = [program_for(c) for c in circuits]
-        T = np.asarray(options.target, dtype="complex128")
+        T = self.device_target(options)
         flat = np.concatenate([np.asarray(v, dtype="float64").ravel() for v in parameter_vectors]) if gps else np.zeros(0)
         return _lib.get_library().eval_distance(gps, np.arange(len(gps), dtype="int32"), flat, T)
+
+
+class StateprepObjective(Objective):
+    """State preparation (reference: qsearch/objectives.py:63-101; comparison.distance_with_initial_state / _jac,
+    comparison.py:114-123): ``s = <A a | U b>`` with a = ``options.target_state``, b = ``options.initial_state``,
+    A = ``options.target``; ``f = 1 - |s|`` and ``df/dv_k = -(Re s Re s_k + Im s Im s_k)/|s|``, ``s_k = <A a | J_k b>``.
+
+    On the device this is the Hilbert-Schmidt kernel with a rank-one matrix in the target slot:
+    ``conj(s) = sum_ij (A a)_i conj(b_j) conj(U_ij) = (1/N) sum_ij T'_ij conj(U_ij)`` with ``T' = N (A a) b^dagger``, so
+    ``1 - |sum T' . conj(U)|/N = 1 - |s|`` and the gradient formula of comparison.py:37-55 applied to ``T'`` is the one
+    above (the kernels never assume that the matrix in the target slot is unitary).  Like the reference it has no
+    residual form (objectives.py:81-101 return None), so the default solver for it is BFGS_Jac_Solver."""
+    has_residuals = False
+
+    def device_target(self, options):
+        a = np.asarray(options.target_state, dtype="complex128").ravel()
+        b = np.asarray(options.initial_state, dtype="complex128").ravel()
+        A = np.asarray(options.target, dtype="complex128")
+        if A.shape != (a.size, a.size) or b.size != a.size:
+            raise ValueError("target_state, initial_state and target must have matching sizes")
+        return np.ascontiguousarray(a.size * np.outer(A @ a, np.conj(b)))
+
+    def gen_error_func(self, circuit, options):
+        gp, T = program_for(circuit), self.device_target(options)
+
+        def generated_error_func(parameters):
+            return float(_lib.get_library().eval_distance([gp], [0], parameters, T)[0])
+        return generated_error_func
+
+    def gen_error_jac(self, circuit, options):
+        gp, T = program_for(circuit), self.device_target(options)
+
+        def generated_error_jac(parameters):
+            f, g = _lib.get_library().eval_hs_grad([gp], [0], parameters, T)
+            return float(f[0]), g
+        return generated_error_jac
+
+    def gen_error_residuals(self, circuit, options):
+        return None
+
+    def gen_error_residuals_jac(self, circuit, options):
+        return None
+
+    def eval_batch(self, circuits, parameter_vectors, options):
+        return MatrixDistanceObjective.eval_batch(self, circuits, parameter_vectors, options)

@@ -13,7 +13,7 @@ from timeit import default_timer as timer
 
 import numpy as np
 
-from .compiler import Compiler, _better, _frontier, _qudits_of, _solve_root
+from .compiler import Compiler, _better, _frontier, _qudits_of, _require_target, _solve_root
 from .gates import ProductGate
 
 
@@ -73,7 +73,7 @@ class LEAPReoptimizing_PostProcessor(Compiler, PostProcessor):
 
     def compile(self, options=None):
         options = self.options.updated(options) if options is not None else self.options.copy()
-        options.make_required("target")
+        _require_target(options)
         logger = options.logger
         window = options.weight_limit if "weight_limit" in options and options.weight_limit else options.reoptimize_size
         start = timer()

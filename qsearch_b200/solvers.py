@@ -19,7 +19,17 @@ from .backends import program_for
 
 
 def _target_of(options):
+    """Matrix for the target slot of the kernels: ``options.target``, or what the objective derives from it
+    (StateprepObjective: the rank-one matrix N (A a) b^dagger, objectives.py)."""
+    obj = options.objective if "objective" in options else None
+    if obj is not None and hasattr(obj, "device_target"):
+        return obj.device_target(options)
     return np.ascontiguousarray(options.target, dtype="complex128")
+
+
+def _has_residuals(options):
+    obj = options.objective if "objective" in options else None
+    return getattr(obj, "has_residuals", True)
 
 
 def _tolerances(options):
@@ -105,6 +115,10 @@ class LeastSquares_Jac_Solver(Solver):
         self.max_iters = int(max_iters)
 
     def _solve_opts(self, options):
+        if not _has_residuals(options):
+            # the reference's least-squares solver silently ignores the objective here (solvers.py:150); fail loudly
+            raise ValueError("LeastSquares_Jac_Solver needs an objective with a residual form; {} has none".format(
+                type(options.objective).__name__))
         o = _tolerances(options)
         o["max_iters"] = self.max_iters
         return o
@@ -196,6 +210,9 @@ class MultiStart_Solver(NaiveMultiStart_Solver):
 
 
 def default_solver(options=None):
-    """The reference picks the least-squares solver whenever the gateset has Jacobians (solvers.py:19-86); every gate
-    the lowering accepts has one on the device, so that is always the choice here."""
+    """The reference picks the least-squares solver whenever the gateset has Jacobians and the objective has a residual
+    form, else BFGS when it has a gradient (solvers.py:19-86).  Every gate the lowering accepts has a device Jacobian, so
+    the choice only depends on the objective (StateprepObjective has no residuals, objectives.py:81-101)."""
+    if options is not None and not _has_residuals(options):
+        return BFGS_Jac_Solver()
     return LeastSquares_Jac_Solver()
