@@ -84,8 +84,8 @@ class SearchCompiler(Compiler):
         branching = gateset.branching_factor(n)
         root = initial_layer if isinstance(initial_layer, ProductGate) else ProductGate(initial_layer)
         if branching <= 0:
-            x, _ = _solve_root(root, options)
-            return {"structure": root, "parameters": x}
+            x, value = _solve_root(root, options)
+            return {"structure": root, "parameters": np.asarray(x), "distance": value, "weight": 0}
         parallel = options.parallelizer(options)
         beams = int(options.beams)
         if beams < 1:
@@ -97,7 +97,7 @@ class SearchCompiler(Compiler):
             best_pair, best_weight = (root, x), 0
             logger.logprint("New best! {} at weight 0".format(best_value))
             if weight_limit == 0:
-                return {"structure": root, "parameters": x}
+                return {"structure": root, "parameters": np.asarray(x), "distance": best_value, "weight": 0}
             queue = [(h(root, x, 0, options, value=best_value), 0, best_value, -1, x, root)]
             tiebreaker = 0
             while queue and timer() - start <= options.timeout and best_value >= options.threshold:
