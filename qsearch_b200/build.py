@@ -41,6 +41,16 @@ def build_cuda(force=False, verbose=False):
     return LIB
 
 
+def build_exp(verbose=False):
+    """DEVELOPER TOOL: evaluation kernels only (no solver kernels), for quick A/B runs of a kernel change through
+    QSB_LIB_PATH (tools/prof_case.py).  Never loaded by the product."""
+    out = os.path.join(HERE, "libqsb200_exp.so")
+    nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+    cmd = [nvcc] + NVCC_FLAGS + ["-DQSB_EXPERIMENT"] + (["-Xptxas", "-v"] if verbose else []) + ["-o", out, os.path.join(CSRC, "qsb_api.cu")]
+    subprocess.run(cmd, check=True)
+    return out
+
+
 def build_emu(force=False):
     """TEST INFRASTRUCTURE: compile the same .cu sources for the host with tests/emu/cuda_emu.h."""
     hdr = os.path.join(ROOT, "tests", "emu", "cuda_emu.h")
@@ -54,7 +64,9 @@ def build_emu(force=False):
 
 
 if __name__ == "__main__":
-    if "--emu" in sys.argv:
+    if "--exp" in sys.argv:
+        print(build_exp(verbose="-v" in sys.argv))
+    elif "--emu" in sys.argv:
         print(build_emu(force="--force" in sys.argv))
     else:
         print(build_cuda(force="--force" in sys.argv, verbose="-v" in sys.argv))

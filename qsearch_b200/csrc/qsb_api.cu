@@ -11,7 +11,9 @@
 #include "qsb_host.h"
 #include "qsb_generic.cuh"
 #include "qsb_warp.cuh"
+#ifndef QSB_EXPERIMENT  // QSB_EXPERIMENT: developer build of the evaluation kernels only (python -m qsearch_b200.build --exp)
 #include "qsb_lm2.cuh"
+#endif
 #include "qsb_launch.h"
 
 // ---------------------------------------------------------------------------- errors
@@ -406,6 +408,9 @@ extern "C" int qsb_batch_fetch(qsb_batch* b, int what, double* a, double* bb, do
 }
 
 // QSB_RUN_LMSYS: tensor-core kernels only (one-qubit leaves + CNOT, 3..5 qubits)
+#ifdef QSB_EXPERIMENT
+static int qsb_launch_lmsys(qsb_batch*, const QsbBatchArgs&, cudaStream_t, int) { return qsb_fail(QSB_ERR_UNSUPPORTED, "experiment build: no solver kernels"); }
+#else
 template <int NQ>
 static int qsb_launch_lmsys_nq(qsb_batch* b, const QsbBatchArgs& args, cudaStream_t st, int sm_count) {
   const size_t NN = (size_t)1 << (2 * NQ), maxP = (size_t)args.max_params;
@@ -446,6 +451,7 @@ static int qsb_launch_lmsys(qsb_batch* b, const QsbBatchArgs& args, cudaStream_t
     default: return qsb_launch_lmsys_nq<5>(b, args, st, sm_count);
   }
 }
+#endif
 
 int qsb_batch_enqueue(qsb_batch* b, int what, int first, int count) {
   const QsbDevice& d = b->ctx->devs[b->slot];
@@ -628,5 +634,12 @@ extern "C" int qsb_eval_residuals_jac(qsb_ctx* ctx, int n_programs, const qsb_pr
   return host_eval(j);
 }
 
+#ifndef QSB_EXPERIMENT
 #include "qsb_solvers.inc"
+#else
+extern "C" int qsb_solve_lm(qsb_ctx*, int, const qsb_program* const*, int, const int32_t*, const double*, const double*,
+                            const qsb_solver_opts*, double*, double*, int32_t*, int32_t*) { return qsb_fail(QSB_ERR_UNSUPPORTED, "experiment build: no solver kernels"); }
+extern "C" int qsb_solve_lbfgs(qsb_ctx*, int, const qsb_program* const*, int, const int32_t*, const double*, const double*,
+                               const qsb_solver_opts*, double*, double*, int32_t*, int32_t*) { return qsb_fail(QSB_ERR_UNSUPPORTED, "experiment build: no solver kernels"); }
+#endif
 #include "qsb_peak.inc"

@@ -424,6 +424,48 @@ QSB_DEVICE void qsb_dmma_half(double (&cr)[TT][TT][2], double (&ci)[TT][TT][2], 
   }
 }
 
+#ifdef QSB_EMU
+static inline double qsb_neg(double x) { return -x; }
+#else
+// sign flip on the integer pipe (the FP64 pipe is the busy one)
+__device__ __forceinline__ double qsb_neg(double x) { return __hiloint2double(__double2hiint(x) ^ (int)0x80000000, __double2loint(x)); }
+#endif
+
+// Projector-type derivatives need no factor arithmetic.  With P1 = |1><1| on the gate's qubit:
+//   output side  dg = c g + i P1 g   (U3 phi: c = 0; XZXZ v1: c = -i/2, since Rz' = -i/2 Z Rz and Z = I - 2 P1)
+//                                     ->  K = c V + i S[:, k1] (g X)[k1, :]     with X BEFORE the peel
+//   input side   dg = c g + i g P1   (U3 lambda: c = 0)
+//                                     ->  K = c V + i (S g)[:, k1] X[k1, :]     with S AFTER its update
+// acc += i S[:, k1] X[k1, :] over the half index range (k1 = the k with the gate's bit set)
+template <int KS, int TT, int KB>
+QSB_DEVICE void qsb_dmma_half_raw(double (&cr)[TT][TT][2], double (&ci)[TT][TT][2], const QsbFrag<KS, TT>& S,
+                                  const QsbFrag<KS, TT>& X) {
+#pragma unroll
+  for (int ks = 0; ks < KS; ++ks) {
+    if (!(ks & KB)) continue;
+    double nxr[TT], nxi[TT];
+#pragma unroll
+    for (int o = 0; o < TT; ++o) { nxr[o] = qsb_neg(X.re[ks][o]); nxi[o] = qsb_neg(X.im[ks][o]); }
+    // (sr + i si) i (xr + i xi):  re = -sr xi - si xr,  im = sr xr - si xi
+#pragma unroll
+    for (int nt = 0; nt < TT; ++nt)
+#pragma unroll
+      for (int mt = 0; mt < TT; ++mt) qsb_dmma884(cr[mt][nt][0], cr[mt][nt][1], S.re[ks][mt], nxi[nt]);
+#pragma unroll
+    for (int nt = 0; nt < TT; ++nt)
+#pragma unroll
+      for (int mt = 0; mt < TT; ++mt) qsb_dmma884(ci[mt][nt][0], ci[mt][nt][1], S.re[ks][mt], X.re[ks][nt]);
+#pragma unroll
+    for (int nt = 0; nt < TT; ++nt)
+#pragma unroll
+      for (int mt = 0; mt < TT; ++mt) qsb_dmma884(cr[mt][nt][0], cr[mt][nt][1], S.im[ks][mt], nxr[nt]);
+#pragma unroll
+    for (int nt = 0; nt < TT; ++nt)
+#pragma unroll
+      for (int mt = 0; mt < TT; ++mt) qsb_dmma884(ci[mt][nt][0], ci[mt][nt][1], S.im[ks][mt], nxi[nt]);
+  }
+}
+
 // V = S X (dense, all k-steps)
 template <int KS, int TT>
 QSB_DEVICE void qsb_dmma_full(double (&cr)[TT][TT][2], double (&ci)[TT][TT][2], const QsbFrag<KS, TT>& S,
@@ -453,61 +495,82 @@ QSB_DEVICE void qsb_dmma_full(double (&cr)[TT][TT][2], double (&ci)[TT][TT][2], 
   }
 }
 
+// One derivative: K = (with_v ? W : 0) + half-size product, written to o.  RAW: projector type (qsb_dmma_half_raw), else
+// the general rank-one form ab = {rho, (row, has_v), b0, b1}.
+template <int NQ, int WHAT, int KB, bool RAW>
+QSB_DEVICE void qsb_jac_param(const QsbFrag<(1 << NQ) / 4, QsbWarpGeom<NQ>::TT>& X, const QsbFrag<(1 << NQ) / 4, QsbWarpGeom<NQ>::TT>& S,
+                              const cplx* ab, bool with_v, const double* wtile, int r0, int c0, int lane, double* o) {
+  using G = QsbWarpGeom<NQ>;
+  constexpr int N = G::N, NN = G::NN, KS = G::KS, TT = G::TT;
+  const int g = lane >> 2, t = lane & 3;
+  double cr[TT][TT][2], ci[TT][TT][2];
+  if (with_v) {  // generator-type parameter: start from W = -i/2 V
+    const double2* w2 = reinterpret_cast<const double2*>(wtile);
+#pragma unroll
+    for (int mt = 0; mt < TT; ++mt)
+#pragma unroll
+      for (int nt = 0; nt < TT; ++nt) {
+        const int i = (mt * TT + nt) * 2;
+        const double2 a = w2[i * 32 + lane], b = w2[(i + 1) * 32 + lane];
+        cr[mt][nt][0] = a.x; cr[mt][nt][1] = a.y; ci[mt][nt][0] = b.x; ci[mt][nt][1] = b.y;
+      }
+  } else {
+#pragma unroll
+    for (int mt = 0; mt < TT; ++mt)
+#pragma unroll
+      for (int nt = 0; nt < TT; ++nt) { cr[mt][nt][0] = cr[mt][nt][1] = ci[mt][nt][0] = ci[mt][nt][1] = 0.0; }
+  }
+  if (RAW) qsb_dmma_half_raw<KS, TT, KB>(cr, ci, S, X);
+  else qsb_dmma_half<KS, TT, KB>(cr, ci, S, X, ab);
+#pragma unroll
+  for (int mt = 0; mt < TT; ++mt)
+#pragma unroll
+    for (int nt = 0; nt < TT; ++nt) {
+      const int e = (r0 + 8 * mt + g) * N + c0 + 8 * nt + 2 * t;
+      if (WHAT == QSB_RUN_MATJAC) {
+        *reinterpret_cast<double2*>(o + 2 * e) = make_double2(cr[mt][nt][0], ci[mt][nt][0]);
+        *reinterpret_cast<double2*>(o + 2 * e + 2) = make_double2(cr[mt][nt][1], ci[mt][nt][1]);
+      } else {
+        *reinterpret_cast<double2*>(o + e) = make_double2(cr[mt][nt][0], cr[mt][nt][1]);
+        *reinterpret_cast<double2*>(o + NN + e) = make_double2(ci[mt][nt][0], ci[mt][nt][1]);
+      }
+    }
+}
+
 // One parameterised (or constant) one-qubit op of the backward sweep whose qubit sits at k-step bit KB:
-// X <- g^dagger X (peel), K_k = c V + (S a_k)(b_k^T X) for its parameters, S <- S g.
+// X <- g^dagger X (peel), K_k = c V + (S a_k)(b_k^T X) for its parameters, S <- S g.  The two leaves of the search
+// gatesets take the projector shortcut for three of their five parameters, as straight-line code (a version that looped
+// over stages and table flags lost 30 % to its extra branches, profiles/r1/ah_*):
+//   U3    phi on (S, g X) | peel | theta (general) | S <- S g | lambda on (S g, X)
+//   XZXZ  v1 on (S, g X)  | peel | v0 (general)    | S <- S g
+// Enabled for n = 5 only (A/B on the B200, profiles/r1/ai_ab.log: n = 5 +11 %; n = 4 -13 %: its hot loop just fits the
+// 32 KB instruction cache without the two extra product sites and no longer does with them).
 template <int NQ, int WHAT, int KB>
 QSB_DEVICE void qsb_jac_op(QsbFrag<(1 << NQ) / 4, QsbWarpGeom<NQ>::TT>& X, QsbFrag<(1 << NQ) / 4, QsbWarpGeom<NQ>::TT>& S,
                            const qsb_op& op, int np, const cplx* gtab, const double* wtile, int r0, int c0, int lane,
                            bool update_s, double* oj) {
   using G = QsbWarpGeom<NQ>;
-  constexpr int N = G::N, NN = G::NN, KS = G::KS, TT = G::TT;
-  const int g = lane >> 2, t = lane & 3;
+  constexpr int NN = G::NN, KS = G::KS, TT = G::TT;
+  constexpr bool PROJ = NQ >= 5;
+  const bool u3 = PROJ && op.opcode == QSB_OP_U3, fast = PROJ && (u3 || op.opcode == QSB_OP_XZXZ);
   cplx m[4];
   qsb_warp_gate(op, gtab, 0, m);
+  if (fast) qsb_jac_param<NQ, WHAT, KB, true>(X, S, nullptr, !u3, wtile, r0, c0, lane, oj + (size_t)2 * NN);
   {
     cplx md[4] = {m[0], m[1], m[2], m[3]};
     qsb_dagger2x2(md);
     qsb_mix_thread<KS, TT, KB>(X, md);  // X = R_j T^dagger
   }
-  for (int k = 0; k < np; ++k) {
-    double cr[TT][TT][2], ci[TT][TT][2];
+  const int ngen = fast ? 1 : np;
+  for (int k = 0; k < ngen; ++k) {
     const cplx* ab = gtab + 4 * (op.reserved + 1 + k);
-    if (ab[1].y != 0.0) {  // generator-type parameter: start from W = -i/2 V
-      const double2* w2 = reinterpret_cast<const double2*>(wtile);
-#pragma unroll
-      for (int mt = 0; mt < TT; ++mt)
-#pragma unroll
-        for (int nt = 0; nt < TT; ++nt) {
-          const int i = (mt * TT + nt) * 2;
-          const double2 a = w2[i * 32 + lane], b = w2[(i + 1) * 32 + lane];
-          cr[mt][nt][0] = a.x; cr[mt][nt][1] = a.y; ci[mt][nt][0] = b.x; ci[mt][nt][1] = b.y;
-        }
-    } else {
-#pragma unroll
-      for (int mt = 0; mt < TT; ++mt)
-#pragma unroll
-        for (int nt = 0; nt < TT; ++nt) { cr[mt][nt][0] = cr[mt][nt][1] = ci[mt][nt][0] = ci[mt][nt][1] = 0.0; }
-    }
-    qsb_dmma_half<KS, TT, KB>(cr, ci, S, X, ab);
-    double* o = oj + (size_t)k * 2 * NN;
-#pragma unroll
-    for (int mt = 0; mt < TT; ++mt)
-#pragma unroll
-      for (int nt = 0; nt < TT; ++nt) {
-        const int e = (r0 + 8 * mt + g) * N + c0 + 8 * nt + 2 * t;
-        if (WHAT == QSB_RUN_MATJAC) {
-          *reinterpret_cast<double2*>(o + 2 * e) = make_double2(cr[mt][nt][0], ci[mt][nt][0]);
-          *reinterpret_cast<double2*>(o + 2 * e + 2) = make_double2(cr[mt][nt][1], ci[mt][nt][1]);
-        } else {
-          *reinterpret_cast<double2*>(o + e) = make_double2(cr[mt][nt][0], cr[mt][nt][1]);
-          *reinterpret_cast<double2*>(o + NN + e) = make_double2(ci[mt][nt][0], ci[mt][nt][1]);
-        }
-      }
+    qsb_jac_param<NQ, WHAT, KB, false>(X, S, ab, ab[1].y != 0.0, wtile, r0, c0, lane, oj + (size_t)k * 2 * NN);
   }
-  if (update_s) {
+  if (update_s || u3) {
     qsb_transpose2x2(m);
     qsb_mix_thread<KS, TT, KB>(S, m);  // S <- S g_j
   }
+  if (u3) qsb_jac_param<NQ, WHAT, KB, true>(X, S, nullptr, false, wtile, r0, c0, lane, oj + (size_t)4 * NN);
 }
 
 // doubles of per-warp shared memory qsb_warp_jac_range needs for W = -i/2 V (one C-fragment tile, re and im)
