@@ -174,37 +174,50 @@ QSB_DEVICE double qsb_hs_finish(const QsbDevProgram& P, const cplx* gtab, const 
 }
 
 // ---------------------------------------------------------------------------- batch kernel (QSB_RUN_HS)
-// 4 warps per CTA; an instance takes N/8 of them, so a CTA works on 4 / (N/8) instances per round.
+// One CTA = the N/8 warps of ONE instance: the instance comes from blockIdx alone and the warp index only selects the column
+// block, so the compiler sees uniform control flow and emits plain SHFLs (with several instances per CTA every shuffle of
+// the trace reductions was wrapped in WARPSYNC.COLLECTIVE / ENDCOLLECTIVE; see qsb_k_warp_jac).
 template <int NQ>
 struct QsbHsGeom {
   static constexpr int NCB = (1 << NQ) / 8;  // column blocks = warps per instance
-  static constexpr int IPC = 4 / NCB;        // instances per CTA
+  static constexpr int IPC = 1;              // instances per CTA
 };
 
-static inline size_t qsb_hs_slot_doubles(int nq, int max_ops, int max_params) {
+QSB_HOST_DEVICE size_t qsb_hs_slot_doubles(int nq, int max_ops, int max_params) {
   const size_t ncb = ((size_t)1 << nq) / 8;
-  return 8 * (size_t)(max_ops + max_params) + 2 * (size_t)max_params + 2 * ncb + 8 * (size_t)max_ops * ncb + 2;
+  return 8 * (size_t)(max_ops + max_params) + 2 * (size_t)max_params + 2 * ncb + 8 * (size_t)max_ops * ncb + 2 +
+         3 * (size_t)(max_ops + (max_ops & 1));  // ... + the staged ops
 }
 
 template <int NQ>
-QSB_GLOBAL __launch_bounds__(128) qsb_k_warp_hs(QsbBatchArgs a) {
+QSB_GLOBAL __launch_bounds__(32 * QsbHsGeom<NQ>::NCB) qsb_k_warp_hs(QsbBatchArgs a) {
   using G = QsbHsGeom<NQ>;
   QSB_DYN_SMEM(smem_raw);
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int sub = warp / G::NCB, cb = warp % G::NCB, tid_i = cb * 32 + lane, nth = G::NCB * 32;
-  size_t slot = 8 * (size_t)(a.max_ops + a.max_params) + 2 * (size_t)a.max_params + 2 * G::NCB + 8 * (size_t)a.max_ops * G::NCB + 2;
+  const int lane = threadIdx.x & 31;
+  const int sub = 0, cb = G::NCB == 1 ? 0 : (int)(threadIdx.x >> 5), tid_i = threadIdx.x, nth = G::NCB * 32;
+  size_t slot = qsb_hs_slot_doubles(NQ, a.max_ops, a.max_params);
   slot = (slot + 1) & ~(size_t)1;
   cplx* gtab = (cplx*)((double*)smem_raw + (size_t)sub * slot);
   double* trig = (double*)(gtab + (size_t)4 * (a.max_ops + a.max_params));
   double* trp = trig + 2 * a.max_params;
   double* cpart = trp + 2 * G::NCB;
+  // the ops of the program worked on last, in shared memory: loads through the program's own (generic) pointer count as
+  // divergent for the compiler, loads from shared memory at a uniform address do not
+  qsb_op* sops = (qsb_op*)(cpart + 8 * (size_t)a.max_ops * G::NCB + 2);
+  int staged = -1;
   const long long p_base = a.param_off[a.first];
   const int per_round = gridDim.x * G::IPC;
   for (int base = 0; base < a.count; base += per_round) {
     const int li = base + blockIdx.x * G::IPC + sub;
     const bool valid = li < a.count;
     const int inst = a.first + (valid ? li : 0);
-    const QsbDevProgram P = a.progs[a.prog_idx[inst]];
+    const int pi = a.prog_idx[inst];
+    QsbDevProgram P = a.progs[pi];
+    if (pi != staged) {  // the previous round ended with a barrier: nobody reads the old ops any more
+      for (int e = tid_i; e < P.n_ops * 6; e += nth) ((int32_t*)sops)[e] = ((const int32_t*)P.ops)[e];
+      staged = pi;
+    }
+    P.ops = sops;
     if (valid) {
       const double* x = a.params + a.param_off[inst];
       for (int p = tid_i; p < P.n_params; p += nth) {

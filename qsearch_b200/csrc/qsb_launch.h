@@ -81,7 +81,7 @@ static inline int qsb_launch_generic(qsb_batch* b, int what, const QsbBatchArgs&
 }
 
 // ---------------------------------------------------------------------------- warp (register / DMMA) kernels
-// 4 warps per CTA, one instance tile per warp, grid = SMs x resident CTAs (persistent warps stride over the items).
+// one CTA per instance (1 warp, n = 5: 4 quadrant warps), grid = SMs x resident CTAs (persistent CTAs stride over the instances).
 #define QSB_WARP_NOFIT 1  // internal: the program's tables do not fit the warp kernel's shared memory -> use the interpreter
 
 template <class K>
@@ -98,13 +98,12 @@ static inline int qsb_resident_ctas(K kernel, int threads, size_t smem) {
 
 template <int NQ, int WHAT>
 static int qsb_launch_warp_kernel(const QsbBatchArgs& args, cudaStream_t st, int sm_count) {
-  constexpr int threads = 128, wpb = threads / 32;
-  const size_t smem = (size_t)wpb * qsb_warp_jac_smem_doubles(args.max_ops, args.max_params) * sizeof(double) + 16;
+  constexpr int wpb = QsbWarpGeom<NQ>::WARPS, threads = 32 * wpb;  // one CTA = the warps of one instance
+  const size_t smem = (qsb_warp_jac_smem_doubles(args.max_ops, args.max_params) + (size_t)(wpb - 1) * QSB_WTILE_DOUBLES) * sizeof(double) + 16;
   if (smem > 200 * 1024) return QSB_WARP_NOFIT;
   int rc = qsb_prepare_kernel(qsb_k_warp_jac<NQ, WHAT>, smem);
   if (rc) return rc;
-  const long long items = (long long)args.count * QsbWarpGeom<NQ>::WARPS;
-  const long long want = (items + wpb - 1) / wpb;
+  const long long want = args.count;
   const int resident = sm_count * qsb_resident_ctas(qsb_k_warp_jac<NQ, WHAT>, threads, smem);
   const int grid = (int)std::max<long long>(1, std::min<long long>(want, resident));
   QSB_LAUNCH((qsb_k_warp_jac<NQ, WHAT>), grid, threads, smem, st, args);
@@ -119,7 +118,7 @@ static inline bool qsb_warp_path(const qsb_batch* b, int what) {
 
 template <int NQ>
 static int qsb_launch_warp_hs(const QsbBatchArgs& args, cudaStream_t st, int sm_count) {
-  constexpr int threads = 128, ipc = QsbHsGeom<NQ>::IPC;
+  constexpr int threads = 32 * QsbHsGeom<NQ>::NCB, ipc = QsbHsGeom<NQ>::IPC;
   size_t slot = qsb_hs_slot_doubles(NQ, args.max_ops, args.max_params);
   slot = (slot + 1) & ~(size_t)1;
   const size_t smem = ipc * slot * sizeof(double) + 16;

@@ -290,17 +290,6 @@ QSB_DEVICE void qsb_warp_gate(const qsb_op& op, const cplx* gtab, int which, cpl
   g[0] = t[0]; g[1] = t[1]; g[2] = t[2]; g[3] = t[3];
 }
 
-// (cos, sin) of the scaled angle of every parameter, in parameter order (one parameter per lane and round)
-QSB_DEVICE void qsb_warp_trig(const QsbDevProgram& P, const double* x, double* trig, int lane) {
-  __syncwarp();
-  for (int p = lane; p < P.n_params; p += 32) {
-    double s, c;
-    sincos(P.pscale[p] * x[p], &s, &c);
-    trig[2 * p] = c; trig[2 * p + 1] = s;
-  }
-  __syncwarp();
-}
-
 // ---------------------------------------------------------------------------- dynamic layout of the contracted index
 // The contracted index k only has to be laid out the SAME way in X (rows) and S (columns), so the kernel is free to
 // move the bit of the qubit it is about to work on from a lane position (0..1) into a k-step position (>= 2), where the
@@ -691,49 +680,55 @@ QSB_DEVICE void qsb_warp_jac_range(const QsbDevProgram& P, const double* target,
   }
 }
 
-template <int NQ, int WHAT>
-QSB_DEVICE void qsb_warp_jac(const QsbDevProgram& P, const double* x, const double* target, double* trig, cplx* gtab,
-                             double* wtile, int tile, int lane, double* out_u, double* out_j) {
-  qsb_warp_trig(P, x, trig, lane);
-  qsb_fill_gates(P, trig, gtab, lane, 32, true);
-  __syncwarp();
-  qsb_warp_jac_range<NQ, WHAT>(P, target, gtab, wtile, tile, lane, 0, P.n_ops, out_u, out_j);
-}
-
-// doubles of shared memory per warp of qsb_k_warp_jac
+// doubles of shared memory of a one-warp CTA of qsb_k_warp_jac (tables + one W tile; every further warp adds a W tile)
 QSB_HOST_DEVICE size_t qsb_warp_jac_smem_doubles(int max_ops, int max_params) {
   return QSB_WTILE_DOUBLES + (size_t)8 * (max_ops + max_params) + 2 * (size_t)(max_params + (max_params & 1)) + 3 * (size_t)(max_ops + (max_ops & 1));
 }
 
+// CTA = the WARPS warps of ONE instance (n <= 4: a single warp; n = 5: the four quadrant warps).  The instance comes from
+// blockIdx alone and the warp index only selects the tile (addresses), so every branch of the sweep depends on values
+// the compiler's divergence analysis can see are uniform.  With the work item derived from threadIdx.x >> 5 every branch
+// counted as potentially divergent and each 32-bit shuffle of the bit exchanges was wrapped in a WARPSYNC.COLLECTIVE /
+// ENDCOLLECTIVE sequence with moves through fixed registers: a third of the kernel's code, which has to stream through a
+// 32 KB instruction cache.  The quadrant warps of n = 5 stay in one CTA: they run the same path in step and share
+// every instruction fetch (one-warp CTAs were 22 % slower there, profiles/r1/aj_ab.log, ak_*).
 template <int NQ, int WHAT>
-QSB_GLOBAL __launch_bounds__(128) qsb_k_warp_jac(QsbBatchArgs a) {
+QSB_GLOBAL __launch_bounds__(32 * QsbWarpGeom<NQ>::WARPS, (NQ == 4 ? 12 : NQ == 5 ? 2 : 1)) qsb_k_warp_jac(QsbBatchArgs a) {
   using G = QsbWarpGeom<NQ>;
   constexpr int NN = G::NN;
   QSB_DYN_SMEM(smem_raw);
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpb = blockDim.x >> 5;
-  // per warp: W tile, gate table [max_ops + max_params][4] complex, the sin/cos table [2 max_params], and the ops of the
-  // program the warp worked on last (every sweep decodes them; from shared memory that is a short-latency load)
-  const size_t per_warp = qsb_warp_jac_smem_doubles(a.max_ops, a.max_params);
-  double* wtile = (double*)smem_raw + (size_t)warp * per_warp;
-  cplx* gtab = (cplx*)(wtile + QSB_WTILE_DOUBLES);
+  const int lane = threadIdx.x & 31, warp = G::WARPS == 1 ? 0 : (int)(threadIdx.x >> 5);
+  // per CTA: gate table [max_ops + max_params][4] complex, the sin/cos table [2 max_params] and the ops of the program
+  // worked on last (every sweep decodes them; from shared memory that is a short-latency load), built by all threads and
+  // shared by the warps (one address for the whole CTA: the values stay uniform for the compiler); per warp: the W tile
+  const size_t tables = qsb_warp_jac_smem_doubles(a.max_ops, a.max_params) - QSB_WTILE_DOUBLES;
+  cplx* gtab = (cplx*)smem_raw;
   double* trig = (double*)(gtab + (size_t)4 * (a.max_ops + a.max_params));
   qsb_op* sops = (qsb_op*)(trig + 2 * (size_t)(a.max_params + (a.max_params & 1)));
+  double* wtile = (double*)smem_raw + tables + (size_t)warp * QSB_WTILE_DOUBLES;
+  const int tid = threadIdx.x, nth = 32 * G::WARPS;
   int staged = -1;
   const long long p_base = a.param_off[a.first];
-  const long long items = (long long)a.count * G::WARPS;
-  for (long long it = (long long)blockIdx.x * wpb + warp; it < items; it += (long long)gridDim.x * wpb) {
-    const int li = (int)(it / G::WARPS), tile = (int)(it % G::WARPS);
+  for (int li = blockIdx.x; li < a.count; li += gridDim.x) {
     const int inst = a.first + li;
     const int pi = a.prog_idx[inst];
     QsbDevProgram P = a.progs[pi];
+    const double* x = a.params + a.param_off[inst];
+    __syncthreads();  // the tables of the previous instance are no longer read
     if (pi != staged) {
-      __syncwarp();
-      for (int e = lane; e < P.n_ops * 6; e += 32) ((int32_t*)sops)[e] = ((const int32_t*)P.ops)[e];
+      for (int e = tid; e < P.n_ops * 6; e += nth) ((int32_t*)sops)[e] = ((const int32_t*)P.ops)[e];
       staged = pi;
-      __syncwarp();
     }
+    for (int p = tid; p < P.n_params; p += nth) {  // (cos, sin) of the scaled angle of every parameter
+      double sn, cs;
+      sincos(P.pscale[p] * x[p], &sn, &cs);
+      trig[2 * p] = cs; trig[2 * p + 1] = sn;
+    }
+    __syncthreads();
     P.ops = sops;
-    qsb_warp_jac<NQ, WHAT>(P, a.params + a.param_off[inst], a.target, trig, gtab, wtile, tile, lane,
-                           a.out_a + (size_t)li * 2 * NN, a.out_b + (size_t)(a.param_off[inst] - p_base) * 2 * NN);
+    qsb_fill_gates(P, trig, gtab, tid, nth, true);
+    __syncthreads();
+    qsb_warp_jac_range<NQ, WHAT>(P, a.target, gtab, wtile, warp, lane, 0, P.n_ops,
+                                 a.out_a + (size_t)li * 2 * NN, a.out_b + (size_t)(a.param_off[inst] - p_base) * 2 * NN);
   }
 }
