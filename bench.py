@@ -280,7 +280,7 @@ def run_ours(args, rank, world, local_rank):
     # what the warp kernel really issues on the FP64 tensor pipe: P half-size complex products (N x N/2 x N, rank-one form
     # of the derivative) + one dense product for U T^dagger = (4 P + 8) N^3 flop per eval
     executed_dmma_tf = (n_inst / (kern_ms * 1e-3)) * (4.0 * P + 8.0) * (N ** 3) / 1e12
-    ncu_traffic = {4: 255639.0, 5: 1068130.0}.get(n)  # dram read+write bytes per eval: profiles/r1/u_ncu_full_resid_n{4,5}_warp.txt
+    ncu_traffic = {4: 255610.0, 5: 1068462.0}.get(n)  # dram read+write bytes per eval: profiles/r1/an_ncu_full_resid_n{4,5}_warp.txt
     line = {
         "metric": "objective+Jacobian evals/sec", "value": value, "unit": "evals/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": kern_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -300,8 +300,8 @@ def run_ours(args, rank, world, local_rank):
                               "second; gate structure lets the kernel execute fewer, so frac can exceed 1. Executed on the tensor pipe: "
                               "(4 P + 8) N^3 flop per eval (see executed); DFMA work shares the same FP64 pipe",
                      "executed": {"dmma_tflops": executed_dmma_tf, "frac_of_dmma_peak": executed_dmma_tf / dmma_peak if dmma_peak else None,
-                                  "ncu_dmma_pipe_active_pct": {4: 45.2, 5: 47.7}.get(n),
-                                  "ncu_fp64_dfma_pipe_active_pct": {4: 22.1, 5: 22.7}.get(n)},
+                                  "ncu_dmma_pipe_active_pct": {4: 44.9, 5: 54.2}.get(n),
+                                  "ncu_fp64_dfma_pipe_active_pct": {4: 21.9, 5: 19.3}.get(n)},
                      "traffic_note": "ncu dram bytes per eval (one --set full capture, profiles/r1) x instances of this launch",
                      "hbm": {"achieved": out_bytes / (kern_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
                              "frac": out_bytes / (kern_ms * 1e-3) / 1e9 / hbm_peak,

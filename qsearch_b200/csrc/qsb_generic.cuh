@@ -32,7 +32,18 @@ struct QsbBatchArgs {
   double* out_a;
   double* out_b;
   double* out_c;
+  int group = 0;  // warp kernels, persistent grid = SMs x group: CTAs per SM (see qsb_cta_first_instance); 0 = plain order
 };
+
+// First instance of a CTA of a persistent grid (stride gridDim.x).  CTAs are handed to the SMs round-robin, so with the
+// plain order the CTAs that share an SM work on instances that lie a whole SM count apart; this order gives the `group`
+// CTAs of one SM consecutive instances, which usually belong to the same circuit: the same code path in the shared 32 KB
+// instruction cache, and neighbouring output rows.  (Only the order changes: any CTA-to-SM placement gives correct results.)
+QSB_DEVICE int qsb_cta_first_instance(int group) {
+  if (group <= 1) return blockIdx.x;
+  const int nsm = gridDim.x / group;
+  return (int)(blockIdx.x % nsm) * group + (int)(blockIdx.x / nsm);
+}
 
 QSB_DEVICE int qsb_insert_zero_bit(int v, int sh) { return ((v >> sh) << (sh + 1)) | (v & ((1 << sh) - 1)); }
 

@@ -208,7 +208,7 @@ QSB_GLOBAL __launch_bounds__(32 * QsbHsGeom<NQ>::NCB) qsb_k_warp_hs(QsbBatchArgs
   const long long p_base = a.param_off[a.first];
   const int per_round = gridDim.x * G::IPC;
   for (int base = 0; base < a.count; base += per_round) {
-    const int li = base + blockIdx.x * G::IPC + sub;
+    const int li = base + qsb_cta_first_instance(a.group);  // IPC = 1
     const bool valid = li < a.count;
     const int inst = a.first + (valid ? li : 0);
     const int pi = a.prog_idx[inst];

@@ -104,9 +104,11 @@ static int qsb_launch_warp_kernel(const QsbBatchArgs& args, cudaStream_t st, int
   int rc = qsb_prepare_kernel(qsb_k_warp_jac<NQ, WHAT>, smem);
   if (rc) return rc;
   const long long want = args.count;
-  const int resident = sm_count * qsb_resident_ctas(qsb_k_warp_jac<NQ, WHAT>, threads, smem);
+  const int per_sm = qsb_resident_ctas(qsb_k_warp_jac<NQ, WHAT>, threads, smem), resident = sm_count * per_sm;
   const int grid = (int)std::max<long long>(1, std::min<long long>(want, resident));
-  QSB_LAUNCH((qsb_k_warp_jac<NQ, WHAT>), grid, threads, smem, st, args);
+  QsbBatchArgs a2 = args;
+  a2.group = grid == resident ? per_sm : 0;
+  QSB_LAUNCH((qsb_k_warp_jac<NQ, WHAT>), grid, threads, smem, st, a2);
   QSB_CUDA(cudaGetLastError());
   return QSB_OK;
 }
@@ -126,8 +128,11 @@ static int qsb_launch_warp_hs(const QsbBatchArgs& args, cudaStream_t st, int sm_
   int rc = qsb_prepare_kernel(qsb_k_warp_hs<NQ>, smem);
   if (rc) return rc;
   const int want = (args.count + ipc - 1) / ipc;
-  const int resident = sm_count * qsb_resident_ctas(qsb_k_warp_hs<NQ>, threads, smem);
-  QSB_LAUNCH((qsb_k_warp_hs<NQ>), std::max(1, std::min(want, resident)), threads, smem, st, args);
+  const int per_sm = qsb_resident_ctas(qsb_k_warp_hs<NQ>, threads, smem), resident = sm_count * per_sm;
+  const int grid = std::max(1, std::min(want, resident));
+  QsbBatchArgs a2 = args;
+  a2.group = grid == resident ? per_sm : 0;
+  QSB_LAUNCH((qsb_k_warp_hs<NQ>), grid, threads, smem, st, a2);
   QSB_CUDA(cudaGetLastError());
   return QSB_OK;
 }

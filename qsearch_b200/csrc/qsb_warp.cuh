@@ -709,7 +709,7 @@ QSB_GLOBAL __launch_bounds__(32 * QsbWarpGeom<NQ>::WARPS, (NQ == 4 ? 12 : NQ == 
   const int tid = threadIdx.x, nth = 32 * G::WARPS;
   int staged = -1;
   const long long p_base = a.param_off[a.first];
-  for (int li = blockIdx.x; li < a.count; li += gridDim.x) {
+  for (int li = qsb_cta_first_instance(a.group); li < a.count; li += gridDim.x) {
     const int inst = a.first + li;
     const int pi = a.prog_idx[inst];
     QsbDevProgram P = a.progs[pi];

@@ -22,8 +22,9 @@ def main():
     ap.add_argument("--qubits", type=int, default=4)
     ap.add_argument("--instances", type=int, default=4736)
     ap.add_argument("--reps", type=int, default=3)
+    ap.add_argument("--circuits", type=int, default=16)
     a = ap.parse_args()
-    n_circ = 16
+    n_circ = a.circuits
     n_vec = (a.instances + n_circ - 1) // n_circ
     circuits, params, targets = workloads.microbench_workload(a.qubits, n_circ, n_vec)
     gps = [lowering.lower(c) for c in circuits]
