@@ -131,7 +131,8 @@ static int qsb_launch_warp_hs(const QsbBatchArgs& args, cudaStream_t st, int sm_
   const int per_sm = qsb_resident_ctas(qsb_k_warp_hs<NQ>, threads, smem), resident = sm_count * per_sm;
   const int grid = std::max(1, std::min(want, resident));
   QsbBatchArgs a2 = args;
-  a2.group = grid == resident ? per_sm : 0;
+  a2.group = 0;  // plain instance order: the SM-local order of the Jacobian kernel is 1-2 % slower here (profiles/r1/aq_ab_hs.log)
+  (void)per_sm;
   QSB_LAUNCH((qsb_k_warp_hs<NQ>), grid, threads, smem, st, a2);
   QSB_CUDA(cudaGetLastError());
   return QSB_OK;
