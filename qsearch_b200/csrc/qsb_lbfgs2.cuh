@@ -1,4 +1,5 @@
-// Batched on-device L-BFGS on the register-resident HS kernels: one CTA of 4 warps per (circuit, start) instance.
+// Batched on-device L-BFGS on the register-resident HS kernels: one CTA of N/8 warps (one per column block) per
+// (circuit, start) instance, so that no branch depends on the warp index (uniform control flow, see qsb_k_warp_jac).
 // Same algorithm, settings and stopping rules as qsb_k_lbfgs (qsb_lbfgs.cuh: BFGS_Jac_Solver, qsearch/solvers.py:138-144;
 // NLopt LD_LBFGS driver, qsrs/src/solvers.rs:33-74); the objective and gradient come from qsb_warp_hs_cols
 // (N/8 warps, column blocks) and the line-search evaluations from the forward-only sweep qsb_warp_forward8.
@@ -16,7 +17,7 @@ template <int NQ>
 QSB_DEVICE double qsb_cta_hs_grad(const QsbDevProgram& P, const double* x, const double* target, const QsbLbfgs2Smem& sm,
                                   double* grad) {
   constexpr int NCB = (1 << NQ) / 8;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31, warp = NCB == 1 ? 0 : (int)(threadIdx.x >> 5);
   __syncthreads();
   for (int p = threadIdx.x; p < P.n_params; p += blockDim.x) {
     double s, c;
@@ -26,7 +27,7 @@ QSB_DEVICE double qsb_cta_hs_grad(const QsbDevProgram& P, const double* x, const
   __syncthreads();
   qsb_fill_gates(P, sm.trig, sm.gtab, threadIdx.x, blockDim.x);
   __syncthreads();
-  if (warp < NCB) qsb_warp_hs_cols<NQ>(P, target, sm.gtab, warp, NCB, lane, sm.trp + 2 * warp, sm.cpart);
+  qsb_warp_hs_cols<NQ>(P, target, sm.gtab, warp, NCB, lane, sm.trp + 2 * warp, sm.cpart);  // blockDim.x == 32 NCB
   __syncthreads();
   const double f = qsb_hs_finish<NQ>(P, sm.gtab, sm.trp, sm.cpart, NCB, threadIdx.x, blockDim.x, grad);
   __syncthreads();
@@ -37,7 +38,7 @@ QSB_DEVICE double qsb_cta_hs_grad(const QsbDevProgram& P, const double* x, const
 template <int NQ>
 QSB_DEVICE double qsb_cta_hs_value(const QsbDevProgram& P, const double* x, const double* target, const QsbLbfgs2Smem& sm) {
   cplx tr;
-  qsb_cta_half_norm<NQ>(P, x, target, sm.trig, sm.gtab, sm.part, &tr);
+  qsb_cta_half_norm<NQ, true>(P, x, target, sm.trig, sm.gtab, sm.part, &tr);
   return 1.0 - sqrt(tr.x * tr.x + tr.y * tr.y) / (1 << NQ);
 }
 
@@ -48,7 +49,7 @@ static inline size_t qsb_lbfgs2_smem_bytes(int nq, int max_ops, int max_params, 
 }
 
 template <int NQ>
-QSB_GLOBAL __launch_bounds__(128) qsb_k_lbfgs2(QsbSolveArgs a) {
+QSB_GLOBAL __launch_bounds__(32 * ((1 << NQ) / 8)) qsb_k_lbfgs2(QsbSolveArgs a) {
   constexpr int NCB = (1 << NQ) / 8;
   QSB_DYN_SMEM(smem_raw);
   cplx* red = (cplx*)smem_raw;  // 32

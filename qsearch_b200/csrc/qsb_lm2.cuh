@@ -164,7 +164,7 @@ QSB_DEVICE void qsb_warp_forward8(const QsbDevProgram& P, const double* target, 
 }
 
 // CTA-wide: (cos, sin) table and gate table of x, then F = |U T^dagger - I|_F^2 / 2 and Tr(U T^dagger).  part: >= 3 * (N/8) doubles.
-template <int NQ>
+template <int NQ, bool ALLW = false>  // ALLW: the CTA has exactly N/8 warps, all of them take a column block (qsb_k_lbfgs2)
 QSB_DEVICE double qsb_cta_half_norm(const QsbDevProgram& P, const double* x, const double* target, double* trig,
                                     cplx* gtab, double* part, cplx* tr_out) {
   constexpr int NCB = (1 << NQ) / 8;
@@ -178,7 +178,7 @@ QSB_DEVICE double qsb_cta_half_norm(const QsbDevProgram& P, const double* x, con
   __syncthreads();
   qsb_fill_gates(P, trig, gtab, threadIdx.x, blockDim.x, true);  // rank-one derivative slots: qsb_cta_jac reads this table
   __syncthreads();
-  if (warp < NCB) {
+  if (ALLW || warp < NCB) {
     double n2; cplx tr;
     qsb_warp_forward8<NQ>(P, target, gtab, warp, lane, n2, tr);
     if (lane == 0) { part[3 * warp] = n2; part[3 * warp + 1] = tr.x; part[3 * warp + 2] = tr.y; }
