@@ -14,6 +14,15 @@
 
 #define QSB_LM_WARPS 8
 
+// Warp index as a value the compiler knows to be the same in all lanes (the broadcast of lane 0, cf. CUTLASS
+// canonical_warp_idx_sync): branches on it - each warp of the solver walks its own program segment - are then warp-uniform
+// for ptxas, which otherwise wraps every shuffle below them in a WARPSYNC.COLLECTIVE sequence (see qsb_k_warp_jac).
+#ifdef QSB_EMU
+static inline int qsb_warp_index() { return (int)(threadIdx.x >> 5); }
+#else
+__device__ __forceinline__ int qsb_warp_index() { return __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0); }
+#endif
+
 #ifdef QSB_EMU
 #define QSB_CLOCK() 0ll
 #define QSB_LDCG(p) (*(p))
@@ -168,7 +177,7 @@ template <int NQ, bool ALLW = false>  // ALLW: the CTA has exactly N/8 warps, al
 QSB_DEVICE double qsb_cta_half_norm(const QsbDevProgram& P, const double* x, const double* target, double* trig,
                                     cplx* gtab, double* part, cplx* tr_out) {
   constexpr int NCB = (1 << NQ) / 8;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31, warp = qsb_warp_index();
   __syncthreads();
   for (int p = threadIdx.x; p < P.n_params; p += blockDim.x) {
     double s, c;
@@ -214,7 +223,7 @@ template <int NQ>
 QSB_DEVICE void qsb_cta_jac(const QsbDevProgram& P, const double* target, const cplx* gtab, double* wtiles, const int* seg,
                             int rank, double* R) {
   using G = QsbWarpGeom<NQ>;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31, warp = qsb_warp_index();
   const int tile = warp % G::WARPS, s = rank * (QSB_LM_WARPS / G::WARPS) + warp / G::WARPS;
   qsb_warp_jac_range<NQ, QSB_RUN_RESID>(P, target, gtab, wtiles + (size_t)warp * QSB_WTILE_DOUBLES, tile, lane, seg[s], seg[s + 1],
                                         R + (size_t)P.n_params * 2 * G::NN, R);
@@ -240,7 +249,7 @@ struct QsbCholSmem {
 
 QSB_DEVICE bool qsb_chol_blocked(const double* A, int rows, const double* d2, double mu, int P, double* Lb, QsbCholSmem* cs) {
   constexpr int NB = QSB_CH_NB, LD = QSB_CH_LD;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+  const int lane = threadIdx.x & 31, warp = qsb_warp_index(), nwarps = blockDim.x >> 5;
   const int g = lane >> 2, t = lane & 3;
   __syncthreads();
   for (int e = threadIdx.x; e < rows * rows; e += blockDim.x) {
@@ -360,7 +369,7 @@ QSB_DEVICE bool qsb_chol_blocked(const double* A, int rows, const double* d2, do
 
 // h = -(L^T)^{-1} y with y = row P of Lb (see qsb_chol_blocked); one warp, rows of L^T are contiguous in Lb.
 QSB_DEVICE void qsb_chol_back(const double* Lb, int rows, int P, double* h) {
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31, warp = qsb_warp_index();
   __syncthreads();
   if (warp == 0) {
     const double* y = Lb + (size_t)P * rows;
@@ -459,7 +468,7 @@ QSB_DEVICE bool qsb_chol_packed(const double* A, int rows, const double* d2, dou
 #define QSB_CH_T(slot) do { if (prof && threadIdx.x == 0) { const long long _n = QSB_CLOCK(); atomicAdd((unsigned long long*)&prof[slot], (unsigned long long)(_n - _tc)); _tc = _n; } } while (0)
   long long _tc = prof ? QSB_CLOCK() : 0ll;
   constexpr int NB = QSB_CH_NB;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+  const int lane = threadIdx.x & 31, warp = qsb_warp_index(), nwarps = blockDim.x >> 5;
   const int g = lane >> 2, t = lane & 3;
   __syncthreads();
   // copy in the lower triangle, one row per warp and round; a row's loads (<= 9 per lane) are all issued before the
@@ -543,7 +552,7 @@ QSB_DEVICE bool qsb_chol_packed(const double* A, int rows, const double* d2, dou
 // h = -(L^T)^{-1} y, y = row P of the packed factor.  One warp, column sweep: once h_j is known every lane folds it
 // into its own entries of the right-hand side (row j of L is contiguous), so there is no reduction on the critical path.
 QSB_DEVICE void qsb_chol_back_packed(const double* Ls, int P, const double* rdiag, double* h) {
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31, warp = qsb_warp_index();
   __syncthreads();
   if (warp == 0) {
     // the right-hand side lives in registers (lane l owns rows l, l + 32, ...): a step is one multiply, one shuffle
@@ -606,7 +615,7 @@ QSB_GLOBAL __launch_bounds__(QSB_LM_WARPS * 32) qsb_k_lm2(QsbSolveArgs a) {
   double* wtiles = (double*)(((uintptr_t)Ls + 15) & ~(uintptr_t)15);
   double* rinv = Ls + (size_t)(a.max_params + 1) * (a.max_params + 2) / 2;
   int* okflag = (int*)(rinv + QSB_CH_NB);
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31, warp = qsb_warp_index();
   // a cluster of a.cluster CTAs works on one instance: they split the Jacobian segments and the SYRK blocks, share
   // R and A through global memory (two cluster barriers per iteration) and repeat the small dense algebra redundantly,
   // so every CTA takes the same decisions without a broadcast.
@@ -764,7 +773,7 @@ QSB_GLOBAL __launch_bounds__(QSB_LM_WARPS * 32) qsb_k_lmsys(QsbBatchArgs a, doub
   cplx* gtab = (cplx*)(part + 16);
   double* wtiles = (double*)(gtab + (size_t)4 * (a.max_ops + a.max_params));
   int* seg = (int*)(wtiles + (size_t)QSB_LM_WARPS * QSB_WTILE_DOUBLES);
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31, warp = qsb_warp_index();
   double* Rg = scratch + (size_t)blockIdx.x * scratch_per_cta;
   const long long p_base = a.param_off[a.first], s_base = sq_off[a.first];
   for (int li = blockIdx.x; li < a.count; li += gridDim.x) {
