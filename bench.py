@@ -259,8 +259,17 @@ def run_ours(args, rank, world, local_rank):
     sel = slice(0, e_inst)
     out_r = lib.pinned_empty((e_inst, 2 * N * N))      # page-locked host buffers (qsb_host_alloc)
     out_J = lib.pinned_empty((e_inst * P, 2 * N * N))
-    for _ in range(max(3, args.warmup)):  # warm-up: page faults of the output buffers, device buffers, host threads
-        lib.eval_residuals_jac(gps, poi[sel], flat[sel], T, out_r, out_J)  # (the first 2-3 calls of a process run at 0.3-0.8x, profiles/r1/as_e2e_ab.log)
+    # warm-up: page faults of the output buffers, device buffers, host threads.  On a fresh box the first calls of a process
+    # run at 0.1-0.8x of the steady rate for a while (profiles/r1/as_e2e_ab.log), so warm up until two consecutive calls
+    # agree within 5 % (at least max(3, W) calls, at most 16)
+    prev = None
+    for w in range(16):
+        tw = time.perf_counter()
+        lib.eval_residuals_jac(gps, poi[sel], flat[sel], T, out_r, out_J)
+        tw = time.perf_counter() - tw
+        if w + 1 >= max(3, args.warmup) and prev is not None and abs(tw - prev) <= 0.05 * max(tw, prev):
+            break
+        prev = tw
     barrier(dist)
     t0 = time.perf_counter()
     e_steps = max(1, min(args.steps, 3))
