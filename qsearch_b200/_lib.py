@@ -30,7 +30,8 @@ class QsbError(RuntimeError):
 class SolverOpts(ctypes.Structure):
     _fields_ = [("max_iters", ctypes.c_int32), ("lbfgs_memory", ctypes.c_int32), ("ftol", ctypes.c_double),
                 ("xtol", ctypes.c_double), ("gtol", ctypes.c_double), ("stop_value", ctypes.c_double),
-                ("reserved", ctypes.c_double * 4)]
+                ("straggler_factor", ctypes.c_double), ("sibling_stop", ctypes.c_double),
+                ("straggler_min_iters", ctypes.c_double), ("reserved", ctypes.c_double)]
 
 
 def _dp(a):
@@ -212,11 +213,12 @@ class Library:
 
     # ------------------------------------------------------------------ solvers
     def solve(self, method, gps, prog_of_instance, x0, target, max_iters=0, ftol=0.0, xtol=0.0, gtol=0.0,
-              stop_value=0.0, lbfgs_memory=10):
+              stop_value=0.0, lbfgs_memory=10, straggler_factor=0.0, sibling_stop=0.0, straggler_min_iters=0.0):
         handles, poi, x0, sizes = self._pack(gps, prog_of_instance, x0)
         T = np.ascontiguousarray(target, dtype="complex128")
         opts = SolverOpts(max_iters=max_iters, lbfgs_memory=lbfgs_memory, ftol=ftol, xtol=xtol, gtol=gtol,
-                          stop_value=stop_value)
+                          stop_value=stop_value, straggler_factor=straggler_factor, sibling_stop=sibling_stop,
+                          straggler_min_iters=straggler_min_iters)
         x = np.empty_like(x0)
         f = np.empty(len(poi), dtype="float64")
         iters = np.empty(len(poi), dtype="int32")

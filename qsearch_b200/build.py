@@ -2,24 +2,55 @@
 
     python -m qsearch_b200.build            # product library  -> qsearch_b200/libqsb200.so
     python -m qsearch_b200.build --emu      # tests only: host emulation of the same sources -> tests/emu/_build/
+
+The library is several translation units compiled in parallel (the solver kernels dominate the compile time) and then
+linked; objects are cached under qsearch_b200/_obj/ (git-ignored) keyed on the modification times of the sources.
 """
 import os
 import subprocess
 import sys
+from concurrent.futures import ThreadPoolExecutor
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libqsb200.so")
+OBJ_DIR = os.path.join(HERE, "_obj")
 EMU_DIR = os.path.join(ROOT, "tests", "emu", "_build")
 EMU_LIB = os.path.join(EMU_DIR, "libqsb200_emu.so")
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
-              "-Xcompiler", "-fPIC,-O2", "-shared", "--threads", "0"]
+              "-Xcompiler", "-fPIC,-O2"]
+
+# (object name, source, extra defines)
+UNITS = [
+    ("api", "qsb_api.cu", []),
+    ("lmsys", "qsb_lmsys.cu", []),
+    ("solve_lm", "qsb_solve.cu", ["-DQSB_SOLVE_TU=0"]),
+    ("solve_lbfgs", "qsb_solve.cu", ["-DQSB_SOLVE_TU=1"]),
+    ("solve_lm5", "qsb_solve.cu", ["-DQSB_SOLVE_TU=2"]),
+    ("peak", "qsb_peak.cu", []),
+]
+
+
+def _unit_deps(src):
+    """Files a translation unit depends on: the transitive closure of its quoted #include lines (+ this script)."""
+    seen, todo = set(), [os.path.join(CSRC, src)]
+    while todo:
+        f = os.path.normpath(todo.pop())
+        if f in seen or not os.path.exists(f):
+            continue
+        seen.add(f)
+        with open(f) as fh:
+            for line in fh:
+                line = line.strip()
+                if line.startswith('#include "'):
+                    todo.append(os.path.join(os.path.dirname(f), line.split('"')[1]))
+    return sorted(seen) + [os.path.abspath(__file__)]
 
 
 def _sources():
-    out = [os.path.join(ROOT, "include", "qsb200.h")]
+    out = [os.path.join(ROOT, "include", "qsb200.h"), os.path.abspath(__file__)]
     for f in sorted(os.listdir(CSRC)):
         out.append(os.path.join(CSRC, f))
     return out
@@ -32,41 +63,62 @@ def _stale(target, deps):
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build_cuda(force=False, verbose=False):
-    if not force and not _stale(LIB, _sources()):
+def _run(cmd):
+    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    return r.returncode, r.stdout
+
+
+def _compile_all(jobs, verbose):
+    """jobs: list of (object path, command).  Compiles the stale ones in parallel; raises on the first failure."""
+    with ThreadPoolExecutor(max_workers=max(1, min(len(jobs), os.cpu_count() or 1))) as ex:
+        results = list(ex.map(lambda j: _run(j[1]), jobs))
+    for (obj, cmd), (rc, out) in zip(jobs, results):
+        if verbose or rc:
+            sys.stdout.write(out)
+        if rc:
+            raise subprocess.CalledProcessError(rc, cmd)
+
+
+def build_cuda(force=False, verbose=False, only=None):
+    deps = _sources()
+    if not force and not _stale(LIB, deps):
         return LIB
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB, os.path.join(CSRC, "qsb_api.cu")]
-    subprocess.run(cmd, check=True)
+    os.makedirs(OBJ_DIR, exist_ok=True)
+    jobs, objs = [], []
+    for name, src, defs in UNITS:
+        obj = os.path.join(OBJ_DIR, name + ".o")
+        objs.append(obj)
+        if force or _stale(obj, _unit_deps(src)) or (only and name in only):
+            jobs.append((obj, [nvcc] + NVCC_FLAGS + defs + (["-Xptxas", "-v"] if verbose else []) +
+                         ["-c", "-o", obj, os.path.join(CSRC, src)]))
+    _compile_all(jobs, verbose)
+    subprocess.run([nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", LIB] + objs, check=True)
     return LIB
-
-
-def build_exp(verbose=False):
-    """DEVELOPER TOOL: evaluation kernels only (no solver kernels), for quick A/B runs of a kernel change through
-    QSB_LIB_PATH (tools/prof_case.py).  Never loaded by the product."""
-    out = os.path.join(HERE, "libqsb200_exp.so")
-    nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-    cmd = [nvcc] + NVCC_FLAGS + ["-DQSB_EXPERIMENT"] + (["-Xptxas", "-v"] if verbose else []) + ["-o", out, os.path.join(CSRC, "qsb_api.cu")]
-    subprocess.run(cmd, check=True)
-    return out
 
 
 def build_emu(force=False):
     """TEST INFRASTRUCTURE: compile the same .cu sources for the host with tests/emu/cuda_emu.h."""
     hdr = os.path.join(ROOT, "tests", "emu", "cuda_emu.h")
-    if not force and not _stale(EMU_LIB, _sources() + [hdr]):
+    deps = _sources() + [hdr]
+    if not force and not _stale(EMU_LIB, deps):
         return EMU_LIB
     os.makedirs(EMU_DIR, exist_ok=True)
-    cmd = ["g++", "-x", "c++", "-std=c++20", "-O2", "-fPIC", "-shared", "-pthread", "-DQSB_EMU", "-DQSB_EMU_DEFINE",
-           "-include", hdr, "-o", EMU_LIB, os.path.join(CSRC, "qsb_api.cu")]
-    subprocess.run(cmd, check=True)
+    jobs, objs = [], []
+    for name, src, defs in UNITS:
+        obj = os.path.join(EMU_DIR, name + ".o")
+        objs.append(obj)
+        if force or _stale(obj, _unit_deps(src) + [hdr]):
+            jobs.append((obj, ["g++", "-x", "c++", "-std=c++20", "-O2", "-fPIC", "-pthread", "-DQSB_EMU"] +
+                         (["-DQSB_EMU_DEFINE"] if name == "api" else []) + defs +
+                         ["-include", hdr, "-c", "-o", obj, os.path.join(CSRC, src)]))
+    _compile_all(jobs, False)
+    subprocess.run(["g++", "-shared", "-pthread", "-o", EMU_LIB] + objs, check=True)
     return EMU_LIB
 
 
 if __name__ == "__main__":
-    if "--exp" in sys.argv:
-        print(build_exp(verbose="-v" in sys.argv))
-    elif "--emu" in sys.argv:
+    if "--emu" in sys.argv:
         print(build_emu(force="--force" in sys.argv))
     else:
         print(build_cuda(force="--force" in sys.argv, verbose="-v" in sys.argv))

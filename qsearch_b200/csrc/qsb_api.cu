@@ -11,14 +11,12 @@
 #include "qsb_host.h"
 #include "qsb_generic.cuh"
 #include "qsb_warp.cuh"
-#ifndef QSB_EXPERIMENT  // QSB_EXPERIMENT: developer build of the evaluation kernels only (python -m qsearch_b200.build --exp)
-#include "qsb_lm2.cuh"
-#endif
 #include "qsb_launch.h"
 
 // ---------------------------------------------------------------------------- errors
 static thread_local std::string g_err;
 void qsb_set_error(const std::string& msg) { g_err = msg; }
+const std::string& qsb_get_error() { return g_err; }
 int qsb_fail(int code, const std::string& msg) { g_err = msg; return code; }
 int qsb_cuda_fail(cudaError_t e, const char* what) {
   g_err = std::string("CUDA error: ") + cudaGetErrorString(e) + " in " + what;
@@ -229,8 +227,23 @@ extern "C" int qsb_program_destroy(qsb_ctx* ctx, qsb_program* prog) {
 extern "C" int qsb_program_num_params(const qsb_program* p) { return p ? p->n_params : -1; }
 extern "C" int qsb_program_num_qubits(const qsb_program* p) { return p ? p->n_qubits : -1; }
 
+// max |T T^dagger - I| <= 1e-9 (N <= 32: a few thousand flops): the body-frame LM forms (qsb_lm3.cuh) need a unitary target
+bool qsb_target_is_unitary(const double* T, int nq) {
+  const int N = 1 << nq;
+  for (int i = 0; i < N; ++i)
+    for (int j = 0; j <= i; ++j) {
+      double re = (i == j) ? -1.0 : 0.0, im = 0.0;
+      for (int k = 0; k < N; ++k) {
+        const double ar = T[2 * (i * N + k)], ai = T[2 * (i * N + k) + 1], br = T[2 * (j * N + k)], bi = T[2 * (j * N + k) + 1];
+        re += ar * br + ai * bi; im += ai * br - ar * bi;
+      }
+      if (!(fabs(re) <= 1e-9) || !(fabs(im) <= 1e-9)) return false;
+    }
+  return true;
+}
+
 // ---------------------------------------------------------------------------- device-resident batches
-static int buf_reserve(QsbBuf& b, size_t bytes) {
+int qsb_buf_reserve(QsbBuf& b, size_t bytes) {
   if (bytes <= b.bytes) return QSB_OK;
   if (b.p) { cudaFree(b.p); b.p = nullptr; b.bytes = 0; }
   cudaError_t e = cudaMalloc(&b.p, bytes);
@@ -327,6 +340,7 @@ extern "C" int qsb_batch_set_target(qsb_batch* b, const double* target) {
   QSB_CUDA(cudaSetDevice(d.id));
   QSB_CUDA(cudaMemcpyAsync(b->d_target, target, sizeof(double) * 2 * ((size_t)1 << (2 * b->n_qubits)), cudaMemcpyHostToDevice, d.stream));
   QSB_CUDA(cudaStreamSynchronize(d.stream));
+  b->target_unitary = qsb_target_is_unitary(target, b->n_qubits);
   return QSB_OK;
 }
 
@@ -368,9 +382,9 @@ extern "C" int qsb_batch_run(qsb_batch* b, int what, int first, int count, float
   size_t a, bb, c;
   out_sizes(b, what, first, count, &a, &bb, &c);
   int rc;
-  if ((rc = buf_reserve(b->out_a, a * sizeof(double)))) return rc;
-  if ((rc = buf_reserve(b->out_b, bb * sizeof(double)))) return rc;
-  if ((rc = buf_reserve(b->out_c, c * sizeof(double)))) return rc;
+  if ((rc = qsb_buf_reserve(b->out_a, a * sizeof(double)))) return rc;
+  if ((rc = qsb_buf_reserve(b->out_b, bb * sizeof(double)))) return rc;
+  if ((rc = qsb_buf_reserve(b->out_c, c * sizeof(double)))) return rc;
   b->last_first = first; b->last_count = count; b->last_what = what;
   if (count == 0) { if (elapsed_ms) *elapsed_ms = 0.f; return QSB_OK; }
   if (elapsed_ms) QSB_CUDA(cudaEventRecord(d.ev0, d.stream));
@@ -407,51 +421,7 @@ extern "C" int qsb_batch_fetch(qsb_batch* b, int what, double* a, double* bb, do
   return QSB_OK;
 }
 
-// QSB_RUN_LMSYS: tensor-core kernels only (one-qubit leaves + CNOT, 3..5 qubits)
-#ifdef QSB_EXPERIMENT
-static int qsb_launch_lmsys(qsb_batch*, const QsbBatchArgs&, cudaStream_t, int) { return qsb_fail(QSB_ERR_UNSUPPORTED, "experiment build: no solver kernels"); }
-#else
-template <int NQ>
-static int qsb_launch_lmsys_nq(qsb_batch* b, const QsbBatchArgs& args, cudaStream_t st, int sm_count) {
-  const size_t NN = (size_t)1 << (2 * NQ), maxP = (size_t)args.max_params;
-  const size_t smem = qsb_lmsys_smem_bytes(args.max_ops, args.max_params);
-  if (smem > 200 * 1024) return qsb_fail(QSB_ERR_UNSUPPORTED, "program too long for QSB_RUN_LMSYS");
-  int rc = qsb_prepare_kernel(qsb_k_lmsys<NQ>, smem);
-  if (rc) return rc;
-  const int threads = QSB_LM_WARPS * 32;
-  const int grid = std::max(1, std::min(args.count, sm_count * qsb_resident_ctas(qsb_k_lmsys<NQ>, threads, smem)));
-  size_t per_cta = (maxP + 1) * 2 * NN + (maxP + 1) * (maxP + 1);
-  per_cta = (per_cta + 1) & ~(size_t)1;
-  const size_t need = (size_t)grid * per_cta * sizeof(double);
-  if (need > b->solver_scratch_bytes) {
-    if (b->solver_scratch) cudaFree(b->solver_scratch);
-    b->solver_scratch = nullptr; b->solver_scratch_bytes = 0;
-    if (cudaMalloc(&b->solver_scratch, need) != cudaSuccess) return qsb_fail(QSB_ERR_NOMEM, "device allocation of the LM-system scratch failed");
-    b->solver_scratch_bytes = need;
-  }
-  if (!b->d_sq_off) {
-    std::vector<long long> sq((size_t)b->n_instances + 1);
-    long long off = 0;
-    for (int i = 0; i < b->n_instances; ++i) { sq[i] = off; const long long p = b->param_off[i + 1] - b->param_off[i]; off += p * p; }
-    sq[b->n_instances] = off;
-    QSB_CUDA(cudaMalloc((void**)&b->d_sq_off, sizeof(long long) * sq.size()));
-    QSB_CUDA(cudaMemcpy(b->d_sq_off, sq.data(), sizeof(long long) * sq.size(), cudaMemcpyHostToDevice));
-  }
-  QSB_LAUNCH((qsb_k_lmsys<NQ>), grid, threads, smem, st, args, (double*)b->solver_scratch, per_cta, (const long long*)b->d_sq_off);
-  QSB_CUDA(cudaGetLastError());
-  return QSB_OK;
-}
-
-static int qsb_launch_lmsys(qsb_batch* b, const QsbBatchArgs& args, cudaStream_t st, int sm_count) {
-  if (!b->fast_ok || b->n_qubits < 3)
-    return qsb_fail(QSB_ERR_UNSUPPORTED, "QSB_RUN_LMSYS needs a one-qubit-leaf + CNOT program on 3..5 qubits");
-  switch (b->n_qubits) {
-    case 3: return qsb_launch_lmsys_nq<3>(b, args, st, sm_count);
-    case 4: return qsb_launch_lmsys_nq<4>(b, args, st, sm_count);
-    default: return qsb_launch_lmsys_nq<5>(b, args, st, sm_count);
-  }
-}
-#endif
+int qsb_launch_lmsys(qsb_batch* b, const QsbBatchArgs& args, cudaStream_t st, int sm_count);  // qsb_lmsys.cu
 
 int qsb_batch_enqueue(qsb_batch* b, int what, int first, int count) {
   const QsbDevice& d = b->ctx->devs[b->slot];
@@ -634,12 +604,3 @@ extern "C" int qsb_eval_residuals_jac(qsb_ctx* ctx, int n_programs, const qsb_pr
   return host_eval(j);
 }
 
-#ifndef QSB_EXPERIMENT
-#include "qsb_solvers.inc"
-#else
-extern "C" int qsb_solve_lm(qsb_ctx*, int, const qsb_program* const*, int, const int32_t*, const double*, const double*,
-                            const qsb_solver_opts*, double*, double*, int32_t*, int32_t*) { return qsb_fail(QSB_ERR_UNSUPPORTED, "experiment build: no solver kernels"); }
-extern "C" int qsb_solve_lbfgs(qsb_ctx*, int, const qsb_program* const*, int, const int32_t*, const double*, const double*,
-                               const qsb_solver_opts*, double*, double*, int32_t*, int32_t*) { return qsb_fail(QSB_ERR_UNSUPPORTED, "experiment build: no solver kernels"); }
-#endif
-#include "qsb_peak.inc"

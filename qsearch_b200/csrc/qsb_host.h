@@ -44,6 +44,7 @@ struct qsb_batch {
   int n_qubits = 0, n_instances = 0, n_programs = 0;
   int max_ops = 0, max_params = 0;
   bool fast_ok = false;
+  bool target_unitary = false;      // set by qsb_batch_set_target: selects the body-frame LM forms (qsb_lm3.cuh)
   bool force_generic = false;       // tests / profiling: run the shared-memory interpreter even where a warp kernel exists
   std::vector<long long> param_off;  // host copy, n_instances + 1
   std::vector<int32_t> prog_idx;
@@ -60,6 +61,9 @@ struct qsb_batch {
 };
 
 void qsb_set_error(const std::string& msg);
+const std::string& qsb_get_error();
+int qsb_buf_reserve(QsbBuf& b, size_t bytes);
+bool qsb_target_is_unitary(const double* T, int n_qubits);
 int qsb_fail(int code, const std::string& msg);
 int qsb_cuda_fail(cudaError_t e, const char* what);
 

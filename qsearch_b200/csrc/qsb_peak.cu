@@ -1,3 +1,6 @@
+// FP64 peak micro-benchmarks (own translation unit).
+#include "qsb_host.h"
+#include "qsb_warp.cuh"
 // FP64 peak micro-benchmarks: the roofline denominator for the complex-fp64 kernels is not in MEASURED_PEAKS.json
 // (it holds HBM and bf16 only), so bench.py measures it on the box with these two kernels:
 //   use_dmma = 0: independent DFMA chains on the FP64 pipe;  use_dmma = 1: mma.sync.m8n8k4.f64 (DMMA) chains.

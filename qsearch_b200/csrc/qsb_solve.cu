@@ -1,27 +1,45 @@
-// Host side of the batched solvers (C ABI: qsb_solve_lm / qsb_solve_lbfgs).  Included by qsb_api.cu.
-#include "qsb_solver.cuh"
+// Host side of the batched solvers (C ABI: qsb_solve_lm / qsb_solve_lbfgs).  One source, three translation units
+// (build.py compiles them in parallel): QSB_SOLVE_TU = 0: Levenberg-Marquardt, 1..4 qubits + qsb_solve_lm;
+// 1: L-BFGS + qsb_solve_lbfgs; 2: Levenberg-Marquardt, 5 qubits.
+#ifndef QSB_SOLVE_TU
+#error "compile with -DQSB_SOLVE_TU=0|1|2"
+#endif
+#include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <thread>
+
+#include "qsb_solve_host.h"
+#include "qsb_launch.h"
+#if QSB_SOLVE_TU == 1
 #include "qsb_lbfgs.cuh"
-#include "qsb_lm2.cuh"
 #include "qsb_lbfgs2.cuh"
+#define QSB_TU_METHOD QSB_SOLVE_LBFGS
+#else
+#include "qsb_lm2.cuh"
+#include "qsb_lm3.cuh"
+#define QSB_TU_METHOD QSB_SOLVE_LM
+#endif
 
-enum { QSB_SOLVE_LM = 0, QSB_SOLVE_LBFGS = 1 };
-
-struct SolveJob {
-  qsb_ctx* ctx; int n_programs; const qsb_program* const* progs; int n_instances; const int32_t* prog_of_instance;
-  const double* x0; const double* target; qsb_solver_opts opts; int method;
-  double* out_x; double* out_f; int32_t* out_iters; int32_t* out_status;
-};
-
+#if QSB_SOLVE_TU != 1
+// ---------------------------------------------------------------------------- Levenberg-Marquardt launches
 template <int NQ>
 static int launch_solver_nq(const SolveJob& job, qsb_batch* b, QsbSolveArgs& args, const QsbDevice& d) {
   const size_t NN = (size_t)1 << (2 * NQ);
   const size_t maxP = (size_t)b->max_params;
-  const bool tensor_lm = job.method == QSB_SOLVE_LM && NQ >= 3 && b->fast_ok && !b->force_generic && maxP + 1 <= QSB_CH_MAXROWS;
-  const bool warp_lbfgs = job.method == QSB_SOLVE_LBFGS && NQ >= 3 && b->fast_ok && !b->force_generic &&
-                          qsb_lbfgs2_smem_bytes(NQ, b->max_ops, b->max_params, job.opts.lbfgs_memory > 0 ? job.opts.lbfgs_memory : 10) <= 200 * 1024;
+  const bool tensor_lm = NQ >= 3 && b->fast_ok && !b->force_generic && maxP + 1 <= QSB_CH_MAXROWS;
+  // body-frame LM (qsb_lm3.cuh): unitary target, packed factor in shared memory; QSB_LM_KERNEL=lm2 forces the general kernel
+  bool body_lm = tensor_lm && job.target_unitary && qsb_lm3_smem_bytes(NQ, b->max_ops, (int)maxP) <= 227 * 1024;
+  if (const char* e = getenv("QSB_LM_KERNEL")) { if (strcmp(e, "lm2") == 0) body_lm = false; }
   int threads = (int)std::max<size_t>(32, NN / 2);
   size_t smem, per_cta;
-  if (tensor_lm) {
+  if (body_lm) {
+    if constexpr (NQ >= 3) threads = QsbQGeom<NQ>::WARPS * 32;
+    smem = qsb_lm3_smem_bytes(NQ, b->max_ops, (int)maxP);
+    per_cta = (maxP + 1) * NN + (maxP + 1) * (maxP + 1);
+  } else if (tensor_lm) {
     threads = QSB_LM_WARPS * 32;
     args.chol_smem = qsb_lm2_smem_bytes(b->max_ops, (int)maxP, true) <= 224 * 1024;
     if (const char* e = getenv("QSB_LM_CHOL")) { if (strcmp(e, "global") == 0) args.chol_smem = 0; }  // profiling
@@ -55,30 +73,23 @@ static int launch_solver_nq(const SolveJob& job, qsb_batch* b, QsbSolveArgs& arg
     if (const char* e = getenv("QSB_LM_CLUSTER")) { int v = atoi(e); if (v >= 1 && v <= QSB_LM_MAX_CLUSTER) csize = v; }
     args.cluster = csize;
     per_cta = (maxP + 1) * 2 * NN + 2 * (maxP + 1) * (maxP + 1) + (args.chol_smem ? 0 : (size_t)csize * (maxP + 1) * (maxP + 1));
-  } else if (job.method == QSB_SOLVE_LM) {
+  } else {
     const size_t nb = (maxP + 1 + 3) / 4;
     smem = (3 * NN + 32) * 16 + 7 * maxP * 8 + (size_t)b->max_ops * QSB_TRIG_STRIDE * 8 + 4 * nb * (QSB_SYRK_MC + 1) * 8 + 64;
     per_cta = (maxP + 1) * 2 * NN + (maxP + 1) * (maxP + 1) + maxP * maxP;
-  } else if (warp_lbfgs) {
-    threads = 32 * ((1 << NQ) / 8);  // one warp per 8-column block
-    smem = qsb_lbfgs2_smem_bytes(NQ, b->max_ops, b->max_params, job.opts.lbfgs_memory > 0 ? job.opts.lbfgs_memory : 10);
-    per_cta = 1;
-  } else {
-    smem = qsb_lbfgs_smem_bytes(NQ, b->max_ops, b->max_params, job.opts.lbfgs_memory > 0 ? job.opts.lbfgs_memory : 10);
-    per_cta = 1;
   }
   if (smem > 227 * 1024) return qsb_fail(QSB_ERR_UNSUPPORTED, "circuit too large for the solver's shared-memory working set");
   int rc = QSB_OK;
   int ctas;
-  if (tensor_lm) {
+  if (body_lm) {
+    if constexpr (NQ >= 3) {
+      if ((rc = qsb_prepare_kernel(qsb_k_lm3<NQ>, smem))) return rc;
+      ctas = qsb_resident_ctas(qsb_k_lm3<NQ>, threads, smem);
+    } else ctas = 1;
+  } else if (tensor_lm) {
     if constexpr (NQ >= 3) {
       if ((rc = qsb_prepare_kernel(qsb_k_lm2<NQ>, smem))) return rc;
       ctas = qsb_resident_ctas(qsb_k_lm2<NQ>, threads, smem);
-    } else ctas = 1;
-  } else if (warp_lbfgs) {
-    if constexpr (NQ >= 3) {
-      if ((rc = qsb_prepare_kernel(qsb_k_lbfgs2<NQ>, smem))) return rc;
-      ctas = qsb_resident_ctas(qsb_k_lbfgs2<NQ>, threads, smem);
     } else ctas = 1;
   } else {
     int by_threads = 2048 / threads, by_smem = (int)((size_t)220 * 1024 / smem);
@@ -86,12 +97,14 @@ static int launch_solver_nq(const SolveJob& job, qsb_batch* b, QsbSolveArgs& arg
   }
   per_cta = (per_cta + 1) & ~(size_t)1;  // 16-byte alignment of every CTA's slab (vector stores of the Jacobian rows)
   int grid = std::max(1, std::min(args.count, d.sm_count * ctas));
-  if (tensor_lm) grid = std::max(1, std::min(args.count, d.sm_count * ctas / args.cluster)) * args.cluster;
-  rc = buf_reserve(b->out_c, (size_t)(grid / args.cluster) * per_cta * sizeof(double));  // solver scratch (per cluster)
+  if (tensor_lm && !body_lm) grid = std::max(1, std::min(args.count, d.sm_count * ctas / args.cluster)) * args.cluster;
+  rc = qsb_buf_reserve(b->out_c, (size_t)(grid / args.cluster) * per_cta * sizeof(double));  // solver scratch (per cluster / CTA)
   if (rc) return rc;
   args.scratch = (double*)b->out_c.p;
   args.scratch_per_cta = per_cta;
-  if (tensor_lm) {
+  if (body_lm) {
+    if constexpr (NQ >= 3) QSB_LAUNCH((qsb_k_lm3<NQ>), grid, threads, smem, d.stream, args);
+  } else if (tensor_lm) {
     if constexpr (NQ >= 3) {
 #ifdef QSB_EMU
       if (args.cluster > 1) QSB_LAUNCH_CLUSTER((qsb_k_lm2<NQ>), grid, threads, smem, args.cluster, args);
@@ -106,11 +119,47 @@ static int launch_solver_nq(const SolveJob& job, qsb_batch* b, QsbSolveArgs& arg
       QSB_CUDA(cudaLaunchKernelEx(&cfg, qsb_k_lm2<NQ>, args));
 #endif
     }
-  } else if (warp_lbfgs) {
-    if constexpr (NQ >= 3) QSB_LAUNCH((qsb_k_lbfgs2<NQ>), grid, threads, smem, d.stream, args);
-  } else if (job.method == QSB_SOLVE_LM) {
+  } else {
     if ((rc = qsb_prepare_kernel(qsb_k_lm<NQ>, smem))) return rc;
     QSB_LAUNCH((qsb_k_lm<NQ>), grid, threads, smem, d.stream, args);
+  }
+  QSB_CUDA(cudaGetLastError());
+  return QSB_OK;
+}
+#else
+// ---------------------------------------------------------------------------- L-BFGS launches
+template <int NQ>
+static int launch_solver_nq(const SolveJob& job, qsb_batch* b, QsbSolveArgs& args, const QsbDevice& d) {
+  const size_t NN = (size_t)1 << (2 * NQ);
+  const int mem = job.opts.lbfgs_memory > 0 ? job.opts.lbfgs_memory : 10;
+  const bool warp_lbfgs = NQ >= 3 && b->fast_ok && !b->force_generic && qsb_lbfgs2_smem_bytes(NQ, b->max_ops, b->max_params, mem) <= 200 * 1024;
+  int threads = (int)std::max<size_t>(32, NN / 2);
+  size_t smem;
+  if (warp_lbfgs) {
+    threads = 32 * ((1 << NQ) / 8);  // one warp per 8-column block
+    smem = qsb_lbfgs2_smem_bytes(NQ, b->max_ops, b->max_params, mem);
+  } else {
+    smem = qsb_lbfgs_smem_bytes(NQ, b->max_ops, b->max_params, mem);
+  }
+  if (smem > 227 * 1024) return qsb_fail(QSB_ERR_UNSUPPORTED, "circuit too large for the solver's shared-memory working set");
+  int rc = QSB_OK;
+  int ctas;
+  if (warp_lbfgs) {
+    if constexpr (NQ >= 3) {
+      if ((rc = qsb_prepare_kernel(qsb_k_lbfgs2<NQ>, smem))) return rc;
+      ctas = qsb_resident_ctas(qsb_k_lbfgs2<NQ>, threads, smem);
+    } else ctas = 1;
+  } else {
+    int by_threads = 2048 / threads, by_smem = (int)((size_t)220 * 1024 / smem);
+    ctas = std::max(1, std::min(std::min(by_threads, by_smem), 16));
+  }
+  const int grid = std::max(1, std::min(args.count, d.sm_count * ctas));
+  rc = qsb_buf_reserve(b->out_c, (size_t)grid * 2 * sizeof(double));
+  if (rc) return rc;
+  args.scratch = (double*)b->out_c.p;
+  args.scratch_per_cta = 2;
+  if (warp_lbfgs) {
+    if constexpr (NQ >= 3) QSB_LAUNCH((qsb_k_lbfgs2<NQ>), grid, threads, smem, d.stream, args);
   } else {
     if ((rc = qsb_prepare_kernel(qsb_k_lbfgs<NQ>, smem))) return rc;
     QSB_LAUNCH((qsb_k_lbfgs<NQ>), grid, threads, smem, d.stream, args);
@@ -118,20 +167,27 @@ static int launch_solver_nq(const SolveJob& job, qsb_batch* b, QsbSolveArgs& arg
   QSB_CUDA(cudaGetLastError());
   return QSB_OK;
 }
+#endif
 
+#if QSB_SOLVE_TU == 2
+int qsb_launch_solver_lm5(const SolveJob& job, qsb_batch* b, QsbSolveArgs& args, const QsbDevice& d) {
+  return launch_solver_nq<5>(job, b, args, d);
+}
+#else
 static int solve_shard(const SolveJob& job, int slot, int i0, int i1, const std::vector<long long>& poff) {
   if (i1 <= i0) return QSB_OK;
   qsb_batch* b = nullptr;
   int rc = qsb_batch_create(job.ctx, slot, job.n_programs, job.progs, i1 - i0, job.prog_of_instance + i0, &b);
   if (rc) return rc;
-  auto done = [&](int code) { std::string keep = g_err; qsb_batch_destroy(b); g_err = keep; return code; };
+  auto done = [&](int code) { std::string keep = qsb_get_error(); qsb_batch_destroy(b); qsb_set_error(keep); return code; };
   const size_t np = (size_t)(poff[i1] - poff[i0]);
   const int n = i1 - i0;
   if ((rc = qsb_batch_set_params(b, job.x0 + poff[i0], np))) return done(rc);
   if ((rc = qsb_batch_set_target(b, job.target))) return done(rc);
   // outputs: out_a = x [np] then f [n]; out_b = iters [n] + status [n] as int32
-  if ((rc = buf_reserve(b->out_a, (np + n + 1) * sizeof(double)))) return done(rc);
-  if ((rc = buf_reserve(b->out_b, (size_t)(2 * n + 2) * sizeof(int32_t)))) return done(rc);
+  if ((rc = qsb_buf_reserve(b->out_a, (np + n + 1) * sizeof(double)))) return done(rc);
+  const size_t n_ctl = (size_t)QSB_CTL_SOLVED + job.n_programs;
+  if ((rc = qsb_buf_reserve(b->out_b, ((size_t)(2 * n + 2) + n_ctl) * sizeof(int32_t)))) return done(rc);
   const QsbDevice& d = job.ctx->devs[slot];
   QsbSolveArgs args;
   args.progs = b->d_progs; args.prog_idx = b->d_prog_idx; args.param_off = b->d_param_off; args.x0 = b->d_params;
@@ -144,6 +200,12 @@ static int solve_shard(const SolveJob& job, int slot, int i0, int i1, const std:
   args.lbfgs_memory = job.opts.lbfgs_memory > 0 ? job.opts.lbfgs_memory : 10;
   args.out_x = (double*)b->out_a.p; args.out_f = args.out_x + np;
   args.out_iters = (int32_t*)b->out_b.p; args.out_status = args.out_iters + n;
+  args.ctl = (int*)(args.out_status + n + 2);
+  args.straggler_c = job.opts.straggler_factor;
+  args.sibling_f = job.opts.sibling_stop;
+  args.straggler_min = job.opts.straggler_min_iters > 0 ? (int)job.opts.straggler_min_iters : 32;
+  if (cudaMemsetAsync(args.ctl, 0, n_ctl * sizeof(int32_t), job.ctx->devs[slot].stream) != cudaSuccess)
+    return done(qsb_fail(QSB_ERR_CUDA, "cudaMemsetAsync of the solver control block failed"));
   b->max_params = args.max_params;
   args.prof = nullptr;
   args.chol_smem = 0;
@@ -157,7 +219,11 @@ static int solve_shard(const SolveJob& job, int slot, int i0, int i1, const std:
     case 2: rc = launch_solver_nq<2>(job, b, args, d); break;
     case 3: rc = launch_solver_nq<3>(job, b, args, d); break;
     case 4: rc = launch_solver_nq<4>(job, b, args, d); break;
+#if QSB_SOLVE_TU == 0
+    case 5: rc = qsb_launch_solver_lm5(job, b, args, d); break;
+#else
     case 5: rc = launch_solver_nq<5>(job, b, args, d); break;
+#endif
     default: rc = qsb_fail(QSB_ERR_UNSUPPORTED, "unsupported qubit count");
   }
   if (rc) return done(rc);
@@ -181,7 +247,7 @@ static int solve_shard(const SolveJob& job, int slot, int i0, int i1, const std:
   return done(QSB_OK);
 }
 
-static int solve_dispatch(const SolveJob& job) {
+static int solve_dispatch(SolveJob job) {
   if (!job.ctx || !job.progs || !job.target || !job.out_f || (job.n_instances > 0 && !job.prog_of_instance))
     return qsb_fail(QSB_ERR_INVALID, "NULL argument");
   if (job.n_instances < 0 || job.n_programs <= 0) return qsb_fail(QSB_ERR_INVALID, "bad batch size");
@@ -196,6 +262,7 @@ static int solve_dispatch(const SolveJob& job) {
   }
   poff[job.n_instances] = off;
   if (off > 0 && (!job.x0 || !job.out_x)) return qsb_fail(QSB_ERR_INVALID, "x0 / out_x is NULL");
+  job.target_unitary = job.method == QSB_SOLVE_LM && qsb_target_is_unitary(job.target, job.progs[0]->n_qubits);
   const int used = std::min((int)job.ctx->devs.size(), job.n_instances);
   if (used == 1) return solve_shard(job, 0, 0, job.n_instances, poff);
   std::vector<int> rcs(used, QSB_OK);
@@ -203,13 +270,14 @@ static int solve_dispatch(const SolveJob& job) {
   std::vector<std::thread> th;
   for (int s = 0; s < used; ++s) {
     int i0 = (int)((long long)job.n_instances * s / used), i1 = (int)((long long)job.n_instances * (s + 1) / used);
-    th.emplace_back([&, s, i0, i1] { rcs[s] = solve_shard(job, s, i0, i1, poff); if (rcs[s]) errs[s] = g_err; });
+    th.emplace_back([&, s, i0, i1] { rcs[s] = solve_shard(job, s, i0, i1, poff); if (rcs[s]) errs[s] = qsb_get_error(); });
   }
   for (auto& t : th) t.join();
   for (int s = 0; s < used; ++s) if (rcs[s]) return qsb_fail(rcs[s], errs[s]);
   return QSB_OK;
 }
 
+#if QSB_SOLVE_TU == 0
 extern "C" int qsb_solve_lm(qsb_ctx* ctx, int n_programs, const qsb_program* const* progs, int n_instances,
                             const int32_t* prog_of_instance, const double* x0, const double* target,
                             const qsb_solver_opts* opts, double* out_x, double* out_f, int32_t* out_iters, int32_t* out_status) {
@@ -218,7 +286,7 @@ extern "C" int qsb_solve_lm(qsb_ctx* ctx, int n_programs, const qsb_program* con
   SolveJob j{ctx, n_programs, progs, n_instances, prog_of_instance, x0, target, o, QSB_SOLVE_LM, out_x, out_f, out_iters, out_status};
   return solve_dispatch(j);
 }
-
+#else
 extern "C" int qsb_solve_lbfgs(qsb_ctx* ctx, int n_programs, const qsb_program* const* progs, int n_instances,
                                const int32_t* prog_of_instance, const double* x0, const double* target,
                                const qsb_solver_opts* opts, double* out_x, double* out_f, int32_t* out_iters, int32_t* out_status) {
@@ -227,3 +295,5 @@ extern "C" int qsb_solve_lbfgs(qsb_ctx* ctx, int n_programs, const qsb_program* 
   SolveJob j{ctx, n_programs, progs, n_instances, prog_of_instance, x0, target, o, QSB_SOLVE_LBFGS, out_x, out_f, out_iters, out_status};
   return solve_dispatch(j);
 }
+#endif
+#endif  // QSB_SOLVE_TU != 2

@@ -12,6 +12,12 @@
 
 #define QSB_SYRK_MC 32
 
+// device-side control block of one solve launch (ints, zeroed by the host before the launch)
+#define QSB_CTL_NEXT 0      // next instance of the queue
+#define QSB_CTL_FINISHED 1  // instances finished so far
+#define QSB_CTL_MEDIAN 2    // max Jacobian-evaluation count among the first half of the instances to finish
+#define QSB_CTL_SOLVED 4    // + program index: 1 once an instance of that program finished below the sibling threshold
+
 struct QsbSolveArgs {
   const QsbDevProgram* progs;
   const int32_t* prog_idx;
@@ -31,6 +37,12 @@ struct QsbSolveArgs {
   int cluster;      // qsb_k_lm2: CTAs per instance (thread-block cluster size; 1 in the interpreter kernels)
   int chol_smem;    // qsb_k_lm2: packed Cholesky factor in shared memory (fits) or in global scratch
   long long* prof;  // optional [12] cycle counters (QSB_LM_PROFILE=1): jac, syrk, cholesky, solve, trial, iterations
+  // qsb_k_lm3: device-side queue and batch-level stop rules (see QSB_CTL_* in qsb_lm3.cuh)
+  int* ctl;             // [4 + n_programs] ints, zeroed before the launch
+  double straggler_c;   // > 0: once half of the batch has finished, stop an instance whose Jacobian-evaluation count
+                        // exceeds straggler_c x the largest count among that first half (status 6)
+  int straggler_min;    // ... but never before this many evaluations
+  double sibling_f;     // > 0: stop an instance once another instance of the same program finished below this distance (status 7)
 };
 
 QSB_DEVICE double qsb_block_max(double v, cplx* red) {
