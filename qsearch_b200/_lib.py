@@ -56,6 +56,8 @@ class Library:
         self._ctx = None
         self._devices = devices
         self._lock = threading.Lock()
+        self._plock = threading.RLock()
+        self._programs = {}
         self._pid = None
 
     # ------------------------------------------------------------------ plumbing
@@ -110,7 +112,7 @@ class Library:
                         ids = (ctypes.c_int32 * len(self._devices))(*self._devices)
                         self.check(self.dll.qsb_init(len(self._devices), ids, ctypes.byref(ctx)))
                     self._ctx, self._pid = ctx, pid
-                    self._programs = {}
+                    self._programs = {}  # key -> [handle, GateProgram, reference count], least recently used first
         return self._ctx
 
     @property
@@ -138,94 +140,139 @@ class Library:
         return n.value
 
     # ------------------------------------------------------------------ programs
-    def program(self, gp):
-        """Device handle for a lowering.GateProgram (uploaded once per context, cached by identity key)."""
+    PROGRAM_CACHE_LIMIT = 4096
+
+    def _acquire(self, gps):
+        """Device handles of GatePrograms (uploaded once per context, cached by identity key), each with one more
+        reference.  Entries are only ever destroyed when nobody references them: a live Batch and every call in flight
+        hold references, so eviction can never free a program a kernel may still read (the cache is an LRU bounded at
+        PROGRAM_CACHE_LIMIT idle entries + whatever is referenced)."""
         ctx = self.ctx
-        key = gp.key if gp.key is not None else id(gp)
-        ent = self._programs.get(key)
-        h = ent[0] if ent is not None else None
-        if h is None:
-            ops = np.ascontiguousarray(gp.ops, dtype=OP_DTYPE)
-            h = _vp()
-            self.check(self.dll.qsb_program_create(ctx, gp.n_qubits, len(ops), ops.ctypes.data_as(_vp), gp.n_params,
-                                                   _dp(gp.consts), gp.consts.size, ctypes.byref(h)))
-            self._programs[key] = (h, gp)  # keep gp alive so an id()-based key cannot be reused
-            if len(self._programs) > 4096:  # bound the cache: drop the oldest half
-                for k in list(self._programs)[:2048]:
-                    if k != key:
-                        self.dll.qsb_program_destroy(ctx, self._programs.pop(k)[0])
-        return h
+        with self._plock:
+            keys = [gp.key if gp.key is not None else id(gp) for gp in gps]
+            if len(self._programs) + len(keys) > self.PROGRAM_CACHE_LIMIT:
+                need = set(keys)
+                for k in list(self._programs):
+                    if len(self._programs) <= self.PROGRAM_CACHE_LIMIT // 2:
+                        break
+                    ent = self._programs[k]
+                    if ent[2] == 0 and k not in need:
+                        self.dll.qsb_program_destroy(ctx, ent[0])
+                        del self._programs[k]
+            handles = []
+            for gp, key in zip(gps, keys):
+                ent = self._programs.get(key)
+                if ent is None:
+                    ops = np.ascontiguousarray(gp.ops, dtype=OP_DTYPE)
+                    h = _vp()
+                    self.check(self.dll.qsb_program_create(ctx, gp.n_qubits, len(ops), ops.ctypes.data_as(_vp), gp.n_params,
+                                                           _dp(gp.consts), gp.consts.size, ctypes.byref(h)))
+                    ent = [h, gp, 0]  # keep gp alive so an id()-based key cannot be reused
+                else:
+                    del self._programs[key]  # re-insert below: most recently used last
+                self._programs[key] = ent
+                ent[2] += 1
+                handles.append(ent[0])
+        return keys, handles
+
+    def _release(self, keys):
+        with self._plock:
+            for k in keys:
+                ent = self._programs.get(k)
+                if ent is not None and ent[2] > 0:
+                    ent[2] -= 1
+
+    def program(self, gp):
+        """Device handle for one GateProgram (no reference kept: use _acquire / _release around launches)."""
+        keys, handles = self._acquire([gp])
+        self._release(keys)
+        return handles[0]
+
+    class _Packed:
+        """Arguments of one host-buffer call; holds program references until the call returns."""
+
+        def __init__(self, lib, gps, prog_of_instance, params):
+            self.lib = lib
+            self.keys, hs = lib._acquire(gps)
+            self.handles = (_vp * len(gps))(*hs)
+            self.poi = np.ascontiguousarray(prog_of_instance, dtype="int32")
+            self.params = _f64(params).ravel()
+            self.sizes = np.array([g.n_params for g in gps], dtype="int64")[self.poi]
+            if self.params.size != int(self.sizes.sum()):
+                lib._release(self.keys)
+                raise ValueError("expected {} parameters in total, got {}".format(int(self.sizes.sum()), self.params.size))
+
+        def __enter__(self):
+            return self.handles, self.poi, self.params, self.sizes
+
+        def __exit__(self, *exc):
+            self.lib._release(self.keys)
+            return False
 
     def _pack(self, gps, prog_of_instance, params):
-        handles = (_vp * len(gps))(*[self.program(g) for g in gps])
-        poi = np.ascontiguousarray(prog_of_instance, dtype="int32")
-        params = _f64(params).ravel()
-        sizes = np.array([g.n_params for g in gps], dtype="int64")[poi]
-        if params.size != int(sizes.sum()):
-            raise ValueError("expected {} parameters in total, got {}".format(int(sizes.sum()), params.size))
-        return handles, poi, params, sizes
+        return Library._Packed(self, gps, prog_of_instance, params)
 
     # ------------------------------------------------------------------ host-buffer evaluation
     def eval_matrix(self, gps, prog_of_instance, params):
-        handles, poi, params, _ = self._pack(gps, prog_of_instance, params)
-        N = 1 << gps[0].n_qubits
-        U = np.empty((len(poi), N, N), dtype="complex128")
-        self.check(self.dll.qsb_eval_matrix(self.ctx, len(gps), handles, len(poi), poi.ctypes.data_as(_c_ip), _dp(params),
-                                            U.ctypes.data_as(_c_dp)))
+        with self._pack(gps, prog_of_instance, params) as (handles, poi, params, _):
+            N = 1 << gps[0].n_qubits
+            U = np.empty((len(poi), N, N), dtype="complex128")
+            self.check(self.dll.qsb_eval_matrix(self.ctx, len(gps), handles, len(poi), poi.ctypes.data_as(_c_ip), _dp(params),
+                                                U.ctypes.data_as(_c_dp)))
         return U
 
     def eval_mat_jac(self, gps, prog_of_instance, params):
-        handles, poi, params, sizes = self._pack(gps, prog_of_instance, params)
-        N = 1 << gps[0].n_qubits
-        U = np.empty((len(poi), N, N), dtype="complex128")
-        J = np.empty((int(sizes.sum()), N, N), dtype="complex128")
-        self.check(self.dll.qsb_eval_mat_jac(self.ctx, len(gps), handles, len(poi), poi.ctypes.data_as(_c_ip), _dp(params),
-                                             U.ctypes.data_as(_c_dp), J.ctypes.data_as(_c_dp)))
+        with self._pack(gps, prog_of_instance, params) as (handles, poi, params, sizes):
+            N = 1 << gps[0].n_qubits
+            U = np.empty((len(poi), N, N), dtype="complex128")
+            J = np.empty((int(sizes.sum()), N, N), dtype="complex128")
+            self.check(self.dll.qsb_eval_mat_jac(self.ctx, len(gps), handles, len(poi), poi.ctypes.data_as(_c_ip), _dp(params),
+                                                 U.ctypes.data_as(_c_dp), J.ctypes.data_as(_c_dp)))
         return U, J
 
     def eval_hs_grad(self, gps, prog_of_instance, params, target):
-        handles, poi, params, sizes = self._pack(gps, prog_of_instance, params)
-        T = np.ascontiguousarray(target, dtype="complex128")
-        f = np.empty(len(poi), dtype="float64")
-        g = np.empty(int(sizes.sum()), dtype="float64")
-        self.check(self.dll.qsb_eval_hs_grad(self.ctx, len(gps), handles, len(poi), poi.ctypes.data_as(_c_ip), _dp(params),
-                                             T.ctypes.data_as(_c_dp), _dp(f), _dp(g)))
+        with self._pack(gps, prog_of_instance, params) as (handles, poi, params, sizes):
+            T = np.ascontiguousarray(target, dtype="complex128")
+            f = np.empty(len(poi), dtype="float64")
+            g = np.empty(int(sizes.sum()), dtype="float64")
+            self.check(self.dll.qsb_eval_hs_grad(self.ctx, len(gps), handles, len(poi), poi.ctypes.data_as(_c_ip), _dp(params),
+                                                 T.ctypes.data_as(_c_dp), _dp(f), _dp(g)))
         return f, g
 
     def eval_distance(self, gps, prog_of_instance, params, target):
-        handles, poi, params, _ = self._pack(gps, prog_of_instance, params)
-        T = np.ascontiguousarray(target, dtype="complex128")
-        f = np.empty(len(poi), dtype="float64")
-        self.check(self.dll.qsb_eval_distance(self.ctx, len(gps), handles, len(poi), poi.ctypes.data_as(_c_ip), _dp(params),
-                                              T.ctypes.data_as(_c_dp), _dp(f)))
+        with self._pack(gps, prog_of_instance, params) as (handles, poi, params, _):
+            T = np.ascontiguousarray(target, dtype="complex128")
+            f = np.empty(len(poi), dtype="float64")
+            self.check(self.dll.qsb_eval_distance(self.ctx, len(gps), handles, len(poi), poi.ctypes.data_as(_c_ip), _dp(params),
+                                                  T.ctypes.data_as(_c_dp), _dp(f)))
         return f
 
     def eval_residuals_jac(self, gps, prog_of_instance, params, target, out_r=None, out_Jr=None):
         """r: [inst, 2N^2]; Jr: [sum P, 2N^2] (row k = parameter k; the reference's array is its transpose view)."""
-        handles, poi, params, sizes = self._pack(gps, prog_of_instance, params)
-        N = 1 << gps[0].n_qubits
-        T = np.ascontiguousarray(target, dtype="complex128")
-        r = out_r if out_r is not None else np.empty((len(poi), 2 * N * N), dtype="float64")
-        Jr = out_Jr if out_Jr is not None else np.empty((int(sizes.sum()), 2 * N * N), dtype="float64")
-        self.check(self.dll.qsb_eval_residuals_jac(self.ctx, len(gps), handles, len(poi), poi.ctypes.data_as(_c_ip),
-                                                   _dp(params), T.ctypes.data_as(_c_dp), _dp(r), _dp(Jr)))
+        with self._pack(gps, prog_of_instance, params) as (handles, poi, params, sizes):
+            N = 1 << gps[0].n_qubits
+            T = np.ascontiguousarray(target, dtype="complex128")
+            r = out_r if out_r is not None else np.empty((len(poi), 2 * N * N), dtype="float64")
+            Jr = out_Jr if out_Jr is not None else np.empty((int(sizes.sum()), 2 * N * N), dtype="float64")
+            self.check(self.dll.qsb_eval_residuals_jac(self.ctx, len(gps), handles, len(poi), poi.ctypes.data_as(_c_ip),
+                                                       _dp(params), T.ctypes.data_as(_c_dp), _dp(r), _dp(Jr)))
         return r, Jr
 
     # ------------------------------------------------------------------ solvers
     def solve(self, method, gps, prog_of_instance, x0, target, max_iters=0, ftol=0.0, xtol=0.0, gtol=0.0,
               stop_value=0.0, lbfgs_memory=10, straggler_factor=0.0, sibling_stop=0.0, straggler_min_iters=0.0):
-        handles, poi, x0, sizes = self._pack(gps, prog_of_instance, x0)
-        T = np.ascontiguousarray(target, dtype="complex128")
-        opts = SolverOpts(max_iters=max_iters, lbfgs_memory=lbfgs_memory, ftol=ftol, xtol=xtol, gtol=gtol,
-                          stop_value=stop_value, straggler_factor=straggler_factor, sibling_stop=sibling_stop,
-                          straggler_min_iters=straggler_min_iters)
-        x = np.empty_like(x0)
-        f = np.empty(len(poi), dtype="float64")
-        iters = np.empty(len(poi), dtype="int32")
-        status = np.empty(len(poi), dtype="int32")
-        fn = self.dll.qsb_solve_lm if method == "lm" else self.dll.qsb_solve_lbfgs
-        self.check(fn(self.ctx, len(gps), handles, len(poi), poi.ctypes.data_as(_c_ip), _dp(x0), T.ctypes.data_as(_c_dp),
-                      ctypes.byref(opts), _dp(x), _dp(f), iters.ctypes.data_as(_c_ip), status.ctypes.data_as(_c_ip)))
+        with self._pack(gps, prog_of_instance, x0) as (handles, poi, x0, sizes):
+            T = np.ascontiguousarray(target, dtype="complex128")
+            opts = SolverOpts(max_iters=max_iters, lbfgs_memory=lbfgs_memory, ftol=ftol, xtol=xtol, gtol=gtol,
+                              stop_value=stop_value, straggler_factor=straggler_factor, sibling_stop=sibling_stop,
+                              straggler_min_iters=straggler_min_iters)
+            x = np.empty_like(x0)
+            f = np.empty(len(poi), dtype="float64")
+            iters = np.empty(len(poi), dtype="int32")
+            status = np.empty(len(poi), dtype="int32")
+            fn = self.dll.qsb_solve_lm if method == "lm" else self.dll.qsb_solve_lbfgs
+            self.check(fn(self.ctx, len(gps), handles, len(poi), poi.ctypes.data_as(_c_ip), _dp(x0), T.ctypes.data_as(_c_dp),
+                          ctypes.byref(opts), _dp(x), _dp(f), iters.ctypes.data_as(_c_ip), status.ctypes.data_as(_c_ip)))
         return x, f, iters, status
 
     def measure_fp64_peak(self, slot=0, use_dmma=False):
@@ -247,10 +294,18 @@ class Batch:
         self.poi = np.ascontiguousarray(prog_of_instance, dtype="int32")
         self.sizes = np.array([g.n_params for g in self.gps], dtype="int64")[self.poi]
         self.n_qubits = self.gps[0].n_qubits
-        handles = (_vp * len(self.gps))(*[lib.program(g) for g in self.gps])
-        self.h = _vp()
-        lib.check(lib.dll.qsb_batch_create(lib.ctx, slot, len(self.gps), handles, len(self.poi),
-                                           self.poi.ctypes.data_as(_c_ip), ctypes.byref(self.h)))
+        self.h = None
+        self._keys, hs = lib._acquire(self.gps)  # the batch keeps its programs referenced until close()
+        handles = (_vp * len(self.gps))(*hs)
+        h = _vp()
+        try:
+            lib.check(lib.dll.qsb_batch_create(lib.ctx, slot, len(self.gps), handles, len(self.poi),
+                                               self.poi.ctypes.data_as(_c_ip), ctypes.byref(h)))
+        except Exception:
+            lib._release(self._keys)
+            self._keys = []
+            raise
+        self.h = h
 
     def set_kernel(self, kind):
         """0 = automatic (DMMA warp kernels where they apply), 1 = shared-memory interpreter."""
@@ -305,6 +360,8 @@ class Batch:
         if self.h is not None and self.h.value:
             self.lib.dll.qsb_batch_destroy(self.h)
             self.h = None
+            self.lib._release(self._keys)
+            self._keys = []
 
     def __del__(self):
         try:

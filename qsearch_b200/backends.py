@@ -7,6 +7,8 @@ evaluates on the B200 through libqsb200.so.  Like ``PyGateWrapper`` (lib.rs:280-
 raise ``ValueError`` (lib.rs:270-273).  There is no silent fallback to a CPU circuit (contrast
 ``SmartDefaultBackend``, backends.py:37-41).
 """
+import hashlib
+
 import numpy as np
 
 from . import _lib
@@ -33,14 +35,21 @@ _PROGRAM_CACHE = {}
 
 
 def program_for(circ):
-    """GateProgram of a circuit structure, cached by repr() - the reference's own notion of gate identity
-    (qsearch/gates.py:82-86)."""
+    """GateProgram of a circuit structure.  Structures without captured constants are cached by repr() - the reference's
+    own notion of gate identity (qsearch/gates.py:82-86).  A tree that captures constant matrices (UGate, CUGate, any
+    unknown zero-parameter gate: lowering.py CONST1 / CONSTK) is lowered every time and keyed by the exact bytes of its
+    program and constant pool: NumPy's repr of a matrix keeps 8 digits and elides large arrays, so two circuits whose
+    constants differ below that would otherwise share one device program."""
     if isinstance(circ, CudaCircuit):
         return circ.program
     key = repr(circ)
     gp = _PROGRAM_CACHE.get(key)
     if gp is None:
         gp = lower(circ)
+        if gp.consts.size:
+            gp.key = ("const", gp.n_qubits, gp.n_params, hashlib.sha1(np.ascontiguousarray(gp.ops).tobytes()).hexdigest(),
+                      hashlib.sha1(gp.consts.tobytes()).hexdigest())
+            return gp
         gp.key = key
         if len(_PROGRAM_CACHE) > 8192:
             _PROGRAM_CACHE.clear()

@@ -51,7 +51,8 @@ def _frontier(parallel, options, new_steps):
     if hasattr(parallel, "solve_frontier"):
         return parallel.solve_frontier(new_steps)
     ev = options.objective.gen_eval_func
-    return [(s, r, d, w, ev(s, options)(r[1])) for s, r, d, w in parallel.solve_circuits_parallel(new_steps)]
+    from .solvers import finite_or_inf
+    return [(s, r, d, w, finite_or_inf(ev(s, options)(r[1]))) for s, r, d, w in parallel.solve_circuits_parallel(new_steps)]
 
 
 def _better(value, weight, best_value, best_weight, threshold):
@@ -62,11 +63,14 @@ def _better(value, weight, best_value, best_weight, threshold):
 
 def _solve_root(root, options):
     solver = options.solver
+    from .solvers import finite_or_inf, rides_on_device
     if hasattr(solver, "solve_batch"):
         res = solver.solve_batch([root], options)
-        return res.x[0], res.distance[0]
+        if rides_on_device(options):
+            return res.x[0], res.distance[0]
+        return res.x[0], finite_or_inf(options.objective.gen_eval_func(root, options)(res.x[0]))
     U, x = solver.solve_for_unitary(options.backend.prepare_circuit(root, options), options)
-    return x, options.objective.gen_eval_func(root, options)(x)
+    return x, finite_or_inf(options.objective.gen_eval_func(root, options)(x))
 
 
 class SearchCompiler(Compiler):

@@ -28,7 +28,7 @@ struct QsbQGeom {
   static constexpr int TT = N / 8;               // 8-wide column tiles: a warp holds ALL columns of X
   static constexpr int NOFF = TT * (TT - 1) / 2; // strictly-lower 8x8 tiles of a Hermitian N x N
   static constexpr int K2 = N * N;               // packed reals per Hermitian matrix: TT * 64 + NOFF * 128
-  static constexpr int WARPS = NQ >= 5 ? 8 : 4;  // warps per CTA (= per instance)
+  static constexpr int WARPS = 8;                 // warps per CTA (= per instance)
 };
 
 // device-side control block of one solve launch: QSB_CTL_* in qsb_solver.cuh
@@ -78,6 +78,268 @@ QSB_DEVICE void qsb_fill_gates_body(const QsbDevProgram& P, const double* trig, 
     }
     gtab[4 * s] = g[0]; gtab[4 * s + 1] = g[1]; gtab[4 * s + 2] = g[2]; gtab[4 * s + 3] = g[3];
   }
+}
+
+// ---------------------------------------------------------------------------- Gram product into a PACKED lower triangle
+// A[TRI(k, l)] = sum_m R[k][m] R[l][m], l <= k < rows.  Same tiling as qsb_syrk_dmma_t (qsb_lm2.cuh), but
+//   * the result goes to the packed layout the factorisation works in (a linear copy brings it to shared memory);
+//   * 8-row tiles that lie entirely beyond `rows`, and the upper-right quarter of a diagonal block, are skipped
+//     (rows = 166 with 32-wide blocks: 60 instead of 84 16x16 tile products).
+template <int TW>
+QSB_DEVICE void qsb_syrk_packed_t(const double* R, int rows, int K2, double* A, int task0, int stride, int lane, int ksplit) {
+  constexpr int TB = 8 * TW;
+  const int g = lane >> 2, t = lane & 3;
+  const int nb = (rows + TB - 1) / TB, ntasks = nb * (nb + 1) / 2 * ksplit;
+  const int klen = K2 / ksplit;
+  for (int task = task0; task < ntasks; task += stride) {
+    const int tile = task / ksplit, kbeg = (task % ksplit) * klen;
+    int bk = (int)((sqrt(8.0 * tile + 1.0) - 1.0) * 0.5);
+    while ((bk + 1) * (bk + 2) / 2 <= tile) ++bk;
+    while (bk * (bk + 1) / 2 > tile) --bk;
+    const int bl = tile - bk * (bk + 1) / 2;
+    const int ni = (rows - TB * bk + 7) / 8 < TW ? (rows - TB * bk + 7) / 8 : TW;  // 8-row tiles of block bk that hold rows
+    const bool diag = bk == bl;
+    double acc[TW][TW][2];
+    const double* pa[TW];
+    const double* pb[TW];
+#pragma unroll
+    for (int i = 0; i < TW; ++i) {
+      int ra = TB * bk + 8 * i + g, rb = TB * bl + 8 * i + g;
+      if (ra > rows - 1) ra = rows - 1;
+      if (rb > rows - 1) rb = rows - 1;
+      pa[i] = R + (size_t)ra * K2 + kbeg + 4 * t;
+      pb[i] = R + (size_t)rb * K2 + kbeg + 4 * t;
+#pragma unroll
+      for (int j = 0; j < TW; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
+    }
+#pragma unroll 2
+    for (int m0 = 0; m0 < klen; m0 += 16) {
+      double2 av[TW][2], bv[TW][2];
+#pragma unroll
+      for (int i = 0; i < TW; ++i) {
+        if (i < ni) { av[i][0] = QSB_LDCG2(pa[i] + m0); av[i][1] = QSB_LDCG2(pa[i] + m0 + 2); }
+        else { av[i][0] = av[i][1] = make_double2(0.0, 0.0); }
+        bv[i][0] = QSB_LDCG2(pb[i] + m0); bv[i][1] = QSB_LDCG2(pb[i] + m0 + 2);
+      }
+#pragma unroll
+      for (int s4 = 0; s4 < 4; ++s4)
+#pragma unroll
+        for (int i = 0; i < TW; ++i) {
+          if (i >= ni) continue;  // warp-uniform
+#pragma unroll
+          for (int j = 0; j < TW; ++j) {
+            if (diag && j > i) continue;  // only the lower 8x8 tiles of a diagonal block
+            const double x = (s4 & 1) ? av[i][s4 >> 1].y : av[i][s4 >> 1].x, y = (s4 & 1) ? bv[j][s4 >> 1].y : bv[j][s4 >> 1].x;
+            qsb_dmma884(acc[i][j][0], acc[i][j][1], x, y);
+          }
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < TW; ++i)
+#pragma unroll
+      for (int j = 0; j < TW; ++j)
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          const int k = TB * bk + 8 * i + g, l = TB * bl + 8 * j + 2 * t + e;
+          if (k < rows && l <= k) {
+            if (ksplit == 1) A[QSB_TRI(k, l)] = acc[i][j][e];
+            else atomicAdd(&A[QSB_TRI(k, l)], acc[i][j][e]);
+          }
+        }
+  }
+}
+
+QSB_DEVICE void qsb_syrk_packed(const double* R, int rows, int K2, double* A, int warp, int nwarps, int lane) {
+  const int plan = qsb_syrk_plan(rows, nwarps), ks = plan >> 8;
+  if ((plan & 255) == 4) qsb_syrk_packed_t<4>(R, rows, K2, A, warp, nwarps, lane, ks);
+  else qsb_syrk_packed_t<2>(R, rows, K2, A, warp, nwarps, lane, ks);
+}
+
+// ---------------------------------------------------------------------------- factorisation with inverted diagonal blocks
+// Same augmented, packed, right-looking Cholesky as qsb_chol_packed (qsb_lm2.cuh), with three changes that take the
+// serial work off the critical path of an LM iteration:
+//   * the matrix arrives packed (qsb_syrk_packed), so the copy into shared memory is linear and vectorised;
+//   * the warp that factors a 16x16 diagonal block also inverts it (W = L_kk^-1, interleaved with the pivot chain), so
+//     the panel below it is ONE tensor-core product X = A_panel W^T instead of a 136-step substitution per row;
+//   * the inverses are kept ([block][16][16] in shared memory): the back-substitution is one 16x16 matrix-vector
+//     product per block instead of one reduction per row.
+#define QSB_CH3_WSZ 256  // doubles per inverted diagonal block
+
+// diagonal block [kb, kb + nbk): lane = row, the row in registers; leaves L in Ls, W (row-major 16x16, zero above the
+// diagonal, identity in the padding) in Wb, 1 / L_jj in rdiag[kb + j]
+QSB_DEVICE void qsb_ch3_diag(double* Ls, int kb, int nbk, double* Wb, double* rdiag, int* okflag, int lane) {
+  constexpr int NB = QSB_CH_NB;
+  const int i = kb + lane;
+  double d[NB], w[NB];
+#pragma unroll
+  for (int j = 0; j < NB; ++j) {
+    d[j] = (lane < nbk && j <= lane) ? Ls[QSB_TRI(i, kb + j)] : ((j == lane) ? 1.0 : 0.0);
+    w[j] = (j == lane) ? 1.0 : 0.0;
+  }
+  bool good = true;
+#pragma unroll
+  for (int j = 0; j < NB; ++j) {
+    const double piv = __shfl_sync(QSB_FULL, d[j], j);
+    if (!(piv > 0.0) || !(piv < 1e300)) { good = false; break; }
+    const double inv = rsqrt(piv);
+    if (lane == j && j < nbk) rdiag[kb + j] = inv;
+    d[j] = (lane == j) ? piv * inv : d[j] * inv;
+#pragma unroll
+    for (int k = j + 1; k < NB; ++k) d[k] = fma(-d[j], __shfl_sync(QSB_FULL, d[j], k), d[k]);
+    // row j of W is final once scaled by 1 / L_jj; rows below subtract L_ij times it (columns c <= j)
+#pragma unroll
+    for (int c = 0; c <= j; ++c) {
+      if (lane == j) w[c] *= inv;
+      const double wj = __shfl_sync(QSB_FULL, w[c], j);
+      if (lane > j) w[c] = fma(-d[j], wj, w[c]);
+    }
+  }
+  if (!good && lane == 0) *okflag = 0;
+  if (lane < NB) {
+#pragma unroll
+    for (int j = 0; j < NB; ++j) {
+      if (lane < nbk && j <= lane) Ls[QSB_TRI(i, kb + j)] = d[j];
+      Wb[lane * NB + j] = (j <= lane) ? w[j] : 0.0;
+    }
+  }
+}
+
+// panel below the diagonal block: rows R0 .. rows-1, X = A_panel W^T, one 8-row tile per warp and round
+QSB_DEVICE void qsb_ch3_panel(double* Ls, int R0, int kb, int nbk, int nrow, const double* Wb, int warp, int nwarps, int lane) {
+  constexpr int NB = QSB_CH_NB;
+  const int g = lane >> 2, t = lane & 3;
+  double bw[2][NB / 4];  // B fragments of W^T: B[k][n] = W[n][k]
+#pragma unroll
+  for (int nt = 0; nt < 2; ++nt)
+#pragma unroll
+    for (int ks = 0; ks < NB / 4; ++ks) bw[nt][ks] = Wb[(8 * nt + g) * NB + 4 * ks + t];
+  const int nmt = (nrow + 7) >> 3;
+  for (int mt = warp; mt < nmt; mt += nwarps) {
+    int r = 8 * mt + g;
+    const bool rv = r < nrow;
+    if (!rv) r = nrow - 1;
+    double* src = Ls + QSB_TRI(R0 + r, kb);
+    double a[NB / 4];
+#pragma unroll
+    for (int ks = 0; ks < NB / 4; ++ks) a[ks] = (4 * ks + t < nbk) ? src[4 * ks + t] : 0.0;
+    double c0[2] = {0.0, 0.0}, c1[2] = {0.0, 0.0};
+#pragma unroll
+    for (int ks = 0; ks < NB / 4; ++ks) {
+      qsb_dmma884(c0[0], c0[1], a[ks], bw[0][ks]);
+      qsb_dmma884(c1[0], c1[1], a[ks], bw[1][ks]);
+    }
+    __syncwarp();  // every lane has read its row before anybody overwrites it
+    if (rv) {
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        if (2 * t + e < nbk) src[2 * t + e] = c0[e];
+        if (8 + 2 * t + e < nbk) src[8 + 2 * t + e] = c1[e];
+      }
+    }
+  }
+}
+
+// Apk: packed Gram matrix of [Q ; -C] in global memory (rows = P + 1).  Returns false (uniformly) if a pivot is not positive.
+QSB_DEVICE bool qsb_chol3(const double* Apk, int rows, const double* d2, double mu, int P, double* Ls, double* Winv, double* rdiag,
+                          int* okflag, long long* prof) {
+#define QSB_CH_T(slot) do { if (prof && threadIdx.x == 0) { const long long _n = QSB_CLOCK(); atomicAdd((unsigned long long*)&prof[slot], (unsigned long long)(_n - _tc)); _tc = _n; } } while (0)
+  long long _tc = prof ? QSB_CLOCK() : 0ll;
+  constexpr int NB = QSB_CH_NB;
+  const int lane = threadIdx.x & 31, warp = qsb_warp_index(), nwarps = blockDim.x >> 5;
+  const int tri = rows * (rows + 1) / 2;
+  __syncthreads();
+  for (int e = 2 * threadIdx.x; e + 1 < tri; e += 2 * blockDim.x) {
+    const double2 v = QSB_LDCG2(Apk + e);
+    *reinterpret_cast<double2*>(Ls + e) = v;
+  }
+  if ((tri & 1) && threadIdx.x == 0) Ls[tri - 1] = QSB_LDCG(Apk + tri - 1);
+  if (threadIdx.x == 0) *okflag = 1;
+  __syncthreads();
+  for (int k = threadIdx.x; k < P; k += blockDim.x) Ls[QSB_TRI(k, k)] += mu * d2[k];
+  __syncthreads();
+  QSB_CH_T(6);
+  if (warp == 0) qsb_ch3_diag(Ls, 0, (P < NB) ? P : NB, Winv, rdiag, okflag, lane);
+  __syncthreads();
+  QSB_CH_T(7);
+  for (int kb = 0; kb < P; kb += NB) {
+    const int nbk = (P - kb < NB) ? P - kb : NB;
+    if (!*okflag) { __syncthreads(); return false; }
+    const int R0 = kb + nbk, nrow = rows - R0;
+    qsb_ch3_panel(Ls, R0, kb, nbk, nrow, Winv + (size_t)(kb / NB) * QSB_CH3_WSZ, warp, nwarps, lane);
+    __syncthreads();
+    QSB_CH_T(8);
+    if (R0 < P) {  // trailing update, 16x16 DMMA tiles of the lower triangle
+      const int nbt = (nrow + 15) >> 4;
+      for (int bi = warp; bi < nbt; bi += nwarps) qsb_chp_tile(Ls, R0, kb, nbk, nrow, bi, 0, lane);  // first block column
+      __syncthreads();
+      const int nbk1 = (P - R0 < NB) ? P - R0 : NB;
+      if (warp == 0) qsb_ch3_diag(Ls, R0, nbk1, Winv + (size_t)(R0 / NB) * QSB_CH3_WSZ, rdiag, okflag, lane);  // next diagonal block ...
+      if (warp != 0 || nwarps == 1) {                                                                          // ... under the rest of the update
+        const int nw = (nwarps == 1) ? 1 : nwarps - 1, w = (nwarps == 1) ? 0 : warp - 1;
+        int bi = 1, bj = 1;
+        for (int skip = w; skip > 0; --skip) { if (++bj > bi) { ++bi; bj = 1; } }
+        while (bi < nbt) {
+          qsb_chp_tile(Ls, R0, kb, nbk, nrow, bi, bj, lane);
+          for (int skip = nw; skip > 0; --skip) { if (++bj > bi) { ++bi; bj = 1; } }
+        }
+      }
+      __syncthreads();
+    }
+    QSB_CH_T(9);
+  }
+  if (!*okflag) { __syncthreads(); return false; }
+  return true;
+#undef QSB_CH_T
+}
+
+// h = -(L^T)^-1 y, y = row P of the packed factor: one warp, one 16-row block per step.  With W_b = L_bb^-1:
+//   h_b = W_b^T (z_b),   z = -y - sum over later blocks c of L_cb^T h_c  (folded into z as soon as h_c is known)
+// zs: 32 doubles of shared memory.
+QSB_DEVICE void qsb_ch3_back(const double* Ls, int P, const double* Winv, double* zs, double* h) {
+  constexpr int NB = QSB_CH_NB;
+  const int lane = threadIdx.x & 31, warp = qsb_warp_index();
+  __syncthreads();
+  if (warp == 0) {
+    constexpr int NR = (QSB_CH_MAXROWS + 31) / 32;
+    const double* y = Ls + QSB_TRI(P, 0);
+    double z[NR];
+#pragma unroll
+    for (int b = 0; b < NR; ++b) {
+      const int i = 32 * b + lane;
+      z[b] = (i < P) ? -y[i] : 0.0;
+    }
+    for (int blk = (P + NB - 1) / NB - 1; blk >= 0; --blk) {
+      const int kb = NB * blk;
+      const double* Wb = Winv + (size_t)blk * QSB_CH3_WSZ;
+      const int chunk = kb >> 5, off = kb & 31, li = lane - off;  // the block's rows sit in z[chunk], lanes off .. off + 15
+      double zb = 0.0;
+#pragma unroll
+      for (int b = 0; b < NR; ++b) if (b == chunk) zb = z[b];
+      if (li >= 0 && li < NB) zs[li] = zb;
+      __syncwarp();
+      double hb = 0.0;
+      if (li >= 0 && li < NB) {
+#pragma unroll
+        for (int j = 0; j < NB; ++j) hb = fma(Wb[j * NB + li], zs[j], hb);  // W is zero above its diagonal: j >= li only
+        zs[NB + li] = hb;
+        if (kb + li < P) h[kb + li] = hb;
+      }
+      __syncwarp();
+      // fold h_b into the right-hand side of the earlier rows: z[i] -= sum_j L[kb + j][i] h_b[j], i < kb
+      const int nbk = (P - kb < NB) ? P - kb : NB;
+#pragma unroll
+      for (int b = 0; b < NR; ++b) {
+        const int i = 32 * b + lane;
+        if (i < kb) {
+          double s = z[b];
+          for (int j = 0; j < nbk; ++j) s = fma(-Ls[QSB_TRI(kb + j, i)], zs[NB + j], s);
+          z[b] = s;
+        }
+      }
+      __syncwarp();
+    }
+  }
+  __syncthreads();
 }
 
 // One parameter whose qubit sits at k-step bit KB: packed Q = gamma I + Y^dagger Y, Y = (w^T (x) I) X, into `row`
@@ -298,14 +560,15 @@ QSB_GLOBAL __launch_bounds__(QsbQGeom<NQ>::WARPS * 32) qsb_k_lm3(QsbSolveArgs a)
   double* wk = d2 + a.max_params;
   double* trig = wk + a.max_params;         // 2 * maxP
   double* part = trig + 2 * a.max_params;   // 16
-  cplx* gtab = (cplx*)(part + 16 + (a.max_params & 1));  // [max_ops + max_params][4], 16-byte aligned
+  cplx* gtab = (cplx*)(part + 16);  // [max_ops + max_params][4]; 16-byte aligned: 8 maxP + 16 doubles precede it
   int* seg = (int*)(gtab + (size_t)4 * (a.max_ops + a.max_params));  // NW + 1 (<= 12 ints), then [12] = queue slot, [13] = ok flag
   qsb_op* sops = (qsb_op*)(seg + 16);       // the program's ops, staged once per instance
   double* Ls = (double*)(sops + a.max_ops); // packed Cholesky factor; during the sweep the same bytes hold V
   Ls = (double*)(((uintptr_t)Ls + 15) & ~(uintptr_t)15);
   cplx* vsm = (cplx*)Ls;
   const size_t tri = (size_t)(a.max_params + 1) * (a.max_params + 2) / 2;
-  double* rinv = Ls + (tri > (size_t)2 * N * N ? tri : (size_t)2 * N * N);
+  double* Winv = Ls + (((tri > (size_t)2 * N * N ? tri : (size_t)2 * N * N) + 1) & ~(size_t)1);  // [ceil(maxP / 16)][256]
+  double* zs = Winv + (size_t)((a.max_params + QSB_CH_NB - 1) / QSB_CH_NB) * QSB_CH3_WSZ;  // 32
   int* okflag = seg + 13;
   const int lane = threadIdx.x & 31, warp = qsb_warp_index();
   double* Rg = a.scratch + (size_t)blockIdx.x * a.scratch_per_cta;
@@ -335,14 +598,14 @@ QSB_GLOBAL __launch_bounds__(QsbQGeom<NQ>::WARPS * 32) qsb_k_lm3(QsbSolveArgs a)
       iters = 1;
       {
         QSB_PROF_BEGIN();
-        if (kzero) { for (int e = threadIdx.x; e < rows * rows; e += blockDim.x) A[e] = 0.0; __syncthreads(); }
-        qsb_syrk_dmma(Rg, rows, K2, A, warp, NW, lane);
+        if (kzero) { for (int e = threadIdx.x; e < rows * (rows + 1) / 2; e += blockDim.x) A[e] = 0.0; __syncthreads(); }
+        qsb_syrk_packed(Rg, rows, K2, A, warp, NW, lane);
         __syncthreads();
         QSB_PROF_END(1);
       }
       for (int k = threadIdx.x; k < P; k += blockDim.x) {
-        g[k] = QSB_LDCG(&A[(size_t)P * rows + k]);
-        const double akk = QSB_LDCG(&A[(size_t)k * rows + k]);
+        g[k] = QSB_LDCG(&A[QSB_TRI(P, k)]);
+        const double akk = QSB_LDCG(&A[QSB_TRI(k, k)]);
         d2[k] = akk > 0.0 ? akk : 1.0;
       }
       __syncthreads();
@@ -354,7 +617,7 @@ QSB_GLOBAL __launch_bounds__(QsbQGeom<NQ>::WARPS * 32) qsb_k_lm3(QsbSolveArgs a)
           double gm = 0.0;
           const double rn = sqrt(2.0 * F);
           for (int k = threadIdx.x; k < P; k += blockDim.x) {
-            const double akk = QSB_LDCG(&A[(size_t)k * rows + k]);
+            const double akk = QSB_LDCG(&A[QSB_TRI(k, k)]);
             if (akk > 0.0) gm = fmax(gm, fabs(g[k]) / (sqrt(akk) * rn));
           }
           if (threadIdx.x == 0) {  // encoded as huge values: every thread sees the same maximum
@@ -368,13 +631,13 @@ QSB_GLOBAL __launch_bounds__(QsbQGeom<NQ>::WARPS * 32) qsb_k_lm3(QsbSolveArgs a)
           if (gm <= a.gtol) { status = 1; break; }
         }
         bool chol_ok;
-        { QSB_PROF_BEGIN(); chol_ok = qsb_chol_packed(A, rows, d2, mu, P, Ls, rinv, wk, okflag, a.prof); QSB_PROF_END(2); }
+        { QSB_PROF_BEGIN(); chol_ok = qsb_chol3(A, rows, d2, mu, P, Ls, Winv, wk, okflag, a.prof); QSB_PROF_END(2); }
         if (!chol_ok) {
           mu *= nu; nu *= 2.0;
           if (++rejects > 60 || mu > 1e30) { status = 5; break; }
           continue;
         }
-        { QSB_PROF_BEGIN(); qsb_chol_back_packed(Ls, P, wk, h); QSB_PROF_END(3); }
+        { QSB_PROF_BEGIN(); qsb_ch3_back(Ls, P, Winv, zs, h); QSB_PROF_END(3); }
         cplx p1 = cmk(0, 0), p2 = cmk(0, 0);
         for (int k = threadIdx.x; k < P; k += blockDim.x) {
           xn[k] = x[k] + h[k];
@@ -405,14 +668,14 @@ QSB_GLOBAL __launch_bounds__(QsbQGeom<NQ>::WARPS * 32) qsb_k_lm3(QsbSolveArgs a)
           ++iters;
           {
             QSB_PROF_BEGIN();
-            if (kzero) { for (int e = threadIdx.x; e < rows * rows; e += blockDim.x) A[e] = 0.0; __syncthreads(); }
-            qsb_syrk_dmma(Rg, rows, K2, A, warp, NW, lane);
+            if (kzero) { for (int e = threadIdx.x; e < rows * (rows + 1) / 2; e += blockDim.x) A[e] = 0.0; __syncthreads(); }
+            qsb_syrk_packed(Rg, rows, K2, A, warp, NW, lane);
             __syncthreads();
             QSB_PROF_END(1);
           }
           for (int k = threadIdx.x; k < P; k += blockDim.x) {
-            g[k] = QSB_LDCG(&A[(size_t)P * rows + k]);
-            d2[k] = fmax(d2[k], QSB_LDCG(&A[(size_t)k * rows + k]));
+            g[k] = QSB_LDCG(&A[QSB_TRI(P, k)]);
+            d2[k] = fmax(d2[k], QSB_LDCG(&A[QSB_TRI(k, k)]));
           }
           __syncthreads();
           const double q = 2.0 * rho - 1.0;
@@ -449,7 +712,7 @@ static inline size_t qsb_lm3_smem_bytes(int nq, int max_ops, int max_params) {
   const size_t N = (size_t)1 << nq;
   const size_t base = 32 * 16 + (size_t)8 * max_params * 8 + 16 * 8 + 8 + (size_t)64 * (max_ops + max_params) + 16 * 4 + (size_t)24 * max_ops + 16;
   const size_t packed = std::max((size_t)(max_params + 1) * (max_params + 2) / 2, 2 * N * N);
-  return base + (packed + QSB_CH_NB + 2) * 8;
+  return base + (packed + 1 + (size_t)((max_params + QSB_CH_NB - 1) / QSB_CH_NB) * QSB_CH3_WSZ + 32) * 8;
 }
 
 // ---------------------------------------------------------------------------- QSB_RUN_LMSYS, unitary target
@@ -488,13 +751,16 @@ QSB_GLOBAL __launch_bounds__(QsbQGeom<NQ>::WARPS * 32) qsb_k_lmsys3(QsbBatchArgs
     qsb_cta_segments_fwd(prog, NW, seg);
     const double F = qsb_cta_half_norm_body<NQ>(prog, a.params + a.param_off[inst], a.target, trig, gtab, part, nullptr);
     qsb_cta_qrows<NQ>(prog, a.target, gtab, seg, vsm, Rg);
-    if (qsb_syrk_needs_zero(rows, NW)) { for (int e = threadIdx.x; e < rows * rows; e += blockDim.x) A[e] = 0.0; __syncthreads(); }
-    qsb_syrk_dmma(Rg, rows, K2, A, warp, NW, lane);
+    if (qsb_syrk_needs_zero(rows, NW)) { for (int e = threadIdx.x; e < rows * (rows + 1) / 2; e += blockDim.x) A[e] = 0.0; __syncthreads(); }
+    qsb_syrk_packed(Rg, rows, K2, A, warp, NW, lane);
     __syncthreads();
     double* og = a.out_b + (a.param_off[inst] - p_base);
     double* oA = a.out_c + (sq_off[inst] - s_base);
-    for (int k = threadIdx.x; k < P; k += blockDim.x) og[k] = QSB_LDCG(&A[(size_t)P * rows + k]);
-    for (int e = threadIdx.x; e < P * P; e += blockDim.x) oA[e] = QSB_LDCG(&A[(size_t)(e / P) * rows + (e % P)]);
+    for (int k = threadIdx.x; k < P; k += blockDim.x) og[k] = QSB_LDCG(&A[QSB_TRI(P, k)]);
+    for (int e = threadIdx.x; e < P * P; e += blockDim.x) {
+      const int k = e / P, l = e - k * P;
+      oA[e] = QSB_LDCG(&A[k >= l ? QSB_TRI(k, l) : QSB_TRI(l, k)]);
+    }
     if (threadIdx.x == 0) a.out_a[li] = 2.0 * F;
   }
 }

@@ -13,6 +13,11 @@ from .backends import program_for
 
 class Objective:
     has_residuals = True  # False: gen_error_residuals* return None, so default_solver avoids least squares (solvers.py:51-52)
+    # True: gen_eval_func is the Hilbert-Schmidt distance against device_target(options), i.e. exactly the value the
+    # on-device solvers return with xopt, so the search may reuse it (parallelizers.solve_frontier).  A subclass with its
+    # own evaluation function leaves this False and is evaluated through gen_eval_func like in the reference
+    # (compiler.py:147, leap_compiler.py:213).
+    device_distance = False
 
     def gen_eval_func(self, circuit, options):
         return self.gen_error_func(circuit, options)
@@ -29,6 +34,8 @@ class Objective:
 
 
 class MatrixDistanceObjective(Objective):
+    device_distance = True
+
     def gen_error_func(self, circuit, options):
         """f(x) = |1 - |Tr(T^dagger U)|/N|   (comparison.matrix_distance_squared, comparison.py:8-22)."""
         gp, T = program_for(circuit), np.asarray(options.target, dtype="complex128")
@@ -81,6 +88,7 @@ class StateprepObjective(Objective):
     above (the kernels never assume that the matrix in the target slot is unitary).  Like the reference it has no
     residual form (objectives.py:81-101 return None), so the default solver for it is BFGS_Jac_Solver."""
     has_residuals = False
+    device_distance = True
 
     def device_target(self, options):
         a = np.asarray(options.target_state, dtype="complex128").ravel()

@@ -7,6 +7,7 @@ per GPU, no collective: SURVEY.md section 8e), and yields the reference's tuples
 It runs in-process: no fork after CUDA initialisation (hard part 4).
 """
 from . import _lib
+from .solvers import finite_or_inf, rides_on_device
 
 
 SM_PER_DEVICE = 148      # B200
@@ -67,13 +68,17 @@ class GpuParallelizer(Parallelizer):
         steps = [t[0] for t in tuples]
         if hasattr(solver, "solve_batch"):
             res = solver.solve_batch(steps, options)
-            return [(step, (res.matrices[i], res.x[i]), depth, weight, res.distance[i])
+            if rides_on_device(options):
+                values = res.distance
+            else:  # a user objective with its own evaluation function: evaluate it like the reference (compiler.py:147)
+                values = [finite_or_inf(options.objective.gen_eval_func(step, options)(res.x[i])) for i, step in enumerate(steps)]
+            return [(step, (res.matrices[i], res.x[i]), depth, weight, values[i])
                     for i, (step, depth, weight) in enumerate(tuples)]
         # a solver without a batched form: evaluate_step one by one (parallelizers.py:34-36)
         backend, out = options.backend, []
         for step, depth, weight in tuples:
             U, x = solver.solve_for_unitary(backend.prepare_circuit(step, options), options)
-            out.append((step, (U, x), depth, weight, options.objective.gen_eval_func(step, options)(x)))
+            out.append((step, (U, x), depth, weight, finite_or_inf(options.objective.gen_eval_func(step, options)(x))))
         return out
 
     def solve_circuits_parallel(self, tuples):

@@ -12,9 +12,12 @@ Every solver also has ``solve_batch(circuits, options, x0s=None)``: one launch f
 (children x starts), which is what ``GpuParallelizer`` calls.  Start vectors are uniform in [0, 2 pi) unless given
 (solvers.py:155,157).  Solvers are stateless and picklable (constructor arguments only).
 """
+import math
+
 import numpy as np
 
 from . import _lib
+from . import objectives as _objectives
 from .backends import program_for
 
 
@@ -30,6 +33,22 @@ def _target_of(options):
 def _has_residuals(options):
     obj = options.objective if "objective" in options else None
     return getattr(obj, "has_residuals", True)
+
+
+def rides_on_device(options):
+    """True if the distance the device solvers return IS options.objective's evaluation function (see
+    objectives.Objective.device_distance); otherwise callers must evaluate objective.gen_eval_func themselves."""
+    obj = options.objective if "objective" in options else None
+    if obj is None:
+        return True
+    return bool(getattr(obj, "device_distance", False)) and \
+        getattr(type(obj), "gen_eval_func", None) is getattr(_objectives.Objective, "gen_eval_func")
+
+
+def finite_or_inf(v):
+    """NaN (a failed solve) compares false with everything and would corrupt heap order: treat it as +inf."""
+    v = float(v)
+    return v if v == v else float("inf")
 
 
 def _tolerances(options):
@@ -91,7 +110,7 @@ class Solver:
             fi = np.where(np.isnan(f[idx]), np.inf, f[idx])
             b = idx[int(np.argmin(fi))]
             best_x.append(x[offs[b]:offs[b + 1]].copy())
-            best_f.append(float(f[b]))
+            best_f.append(finite_or_inf(f[b]))
             best_it.append(int(iters[b]))
             best_st.append(int(status[b]))
         mats = None
@@ -138,6 +157,11 @@ class BFGS_Jac_Solver(Solver):
         self.max_iters = int(max_iters)
 
     def _solve_opts(self, options):
+        if not rides_on_device(options):
+            # the reference's BFGS minimises objective.gen_error_jac (solvers.py:142); the device kernel minimises the
+            # Hilbert-Schmidt distance against objective.device_target - refuse anything else instead of ignoring it
+            raise ValueError("BFGS_Jac_Solver on the device needs MatrixDistanceObjective or StateprepObjective, got {}".format(
+                type(options.objective).__name__))
         thr = options.threshold if "threshold" in options else 1e-10
         strict = "max_quality_optimization" in options and options.max_quality_optimization
         # scipy BFGS: gtol = options.threshold (solvers.py:142); NLopt: stopval 1e-16 (solvers.rs:64)
@@ -180,12 +204,39 @@ class NaiveMultiStart_Solver(Solver):
         return inner.solve_batch(circuits, options, starts, want_matrices)
 
 
+def aposmm_start_indices(x_on_cube, f, mu=1e-4):
+    """Start points of APOSMM for ONE batch of uniform samples with no local-optimisation history: the case
+    MultiStart_Solver creates (qsearch/multistart_solvers.py:66-88).  Restates, vectorised over the sample,
+    persistent_aposmm.update_history_dist (:299-358: for every point the distance to the nearest other point whose
+    value is not worse), decide_where_to_start_localopt (:421-541: keep points with no such point within r_k and at least
+    `mu` away from the cube's boundary, sorted by value) and calc_rk (:544-556) with the default rk_const of
+    initialize_APOSMM (:568).  Returns sample indices, best first."""
+    x = np.asarray(x_on_cube, dtype="float64")
+    f = np.asarray(f, dtype="float64")
+    n_s, n = x.shape
+    ok = ~np.isnan(f)
+    sq = np.einsum("ij,ij->i", x, x)
+    d = np.sqrt(np.maximum(sq[:, None] + sq[None, :] - 2.0 * (x @ x.T), 0.0))
+    cand = (f[None, :] <= f[:, None]) & ok[None, :] & ok[:, None]  # cand[i, j]: j is not worse than i
+    np.fill_diagonal(cand, False)
+    dist_to_better = np.where(cand, d, np.inf).min(axis=1)
+    if n_s and not np.isinf(dist_to_better).any():
+        # the minimum is not unique, so no point is "best": the first one with the minimal value is (:361-368)
+        dist_to_better[int(np.nonzero(f == np.nanmin(f))[0][0])] = np.inf
+    rk_const = math.exp((math.lgamma(1.0 + n / 2.0) + math.log(5.0)) / n) / math.sqrt(math.pi)
+    r_k = rk_const * (math.log(n_s) / n_s) ** (1.0 / n)
+    to_bounds = np.minimum((1.0 - x).min(axis=1), x.min(axis=1))
+    keep = ok & ~np.isinf(f) & (dist_to_better > r_k) & (to_bounds >= mu)
+    idx = np.nonzero(keep)[0]
+    return idx[np.argsort(f[idx], kind="stable")]
+
+
 class MultiStart_Solver(NaiveMultiStart_Solver):
     """Sample-then-refine multistart (reference: qsearch/multistart_solvers.py:44-110): 100 uniform samples of the
-    error function per circuit (scored in ONE launch), then `num_threads` local solves from the best distinct
-    samples, run as one batch, argmin kept.  The reference picks its start points with APOSMM's r_k rule
-    (persistent_aposmm.py:421-541); here the starts are simply the lowest-valued samples - the APOSMM bookkeeping is
-    host-side control flow outside the hot path."""
+    error function per circuit (ALL circuits of a frontier expansion scored in ONE launch), APOSMM's start selection on
+    every circuit's sample (`aposmm_start_indices`: no better sample within r_k, multistart_solvers.py:85-88), then at
+    most `num_threads` local solves per circuit from the selected points, run as one batch, argmin kept.  If fewer
+    than `num_threads` points qualify, fewer solves are started, like the reference (:88)."""
     n_samples = 100
 
     def solve_batch(self, circuits, options, x0s=None, want_matrices=True):
@@ -194,14 +245,19 @@ class MultiStart_Solver(NaiveMultiStart_Solver):
         T = _target_of(options)
         gps = [program_for(c) for c in circuits]
         rng = np.random.default_rng(options.seed) if "seed" in options and options.seed is not None else np.random.default_rng()
-        samples = [rng.random((self.n_samples, gp.n_params)) * (2 * np.pi) for gp in gps]
+        cubes = [rng.uniform(0.0, 1.0, (self.n_samples, gp.n_params)) for gp in gps]
         poi = np.repeat(np.arange(len(gps), dtype="int32"), self.n_samples)
-        vals = lib.eval_distance(gps, poi, np.concatenate([s.ravel() for s in samples]) if gps else np.zeros(0), T)
+        vals = lib.eval_distance(gps, poi, np.concatenate([(2 * np.pi * s).ravel() for s in cubes]) if gps else np.zeros(0), T)
         vals = vals.reshape(len(gps), self.n_samples)
         starts = []
         for ci in range(len(gps)):
-            order = np.argsort(vals[ci])[: self.num_threads]
-            pts = samples[ci][order]
+            if gps[ci].n_params == 0:
+                starts.append(np.zeros((1, 0)))
+                continue
+            order = aposmm_start_indices(cubes[ci], vals[ci])[: self.num_threads]
+            if len(order) == 0:
+                order = np.argsort(vals[ci])[:1]
+            pts = 2 * np.pi * cubes[ci][order]
             if x0s is not None and x0s[ci] is not None:
                 pts = np.vstack([np.asarray(x0s[ci], dtype="float64")[None, :], pts[:-1]]) if len(pts) > 1 else \
                     np.asarray(x0s[ci], dtype="float64")[None, :]

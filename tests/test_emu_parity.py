@@ -155,3 +155,62 @@ def test_every_leaf_type_through_the_warp_kernels():
     lib = emulated_library()
     for n in (3, 4):
         _parity.check_every_leaf_type(lib, n)
+
+
+def test_program_cache_eviction_keeps_referenced_programs():
+    """the device-program cache must never destroy a program a live Batch (or a call in flight) references.
+    A tiny cache limit forces evictions while a batch is held; the batch must still evaluate correctly afterwards."""
+    from oracle import qs_oracle as O
+    from qsearch_b200 import _lib, lowering, gates, gatesets
+    lib = _lib.Library(emulated_library().path)
+    lib.PROGRAM_CACHE_LIMIT = 8
+    rng = np.random.default_rng(5)
+    g = gatesets.QubitCNOTLinear()
+    base = gates.ProductGate(g.initial_layer(2)).appending(g.search_layers(2)[0][0])
+    gp0 = lowering.lower(base)
+    gp0.key = "held"
+    x = rng.random((2, gp0.n_params)) * 2 * np.pi
+    held = lib.batch([gp0], np.zeros(2, dtype="int32"))
+    held.set_params(x)
+    for i in range(40):  # 40 distinct programs through a cache of 8: evictions happen, `held` stays referenced
+        gpi = lowering.lower(base)
+        gpi.key = "tmp%d" % i
+        lib.eval_matrix([gpi], [0], x[0])
+    assert len(lib._programs) <= 9 and "held" in lib._programs and lib._programs["held"][2] == 1
+    # a single call with more distinct programs than the limit keeps all of ITS programs alive
+    many = []
+    for i in range(12):
+        gpi = lowering.lower(base)
+        gpi.key = "many%d" % i
+        many.append(gpi)
+    U = lib.eval_matrix(many, np.arange(12, dtype="int32"), np.tile(x[0], 12))
+    assert np.abs(U - O.matrix(base, x[0])[None]).max() < 1e-12
+    held.run(_lib.RUN_MATRIX)
+    Uh, _, _ = held.fetch()
+    for k in range(2):
+        assert np.abs(Uh[k] - O.matrix(base, x[k])).max() < 1e-12
+    held.close()
+    assert lib._programs["held"][2] == 0
+
+
+def test_captured_constants_are_keyed_by_their_exact_bytes():
+    """two UGates that differ by 1e-10 (below the 8 digits of NumPy's repr) must not share a device program."""
+    from oracle import qs_oracle as O
+    from qsearch_b200 import backends, gates
+    lib = emulated_library()
+    prev = __import__("qsearch_b200")._lib.use_library(lib)
+    try:
+        rng = np.random.default_rng(9)
+        A = np.linalg.qr(rng.normal(size=(4, 4)) + 1j * rng.normal(size=(4, 4)))[0]
+        B = A.copy()
+        B[1, 2] += 1e-10
+        ca = gates.ProductGate(gates.KroneckerGate(gates.U3Gate(), gates.U3Gate()), gates.UGate(A))
+        cb = gates.ProductGate(gates.KroneckerGate(gates.U3Gate(), gates.U3Gate()), gates.UGate(B))
+        assert repr(ca) == repr(cb)
+        x = rng.random(6) * 2 * np.pi
+        Ua = backends.CudaBackend().prepare_circuit(ca).matrix(x)
+        Ub = backends.CudaBackend().prepare_circuit(cb).matrix(x)
+        assert np.abs(Ua - O.matrix(ca, x)).max() < 1e-12 and np.abs(Ub - O.matrix(cb, x)).max() < 1e-12
+        assert np.abs(Ua - Ub).max() > 1e-11
+    finally:
+        __import__("qsearch_b200")._lib.use_library(prev)

@@ -80,3 +80,14 @@ def test_oracle_against_live_reference():
         f, g = rc.matrix_distance_squared_jac(T, U, J)
         fo, go = O.matrix_distance_squared_jac(T, Uo, Jo)
         assert abs(f - fo) < TOL and np.abs(g - go).max() < TOL
+
+
+def test_aposmm_start_selection_matches_the_reference():
+    """MultiStart_Solver's start points (qsearch/multistart_solvers.py:66-88): `solvers.aposmm_start_indices` against indices
+    produced by the reference's own persistent_aposmm functions (tests/golden/make_golden_aposmm.py): 22 seeded samples,
+    dimensions 1..165, including a tie for the minimum and a point closer to the boundary than mu."""
+    import os
+    from qsearch_b200.solvers import aposmm_start_indices
+    z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "aposmm.npz"))
+    for k in range(int(z["n_cases"])):
+        assert np.array_equal(aposmm_start_indices(z["x_%d" % k], z["f_%d" % k]), z["start_%d" % k]), k
