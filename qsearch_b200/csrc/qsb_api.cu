@@ -277,6 +277,7 @@ extern "C" int qsb_batch_create(qsb_ctx* ctx, int slot, int n_programs, const qs
     dp[p].n_ops = progs[p]->n_ops; dp[p].n_params = progs[p]->n_params;
     b->max_ops = std::max(b->max_ops, progs[p]->n_ops);
     b->max_params = std::max(b->max_params, progs[p]->n_params);
+    b->max_pops = std::max(b->max_pops, qsb_count_param_ops(progs[p]->ops.data(), progs[p]->n_ops));
     b->fast_ok = b->fast_ok && progs[p]->fast_ok;
   }
   b->param_off.resize((size_t)n_instances + 1);

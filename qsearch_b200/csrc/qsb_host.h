@@ -43,6 +43,7 @@ struct qsb_batch {
   int slot = 0;
   int n_qubits = 0, n_instances = 0, n_programs = 0;
   int max_ops = 0, max_params = 0;
+  int max_pops = 0;                 // most ops with parameters in one program (snapshots of the body-frame LM's forward pass)
   bool fast_ok = false;
   bool target_unitary = false;      // set by qsb_batch_set_target: selects the body-frame LM forms (qsb_lm3.cuh)
   bool force_generic = false;       // tests / profiling: run the shared-memory interpreter even where a warp kernel exists
@@ -59,6 +60,18 @@ struct qsb_batch {
   void* solver_scratch = nullptr;
   size_t solver_scratch_bytes = 0;
 };
+
+// number of ops of a program that have parameters (= snapshots of a forward pass); host side
+static inline int qsb_count_param_ops(const qsb_op* ops, int n_ops) {
+  int n = 0;
+  for (int j = 0; j < n_ops; ++j) {
+    switch (ops[j].opcode) {
+      case QSB_OP_RX: case QSB_OP_RY: case QSB_OP_RZ: case QSB_OP_U1: case QSB_OP_U2: case QSB_OP_U3: case QSB_OP_XZXZ: case QSB_OP_ZXZXZ: ++n; break;
+      default: break;
+    }
+  }
+  return n;
+}
 
 void qsb_set_error(const std::string& msg);
 const std::string& qsb_get_error();

@@ -21,6 +21,10 @@
 #pragma once
 #include "qsb_lm2.cuh"
 
+// plain 16-byte load: the slab and the snapshots are written and read by ONE CTA (block-level visibility after a barrier
+// holds for cached loads), so the L1 may keep the rows that several Gram tiles of the SM share
+#define QSB_LD2(p) (*reinterpret_cast<const double2*>(p))
+
 template <int NQ>
 struct QsbQGeom {
   static constexpr int N = 1 << NQ;
@@ -70,6 +74,25 @@ QSB_DEVICE void qsb_fill_gates_body(const QsbDevProgram& P, const double* trig, 
       g[0] = cmk(c[0], c[1]); g[1] = cmk(c[2], c[3]); g[2] = cmk(c[4], c[5]); g[3] = cmk(c[6], c[7]);
     } else if ((code & 3) == 0) {
       qsb_gate2x2(op.opcode, trig + 2 * op.param_off, 0, g);
+    } else if (op.opcode == QSB_OP_U3 || op.opcode == QSB_OP_XZXZ) {
+      // The two leaves of the search gatesets have closed forms (w = sqrt(mu) conj(v), mu = 1 throughout):
+      //   U3 = diag(1, e^{i phi}) Ry(theta) diag(1, e^{i lambda}):  lambda: -i g^dagger dg = P1            v = e1, gamma = 0
+      //        phi: g^dagger P1 g, v = g^dagger e1 (w = row 1 of g), gamma = 0;   theta: -1/2 R^dagger Y R, R = diag(1, e^{i lambda}):
+      //        v = (1, -i e^{-i lambda}) / sqrt 2, gamma = -1/2
+      //   XZXZ = Rz(b) SX Rz(a) SX:  b: -1/2 g^dagger Z g = -1/2 I + g^dagger P1 g, w = row 1 of g, gamma = -1/2;
+      //        a: -1/2 SX^dagger Z SX = -1/2 I + (SX^dagger e1)(..)^dagger, w = row 1 of SX = ((1-i)/2, (1+i)/2), gamma = -1/2
+      const double* tg = trig + 2 * op.param_off;
+      const int which = code & 3;
+      const cplx z = cmk(0, 0);
+      g[3] = z;
+      if (op.opcode == QSB_OP_U3) {
+        if (which == 1) { const double k = 0.70710678118654752440; g[0] = cmk(k, 0); g[1] = cmk(-k * tg[5], k * tg[4]); g[2] = cmk(-0.5, 0); }
+        else if (which == 2) { cplx g0[4]; qsb_gate2x2(op.opcode, tg, 0, g0); g[0] = g0[2]; g[1] = g0[3]; g[2] = z; }
+        else { g[0] = z; g[1] = cmk(1, 0); g[2] = z; }
+      } else {
+        if (which == 1) { g[0] = cmk(0.5, -0.5); g[1] = cmk(0.5, 0.5); g[2] = cmk(-0.5, 0); }
+        else { cplx g0[4]; qsb_gate2x2(op.opcode, tg, 0, g0); g[0] = g0[2]; g[1] = g0[3]; g[2] = cmk(-0.5, 0); }
+      }
     } else {
       cplx g0[4], d[4];
       qsb_gate2x2(op.opcode, trig + 2 * op.param_off, 0, g0);
@@ -112,27 +135,67 @@ QSB_DEVICE void qsb_syrk_packed_t(const double* R, int rows, int K2, double* A, 
 #pragma unroll
       for (int j = 0; j < TW; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
     }
-#pragma unroll 2
-    for (int m0 = 0; m0 < klen; m0 += 16) {
-      double2 av[TW][2], bv[TW][2];
+    if constexpr (TW == 2) {
+      // software pipeline: the 16-column chunk m0 + 16 is in flight (L2 latency) while chunk m0 feeds the tensor cores
+      double2 av[2][TW][2], bv[2][TW][2];
 #pragma unroll
       for (int i = 0; i < TW; ++i) {
-        if (i < ni) { av[i][0] = QSB_LDCG2(pa[i] + m0); av[i][1] = QSB_LDCG2(pa[i] + m0 + 2); }
-        else { av[i][0] = av[i][1] = make_double2(0.0, 0.0); }
-        bv[i][0] = QSB_LDCG2(pb[i] + m0); bv[i][1] = QSB_LDCG2(pb[i] + m0 + 2);
+        if (i < ni) { av[0][i][0] = QSB_LD2(pa[i]); av[0][i][1] = QSB_LD2(pa[i] + 2); }
+        else { av[0][i][0] = av[0][i][1] = make_double2(0.0, 0.0); }
+        bv[0][i][0] = QSB_LD2(pb[i]); bv[0][i][1] = QSB_LD2(pb[i] + 2);
       }
+#pragma unroll 1
+      for (int m0 = 0; m0 < klen; m0 += 32) {
 #pragma unroll
-      for (int s4 = 0; s4 < 4; ++s4)
+        for (int ph = 0; ph < 2; ++ph) {
+          const int mc = m0 + 16 * ph, mn = mc + 16;
+          if (mc < klen) {
+            if (mn < klen) {
 #pragma unroll
-        for (int i = 0; i < TW; ++i) {
-          if (i >= ni) continue;  // warp-uniform
+              for (int i = 0; i < TW; ++i) {
+                if (i < ni) { av[ph ^ 1][i][0] = QSB_LD2(pa[i] + mn); av[ph ^ 1][i][1] = QSB_LD2(pa[i] + mn + 2); }
+                else { av[ph ^ 1][i][0] = av[ph ^ 1][i][1] = make_double2(0.0, 0.0); }
+                bv[ph ^ 1][i][0] = QSB_LD2(pb[i] + mn); bv[ph ^ 1][i][1] = QSB_LD2(pb[i] + mn + 2);
+              }
+            }
 #pragma unroll
-          for (int j = 0; j < TW; ++j) {
-            if (diag && j > i) continue;  // only the lower 8x8 tiles of a diagonal block
-            const double x = (s4 & 1) ? av[i][s4 >> 1].y : av[i][s4 >> 1].x, y = (s4 & 1) ? bv[j][s4 >> 1].y : bv[j][s4 >> 1].x;
-            qsb_dmma884(acc[i][j][0], acc[i][j][1], x, y);
+            for (int s4 = 0; s4 < 4; ++s4)
+#pragma unroll
+              for (int i = 0; i < TW; ++i) {
+                if (i >= ni) continue;  // warp-uniform
+#pragma unroll
+                for (int j = 0; j < TW; ++j) {
+                  if (diag && j > i) continue;  // only the lower 8x8 tiles of a diagonal block
+                  const double x = (s4 & 1) ? av[ph][i][s4 >> 1].y : av[ph][i][s4 >> 1].x, y = (s4 & 1) ? bv[ph][j][s4 >> 1].y : bv[ph][j][s4 >> 1].x;
+                  qsb_dmma884(acc[i][j][0], acc[i][j][1], x, y);
+                }
+              }
           }
         }
+      }
+    } else {  // 32-wide blocks: the second operand buffer would not fit the register file; two chunks per trip instead
+#pragma unroll 2
+      for (int m0 = 0; m0 < klen; m0 += 16) {
+        double2 av[TW][2], bv[TW][2];
+#pragma unroll
+        for (int i = 0; i < TW; ++i) {
+          if (i < ni) { av[i][0] = QSB_LD2(pa[i] + m0); av[i][1] = QSB_LD2(pa[i] + m0 + 2); }
+          else { av[i][0] = av[i][1] = make_double2(0.0, 0.0); }
+          bv[i][0] = QSB_LD2(pb[i] + m0); bv[i][1] = QSB_LD2(pb[i] + m0 + 2);
+        }
+#pragma unroll
+        for (int s4 = 0; s4 < 4; ++s4)
+#pragma unroll
+          for (int i = 0; i < TW; ++i) {
+            if (i >= ni) continue;  // warp-uniform
+#pragma unroll
+            for (int j = 0; j < TW; ++j) {
+              if (diag && j > i) continue;  // only the lower 8x8 tiles of a diagonal block
+              const double x = (s4 & 1) ? av[i][s4 >> 1].y : av[i][s4 >> 1].x, y = (s4 & 1) ? bv[j][s4 >> 1].y : bv[j][s4 >> 1].x;
+              qsb_dmma884(acc[i][j][0], acc[i][j][1], x, y);
+            }
+          }
+      }
     }
 #pragma unroll
     for (int i = 0; i < TW; ++i)
@@ -149,98 +212,151 @@ QSB_DEVICE void qsb_syrk_packed_t(const double* R, int rows, int K2, double* A, 
   }
 }
 
+// 16-wide blocks throughout (the L1 serves the rows that tiles share, so wider blocks buy nothing and cost a third of the
+// register file); the contraction is cut in two when that fills the warps better (two addends per element: deterministic)
+QSB_DEVICE int qsb_syrk_ksplit3(int rows, int nwarps) {
+  const int nb = (rows + 15) / 16, tasks = nb * (nb + 1) / 2;
+  const int r1 = (tasks + nwarps - 1) / nwarps, r2 = (2 * tasks + nwarps - 1) / nwarps;
+  return (r2 + 1 < 2 * r1) ? 2 : 1;  // half-length rounds: r2 / 2 against r1, plus a little for the atomics
+}
 QSB_DEVICE void qsb_syrk_packed(const double* R, int rows, int K2, double* A, int warp, int nwarps, int lane) {
-  const int plan = qsb_syrk_plan(rows, nwarps), ks = plan >> 8;
-  if ((plan & 255) == 4) qsb_syrk_packed_t<4>(R, rows, K2, A, warp, nwarps, lane, ks);
-  else qsb_syrk_packed_t<2>(R, rows, K2, A, warp, nwarps, lane, ks);
+  qsb_syrk_packed_t<2>(R, rows, K2, A, warp, nwarps, lane, qsb_syrk_ksplit3(rows, nwarps));
 }
 
-// ---------------------------------------------------------------------------- factorisation with inverted diagonal blocks
-// Same augmented, packed, right-looking Cholesky as qsb_chol_packed (qsb_lm2.cuh), with three changes that take the
-// serial work off the critical path of an LM iteration:
-//   * the matrix arrives packed (qsb_syrk_packed), so the copy into shared memory is linear and vectorised;
-//   * the warp that factors a 16x16 diagonal block also inverts it (W = L_kk^-1, interleaved with the pivot chain), so
-//     the panel below it is ONE tensor-core product X = A_panel W^T instead of a 136-step substitution per row;
-//   * the inverses are kept ([block][16][16] in shared memory): the back-substitution is one 16x16 matrix-vector
-//     product per block instead of one reduction per row.
+// ---------------------------------------------------------------------------- factorisation
+// Same augmented, packed, right-looking Cholesky as qsb_chol_packed (qsb_lm2.cuh): B = [A + mu diag(d2), g ; g^T, .],
+// rows = P + 1, row P ends up as y with L y = g.  What changed, phase by phase (cycles at P = 62, profiles/r2):
+//   copy      the matrix arrives packed (qsb_syrk_packed): linear, vectorised copy into shared memory;
+//   diagonal  16x16 block by one warp in registers + shuffles (qsb_chp_diag's chain), also written DENSE (17-stride) so
+//             that the panel reads it with broadcast loads and no triangular index arithmetic;
+//   panel     one row per thread, column-oriented substitution (16 dependent steps, not 136);
+//   trailing  16x16 DMMA tiles, 32-bit index arithmetic (the packed index of a 272-row matrix fits easily);
+//   inverse   W_b = L_bb^-1 of every diagonal block, computed by an otherwise idle warp OFF the critical path; the
+//             back-substitution then is one 16x16 matrix-vector product per block instead of one reduction per row.
 #define QSB_CH3_WSZ 256  // doubles per inverted diagonal block
+#define QSB_CH4_DLD 17
+#define QSB_CH4_DSZ (QSB_CH_NB * QSB_CH4_DLD + QSB_CH_NB)  // dense block + 1 / L_jj
+#define QSB_TRI32(i, j) ((((i) * ((i) + 1)) >> 1) + (j))
 
-// diagonal block [kb, kb + nbk): lane = row, the row in registers; leaves L in Ls, W (row-major 16x16, zero above the
-// diagonal, identity in the padding) in Wb, 1 / L_jj in rdiag[kb + j]
-QSB_DEVICE void qsb_ch3_diag(double* Ls, int kb, int nbk, double* Wb, double* rdiag, int* okflag, int lane) {
-  constexpr int NB = QSB_CH_NB;
-  const int i = kb + lane;
-  double d[NB], w[NB];
+// diagonal block [kb, kb + nbk): lane = row, the row in registers.  Leaves L in Ls and, dense, in Dk (identity in the
+// padding of a short block), 1 / L_jj in Dk[NB * DLD + j].
+QSB_DEVICE void qsb_ch4_diag(double* Ls, int kb, int nbk, double* Dk, int* okflag, int lane) {
+  constexpr int NB = QSB_CH_NB, LD = QSB_CH4_DLD;
+  const int base = QSB_TRI32(kb + lane, kb);
+  double d[NB];
 #pragma unroll
-  for (int j = 0; j < NB; ++j) {
-    d[j] = (lane < nbk && j <= lane) ? Ls[QSB_TRI(i, kb + j)] : ((j == lane) ? 1.0 : 0.0);
-    w[j] = (j == lane) ? 1.0 : 0.0;
-  }
+  for (int j = 0; j < NB; ++j) d[j] = (lane < nbk && j <= lane) ? Ls[base + j] : ((j == lane) ? 1.0 : 0.0);
   bool good = true;
 #pragma unroll
   for (int j = 0; j < NB; ++j) {
     const double piv = __shfl_sync(QSB_FULL, d[j], j);
     if (!(piv > 0.0) || !(piv < 1e300)) { good = false; break; }
     const double inv = rsqrt(piv);
-    if (lane == j && j < nbk) rdiag[kb + j] = inv;
+    if (lane == j) Dk[NB * LD + j] = inv;
     d[j] = (lane == j) ? piv * inv : d[j] * inv;
 #pragma unroll
     for (int k = j + 1; k < NB; ++k) d[k] = fma(-d[j], __shfl_sync(QSB_FULL, d[j], k), d[k]);
-    // row j of W is final once scaled by 1 / L_jj; rows below subtract L_ij times it (columns c <= j)
-#pragma unroll
-    for (int c = 0; c <= j; ++c) {
-      if (lane == j) w[c] *= inv;
-      const double wj = __shfl_sync(QSB_FULL, w[c], j);
-      if (lane > j) w[c] = fma(-d[j], wj, w[c]);
-    }
   }
   if (!good && lane == 0) *okflag = 0;
   if (lane < NB) {
 #pragma unroll
     for (int j = 0; j < NB; ++j) {
-      if (lane < nbk && j <= lane) Ls[QSB_TRI(i, kb + j)] = d[j];
-      Wb[lane * NB + j] = (j <= lane) ? w[j] : 0.0;
+      if (lane < nbk && j <= lane) Ls[base + j] = d[j];
+      Dk[lane * LD + j] = (j <= lane) ? d[j] : 0.0;
     }
   }
 }
 
-// panel below the diagonal block: rows R0 .. rows-1, X = A_panel W^T, one 8-row tile per warp and round
-QSB_DEVICE void qsb_ch3_panel(double* Ls, int R0, int kb, int nbk, int nrow, const double* Wb, int warp, int nwarps, int lane) {
+// rows R0 .. R0 + nrow - 1 of the panel below the block: x L_kk^T = a, one row per thread; after x_j is known it is
+// folded into the columns to its right, so the dependent chain is 16 multiply + FMA pairs
+QSB_DEVICE void qsb_ch4_panel(double* Ls, int R0, int kb, int nbk, int nrow, const double* Dk) {
+  constexpr int NB = QSB_CH_NB, LD = QSB_CH4_DLD;
+  for (int ri = threadIdx.x; ri < nrow; ri += blockDim.x) {
+    double* src = Ls + QSB_TRI32(R0 + ri, kb);
+    double x[NB];
+#pragma unroll
+    for (int j = 0; j < NB; ++j) x[j] = (j < nbk) ? src[j] : 0.0;
+#pragma unroll
+    for (int j = 0; j < NB; ++j) {
+      const double xj = x[j] * Dk[NB * LD + j];
+      x[j] = xj;
+#pragma unroll
+      for (int c = j + 1; c < NB; ++c) x[c] = fma(-xj, Dk[c * LD + j], x[c]);
+    }
+#pragma unroll
+    for (int j = 0; j < NB; ++j) if (j < nbk) src[j] = x[j];
+  }
+}
+
+// W = L_kk^-1 (row-major 16x16, zero above the diagonal) from the dense block; one warp, lane = column of W
+QSB_DEVICE void qsb_ch4_inverse(const double* Dk, double* Wb, int lane) {
+  constexpr int NB = QSB_CH_NB, LD = QSB_CH4_DLD;
+  if (lane < NB) {
+    double w[NB];
+#pragma unroll
+    for (int i = 0; i < NB; ++i) w[i] = (i == lane) ? 1.0 : 0.0;
+#pragma unroll
+    for (int j = 0; j < NB; ++j) {
+      const double wj = w[j] * Dk[NB * LD + j];
+      w[j] = wj;
+#pragma unroll
+      for (int i = j + 1; i < NB; ++i) w[i] = fma(-Dk[i * LD + j], wj, w[i]);
+    }
+#pragma unroll
+    for (int i = 0; i < NB; ++i) Wb[i * NB + lane] = w[i];
+  }
+}
+
+// one 16x16 tile (bi, bj) of the trailing update C -= X X^T behind panel [kb, kb + nbk); the trailing matrix starts at R0
+QSB_DEVICE void qsb_ch4_tile(double* Ls, int R0, int kb, int nbk, int nrow, int bi, int bj, int lane) {
   constexpr int NB = QSB_CH_NB;
   const int g = lane >> 2, t = lane & 3;
-  double bw[2][NB / 4];  // B fragments of W^T: B[k][n] = W[n][k]
+  double acc[2][2][2];
+  int pa[2], pb[2], rowb[2];
 #pragma unroll
-  for (int nt = 0; nt < 2; ++nt)
+  for (int i = 0; i < 2; ++i) {
+    const int r = 16 * bi + 8 * i + g;
+    int ra = r, rb = 16 * bj + 8 * i + g;
+    if (ra > nrow - 1) ra = nrow - 1;
+    if (rb > nrow - 1) rb = nrow - 1;
+    pa[i] = QSB_TRI32(R0 + ra, kb) + t;
+    pb[i] = QSB_TRI32(R0 + rb, kb) + t;
+    rowb[i] = QSB_TRI32(R0 + r, R0);
+  }
 #pragma unroll
-    for (int ks = 0; ks < NB / 4; ++ks) bw[nt][ks] = Wb[(8 * nt + g) * NB + 4 * ks + t];
-  const int nmt = (nrow + 7) >> 3;
-  for (int mt = warp; mt < nmt; mt += nwarps) {
-    int r = 8 * mt + g;
-    const bool rv = r < nrow;
-    if (!rv) r = nrow - 1;
-    double* src = Ls + QSB_TRI(R0 + r, kb);
-    double a[NB / 4];
+  for (int i = 0; i < 2; ++i)
 #pragma unroll
-    for (int ks = 0; ks < NB / 4; ++ks) a[ks] = (4 * ks + t < nbk) ? src[4 * ks + t] : 0.0;
-    double c0[2] = {0.0, 0.0}, c1[2] = {0.0, 0.0};
-#pragma unroll
-    for (int ks = 0; ks < NB / 4; ++ks) {
-      qsb_dmma884(c0[0], c0[1], a[ks], bw[0][ks]);
-      qsb_dmma884(c1[0], c1[1], a[ks], bw[1][ks]);
-    }
-    __syncwarp();  // every lane has read its row before anybody overwrites it
-    if (rv) {
+    for (int j = 0; j < 2; ++j)
 #pragma unroll
       for (int e = 0; e < 2; ++e) {
-        if (2 * t + e < nbk) src[2 * t + e] = c0[e];
-        if (8 + 2 * t + e < nbk) src[8 + 2 * t + e] = c1[e];
+        const int r = 16 * bi + 8 * i + g, c = 16 * bj + 8 * j + 2 * t + e;
+        acc[i][j][e] = (r < nrow && c <= r) ? Ls[rowb[i] + c] : 0.0;
       }
-    }
+#pragma unroll
+  for (int ks = 0; ks < NB / 4; ++ks) {
+    const bool in = 4 * ks + t < nbk;
+    const double a0 = in ? -Ls[pa[0] + 4 * ks] : 0.0, a1 = in ? -Ls[pa[1] + 4 * ks] : 0.0;
+    const double b0 = in ? Ls[pb[0] + 4 * ks] : 0.0, b1 = in ? Ls[pb[1] + 4 * ks] : 0.0;
+    qsb_dmma884(acc[0][0][0], acc[0][0][1], a0, b0);
+    qsb_dmma884(acc[0][1][0], acc[0][1][1], a0, b1);
+    qsb_dmma884(acc[1][0][0], acc[1][0][1], a1, b0);
+    qsb_dmma884(acc[1][1][0], acc[1][1][1], a1, b1);
   }
+  __syncwarp();
+#pragma unroll
+  for (int i = 0; i < 2; ++i)
+#pragma unroll
+    for (int j = 0; j < 2; ++j)
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        const int r = 16 * bi + 8 * i + g, c = 16 * bj + 8 * j + 2 * t + e;
+        if (r < nrow && c <= r) Ls[rowb[i] + c] = acc[i][j][e];
+      }
 }
 
-// Apk: packed Gram matrix of [Q ; -C] in global memory (rows = P + 1).  Returns false (uniformly) if a pivot is not positive.
-QSB_DEVICE bool qsb_chol3(const double* Apk, int rows, const double* d2, double mu, int P, double* Ls, double* Winv, double* rdiag,
+// Apk: packed Gram matrix of [Q ; -C] in global memory (rows = P + 1).  Dk: 2 * QSB_CH4_DSZ doubles, Winv:
+// ceil(P / 16) * 256 doubles of shared memory.  Needs >= 3 warps.  Returns false (uniformly) if a pivot is not positive.
+QSB_DEVICE bool qsb_chol4(const double* Apk, int rows, const double* d2, double mu, int P, double* Ls, double* Dk, double* Winv,
                           int* okflag, long long* prof) {
 #define QSB_CH_T(slot) do { if (prof && threadIdx.x == 0) { const long long _n = QSB_CLOCK(); atomicAdd((unsigned long long*)&prof[slot], (unsigned long long)(_n - _tc)); _tc = _n; } } while (0)
   long long _tc = prof ? QSB_CLOCK() : 0ll;
@@ -248,41 +364,43 @@ QSB_DEVICE bool qsb_chol3(const double* Apk, int rows, const double* d2, double 
   const int lane = threadIdx.x & 31, warp = qsb_warp_index(), nwarps = blockDim.x >> 5;
   const int tri = rows * (rows + 1) / 2;
   __syncthreads();
-  for (int e = 2 * threadIdx.x; e + 1 < tri; e += 2 * blockDim.x) {
-    const double2 v = QSB_LDCG2(Apk + e);
-    *reinterpret_cast<double2*>(Ls + e) = v;
-  }
+  for (int e = 2 * threadIdx.x; e + 1 < tri; e += 2 * blockDim.x) *reinterpret_cast<double2*>(Ls + e) = QSB_LDCG2(Apk + e);
   if ((tri & 1) && threadIdx.x == 0) Ls[tri - 1] = QSB_LDCG(Apk + tri - 1);
   if (threadIdx.x == 0) *okflag = 1;
   __syncthreads();
-  for (int k = threadIdx.x; k < P; k += blockDim.x) Ls[QSB_TRI(k, k)] += mu * d2[k];
+  for (int k = threadIdx.x; k < P; k += blockDim.x) Ls[QSB_TRI32(k, k)] += mu * d2[k];
   __syncthreads();
   QSB_CH_T(6);
-  if (warp == 0) qsb_ch3_diag(Ls, 0, (P < NB) ? P : NB, Winv, rdiag, okflag, lane);
+  if (warp == 0) qsb_ch4_diag(Ls, 0, (P < NB) ? P : NB, Dk, okflag, lane);
   __syncthreads();
   QSB_CH_T(7);
   for (int kb = 0; kb < P; kb += NB) {
-    const int nbk = (P - kb < NB) ? P - kb : NB;
+    const int blk = kb / NB, nbk = (P - kb < NB) ? P - kb : NB;
+    double* Dc = Dk + (blk & 1) * QSB_CH4_DSZ;
     if (!*okflag) { __syncthreads(); return false; }
     const int R0 = kb + nbk, nrow = rows - R0;
-    qsb_ch3_panel(Ls, R0, kb, nbk, nrow, Winv + (size_t)(kb / NB) * QSB_CH3_WSZ, warp, nwarps, lane);
+    qsb_ch4_panel(Ls, R0, kb, nbk, nrow, Dc);
     __syncthreads();
     QSB_CH_T(8);
-    if (R0 < P) {  // trailing update, 16x16 DMMA tiles of the lower triangle
+    if (R0 < P) {
       const int nbt = (nrow + 15) >> 4;
-      for (int bi = warp; bi < nbt; bi += nwarps) qsb_chp_tile(Ls, R0, kb, nbk, nrow, bi, 0, lane);  // first block column
+      for (int bi = warp; bi < nbt; bi += nwarps) qsb_ch4_tile(Ls, R0, kb, nbk, nrow, bi, 0, lane);  // first block column
       __syncthreads();
       const int nbk1 = (P - R0 < NB) ? P - R0 : NB;
-      if (warp == 0) qsb_ch3_diag(Ls, R0, nbk1, Winv + (size_t)(R0 / NB) * QSB_CH3_WSZ, rdiag, okflag, lane);  // next diagonal block ...
-      if (warp != 0 || nwarps == 1) {                                                                          // ... under the rest of the update
-        const int nw = (nwarps == 1) ? 1 : nwarps - 1, w = (nwarps == 1) ? 0 : warp - 1;
+      if (warp == 0) qsb_ch4_diag(Ls, R0, nbk1, Dk + ((blk + 1) & 1) * QSB_CH4_DSZ, okflag, lane);  // next diagonal block ...
+      else if (warp == 1) qsb_ch4_inverse(Dc, Winv + (size_t)blk * QSB_CH3_WSZ, lane);               // ... this block's inverse ...
+      else {                                                                                         // ... under the rest of the update
+        const int nw = nwarps - 2, w = warp - 2;
         int bi = 1, bj = 1;
         for (int skip = w; skip > 0; --skip) { if (++bj > bi) { ++bi; bj = 1; } }
         while (bi < nbt) {
-          qsb_chp_tile(Ls, R0, kb, nbk, nrow, bi, bj, lane);
+          qsb_ch4_tile(Ls, R0, kb, nbk, nrow, bi, bj, lane);
           for (int skip = nw; skip > 0; --skip) { if (++bj > bi) { ++bi; bj = 1; } }
         }
       }
+      __syncthreads();
+    } else {
+      if (warp == 1) qsb_ch4_inverse(Dc, Winv + (size_t)blk * QSB_CH3_WSZ, lane);
       __syncthreads();
     }
     QSB_CH_T(9);
@@ -293,15 +411,15 @@ QSB_DEVICE bool qsb_chol3(const double* Apk, int rows, const double* d2, double 
 }
 
 // h = -(L^T)^-1 y, y = row P of the packed factor: one warp, one 16-row block per step.  With W_b = L_bb^-1:
-//   h_b = W_b^T (z_b),   z = -y - sum over later blocks c of L_cb^T h_c  (folded into z as soon as h_c is known)
+//   h_b = W_b^T z_b,   z = -y - sum over later blocks c of L_cb^T h_c  (folded into z as soon as h_c is known)
 // zs: 32 doubles of shared memory.
-QSB_DEVICE void qsb_ch3_back(const double* Ls, int P, const double* Winv, double* zs, double* h) {
+QSB_DEVICE void qsb_ch4_back(const double* Ls, int P, const double* Winv, double* zs, double* h) {
   constexpr int NB = QSB_CH_NB;
   const int lane = threadIdx.x & 31, warp = qsb_warp_index();
   __syncthreads();
   if (warp == 0) {
     constexpr int NR = (QSB_CH_MAXROWS + 31) / 32;
-    const double* y = Ls + QSB_TRI(P, 0);
+    const double* y = Ls + QSB_TRI32(P, 0);
     double z[NR];
 #pragma unroll
     for (int b = 0; b < NR; ++b) {
@@ -317,8 +435,8 @@ QSB_DEVICE void qsb_ch3_back(const double* Ls, int P, const double* Winv, double
       for (int b = 0; b < NR; ++b) if (b == chunk) zb = z[b];
       if (li >= 0 && li < NB) zs[li] = zb;
       __syncwarp();
-      double hb = 0.0;
       if (li >= 0 && li < NB) {
+        double hb = 0.0;
 #pragma unroll
         for (int j = 0; j < NB; ++j) hb = fma(Wb[j * NB + li], zs[j], hb);  // W is zero above its diagonal: j >= li only
         zs[NB + li] = hb;
@@ -330,9 +448,12 @@ QSB_DEVICE void qsb_ch3_back(const double* Ls, int P, const double* Winv, double
 #pragma unroll
       for (int b = 0; b < NR; ++b) {
         const int i = 32 * b + lane;
-        if (i < kb) {
+        if (32 * b < kb) {  // warp-uniform
           double s = z[b];
-          for (int j = 0; j < nbk; ++j) s = fma(-Ls[QSB_TRI(kb + j, i)], zs[NB + j], s);
+          if (i < kb) {
+            int rb = QSB_TRI32(kb, i);
+            for (int j = 0; j < nbk; ++j) { s = fma(-Ls[rb], zs[NB + j], s); rb += kb + j + 1; }
+          }
           z[b] = s;
         }
       }
@@ -406,64 +527,6 @@ QSB_DEVICE void qsb_q_param(const QsbFrag<(1 << NQ) / 4, (1 << NQ) / 8>& X, cons
   }
 }
 
-// One warp: forward sweep X <- g_j X over ops [0, je) starting from T^dagger, writing the packed Q_k of the parameters
-// of ops [jb, je) to slab + k * K2.  The warp that reaches the last op also leaves V = U T^dagger in vout (N x N
-// complex, natural row-major order; shared memory).
-template <int NQ>
-QSB_DEVICE void qsb_warp_qsweep(const QsbDevProgram& P, const double* target, const cplx* gtab, int lane, int jb, int je,
-                                double* slab, cplx* vout) {
-  using G = QsbQGeom<NQ>;
-  constexpr int N = G::N, KS = G::KS, TT = G::TT, K2 = G::K2;
-  const int g = lane >> 2, t = lane & 3;
-  QsbFrag<KS, TT> X;
-  QsbKLayout L;
-  L.pos = L.log = 0x43210u;
-  L.mru = -1; L.mru2 = -1;
-#pragma unroll
-  for (int ks = 0; ks < KS; ++ks)
-#pragma unroll
-    for (int o = 0; o < TT; ++o) {
-      const int k = 4 * ks + t, c = 8 * o + g;
-      const double2 tv = *reinterpret_cast<const double2*>(target + 2 * (c * N + k));
-      X.re[ks][o] = tv.x; X.im[ks][o] = -tv.y;
-    }
-  for (int j = 0; j < je; ++j) {
-    const qsb_op op = P.ops[j];
-    if (op.opcode == QSB_OP_CNOT) {
-      const int kb = qsb_bring_in<NQ, TT, false>(X, X, L, NQ - 1 - op.q1, lane);
-      qsb_cnot_slot<NQ, TT>(X, kb, qsb_nib(L.pos, NQ - 1 - op.q0), lane);
-      continue;
-    }
-    const int kb = qsb_bring_in<NQ, TT, false>(X, X, L, NQ - 1 - op.q0, lane);
-    const int np = qsb_num_params(op.opcode);
-    if (j >= jb && np > 0) {
-      for (int k = 0; k < np; ++k) {
-        const cplx* slot = gtab + 4 * (op.reserved + 1 + k);
-        double* row = slab + (size_t)(op.param_off + k) * K2;
-        switch (kb) {
-          case 1: qsb_q_param<NQ, 1>(X, slot, row, lane); break;
-          case 2: if (NQ >= 4) qsb_q_param<NQ, (NQ >= 4 ? 2 : 1)>(X, slot, row, lane); break;
-          default: if (NQ >= 5) qsb_q_param<NQ, (NQ >= 5 ? 4 : 1)>(X, slot, row, lane); break;
-        }
-      }
-    }
-    cplx m[4];
-    qsb_warp_gate(op, gtab, 0, m);
-    qsb_mix_slot<NQ, TT>(X, kb, m);
-  }
-  if (je == P.n_ops) {
-#pragma unroll
-    for (int ks = 0; ks < KS; ++ks) {
-      const int kp = 4 * ks + t;
-      int kl = 0;
-#pragma unroll
-      for (int b = 0; b < NQ; ++b) kl |= ((kp >> b) & 1) << qsb_nib(L.log, b);
-#pragma unroll
-      for (int o = 0; o < TT; ++o) vout[kl * N + 8 * o + g] = cmk(X.re[ks][o], X.im[ks][o]);
-    }
-  }
-}
-
 // row P of the slab: -C packed like a Q row, C = (V^dagger - V) / (2i); all threads of the CTA
 template <int NQ>
 QSB_DEVICE void qsb_q_crow(const cplx* V, double* row) {
@@ -487,11 +550,93 @@ QSB_DEVICE void qsb_q_crow(const cplx* V, double* row) {
   }
 }
 
-// CTA-wide: (cos, sin) table and body-frame gate table of x, then F = |U T^dagger - I|_F^2 / 2 and Tr(U T^dagger)
+// ---------------------------------------------------------------------------- forward pass, one matrix row per lane
+// X <- g_j X from T^dagger with the N columns of X dealt to the warps of the CTA and lane = row: a one-qubit gate is one
+// __shfl_xor of the partner row and one 2x2 combination per element, a CNOT one shuffle and a select - no bit juggling,
+// a few hundred cycles per op for the whole CTA.  This IS the trial evaluation of an LM step (it ends with V = U T^dagger,
+// |V - I|^2 and Tr V), and on the way it leaves a snapshot of X in front of every op that has parameters
+// (snap + ordinal * 2 N^2 doubles, TRANSPOSED: [col][row] complex, so the stores of a warp are contiguous).  If the step
+// is accepted, the product phase below reads the snapshots: no warp ever recomputes a prefix.
 template <int NQ>
-QSB_DEVICE double qsb_cta_half_norm_body(const QsbDevProgram& P, const double* x, const double* target, double* trig,
-                                         cplx* gtab, double* part, cplx* tr_out) {
-  constexpr int NCB = (1 << NQ) / 8;
+struct QsbRowGeom {
+  static constexpr int N = 1 << NQ;
+  static constexpr int SLOTS = 32 / N;                          // columns that fit side by side in one warp (N <= 32)
+  static constexpr int CW = (N / 8 > SLOTS) ? N / 8 : SLOTS;    // columns per warp: n = 5: 4, n = 4: 2, n = 3: 4
+  static constexpr int EPL = CW / SLOTS;                        // elements per lane
+  static constexpr int AW = N / CW;                             // warps that take part (n = 3: 2 of the 8)
+};
+
+template <int NQ>
+QSB_DEVICE void qsb_warp_forward_rows(const QsbDevProgram& P, const double* target, const cplx* gtab, int warp, int lane,
+                                      double* snap, cplx* vout, double& norm2, cplx& tr) {
+  using R = QsbRowGeom<NQ>;
+  constexpr int N = R::N, EPL = R::EPL;
+  const int r = lane & (N - 1), c0 = R::CW * warp + (lane >> NQ);
+  double xr[EPL], xi[EPL];
+#pragma unroll
+  for (int e = 0; e < EPL; ++e) {  // X = T^dagger
+    const int c = c0 + R::SLOTS * e;
+    const double2 tv = *reinterpret_cast<const double2*>(target + 2 * (c * N + r));
+    xr[e] = tv.x; xi[e] = -tv.y;
+  }
+  int pidx = 0;
+  for (int j = 0; j < P.n_ops; ++j) {
+    const qsb_op op = P.ops[j];
+    if (op.opcode == QSB_OP_CNOT) {
+      const int mask = 1 << (NQ - 1 - op.q1);
+      const bool ctrl = (r >> (NQ - 1 - op.q0)) & 1;
+#pragma unroll
+      for (int e = 0; e < EPL; ++e) {
+        const double pr = __shfl_xor_sync(QSB_FULL, xr[e], mask), pi = __shfl_xor_sync(QSB_FULL, xi[e], mask);
+        if (ctrl) { xr[e] = pr; xi[e] = pi; }
+      }
+      continue;
+    }
+    if (qsb_num_params(op.opcode) > 0) {
+      if (snap) {
+        double* sp = snap + (size_t)pidx * 2 * N * N;
+#pragma unroll
+        for (int e = 0; e < EPL; ++e) *reinterpret_cast<double2*>(sp + 2 * ((c0 + R::SLOTS * e) * N + r)) = make_double2(xr[e], xi[e]);
+      }
+      ++pidx;
+    }
+    const cplx* m = gtab + 4 * op.reserved;
+    const int bit = NQ - 1 - op.q0, mask = 1 << bit;
+    const bool hi = (r >> bit) & 1;
+    const cplx ca = hi ? m[3] : m[0], cb = hi ? m[2] : m[1];
+#pragma unroll
+    for (int e = 0; e < EPL; ++e) {
+      const double ar = xr[e], ai = xi[e];
+      const double pr = __shfl_xor_sync(QSB_FULL, ar, mask), pi = __shfl_xor_sync(QSB_FULL, ai, mask);
+      xr[e] = fma(cb.x, pr, fma(-cb.y, pi, fma(ca.x, ar, -ca.y * ai)));
+      xi[e] = fma(cb.x, pi, fma(cb.y, pr, fma(ca.x, ai, ca.y * ar)));
+    }
+  }
+  double s = 0.0;
+  cplx d = cmk(0, 0);
+#pragma unroll
+  for (int e = 0; e < EPL; ++e) {
+    const int c = c0 + R::SLOTS * e;
+    const bool diag = r == c;
+    const double re = xr[e] - (diag ? 1.0 : 0.0), im = xi[e];
+    s = fma(re, re, s); s = fma(im, im, s);
+    if (diag) { d.x += xr[e]; d.y += xi[e]; }
+    if (vout) vout[r * N + c] = cmk(xr[e], xi[e]);
+  }
+  for (int m = 16; m > 0; m >>= 1) {
+    s += __shfl_xor_sync(QSB_FULL, s, m);
+    d.x += __shfl_xor_sync(QSB_FULL, d.x, m);
+    d.y += __shfl_xor_sync(QSB_FULL, d.y, m);
+  }
+  norm2 = s; tr = d;
+}
+
+// CTA-wide: (cos, sin) table and body-frame gate table of x, the forward pass above, then F = |U T^dagger - I|_F^2 / 2 and
+// Tr(U T^dagger).  snap / vsm may be null (no snapshots / V not wanted).  part: >= 3 * 8 doubles.
+template <int NQ>
+QSB_DEVICE double qsb_cta_eval_rows(const QsbDevProgram& P, const double* x, const double* target, double* trig, cplx* gtab,
+                                    double* part, double* snap, cplx* vsm, cplx* tr_out) {
+  constexpr int AW = QsbRowGeom<NQ>::AW;
   const int lane = threadIdx.x & 31, warp = qsb_warp_index();
   __syncthreads();
   for (int p = threadIdx.x; p < P.n_params; p += blockDim.x) {
@@ -502,48 +647,56 @@ QSB_DEVICE double qsb_cta_half_norm_body(const QsbDevProgram& P, const double* x
   __syncthreads();
   qsb_fill_gates_body(P, trig, gtab, threadIdx.x, blockDim.x);
   __syncthreads();
-  if (warp < NCB) {
+  if (warp < AW) {
     double n2; cplx tr;
-    qsb_warp_forward8<NQ>(P, target, gtab, warp, lane, n2, tr);
+    qsb_warp_forward_rows<NQ>(P, target, gtab, warp, lane, snap, vsm, n2, tr);
     if (lane == 0) { part[3 * warp] = n2; part[3 * warp + 1] = tr.x; part[3 * warp + 2] = tr.y; }
   }
   __syncthreads();
   double F = 0.0;
   cplx tr = cmk(0, 0);
-  for (int w = 0; w < NCB; ++w) { F += part[3 * w]; tr.x += part[3 * w + 1]; tr.y += part[3 * w + 2]; }
+  for (int w = 0; w < AW; ++w) { F += part[3 * w]; tr.x += part[3 * w + 1]; tr.y += part[3 * w + 2]; }
   if (tr_out) *tr_out = tr;
   return 0.5 * F;
 }
 
-// Q rows 0..P-1 and -C in row P of the slab (row-major [(P+1)][K2]); gtab = body-frame table of the current x.
-// vsm: N x N complex of shared memory.  Ends with a block barrier: the slab is complete for every warp.
+// ---------------------------------------------------------------------------- product phase
+// Q rows 0..P-1 and -C in row P of the slab (row-major [(P+1)][K2]) from the snapshots and V of the forward pass at the
+// SAME parameter vector (gtab = its body-frame table).  The ops that have parameters are dealt round-robin to the warps;
+// a warp loads the snapshot in front of its op as a DMMA B fragment with the op's qubit mapped to k-step bit 0 (the rows
+// come from memory, so any row order is free), which leaves ONE code path for every qubit.  Ends with a block barrier.
 template <int NQ>
-QSB_DEVICE void qsb_cta_qrows(const QsbDevProgram& P, const double* target, const cplx* gtab, const int* seg, cplx* vsm, double* slab) {
+QSB_DEVICE void qsb_cta_qrows_snap(const QsbDevProgram& P, const cplx* gtab, const double* snap, const cplx* vsm, double* slab) {
   using G = QsbQGeom<NQ>;
-  const int lane = threadIdx.x & 31, warp = qsb_warp_index();
-  const int jb = seg[warp], je = seg[warp + 1];
-  if (jb < je || je == P.n_ops) qsb_warp_qsweep<NQ>(P, target, gtab, lane, jb, je, slab, vsm);
-  __syncthreads();
-  qsb_q_crow<NQ>(vsm, slab + (size_t)P.n_params * G::K2);
-  __syncthreads();
-}
-
-// segments for the forward-only sweep: warp w pays for the whole prefix [0, seg[w + 1]), so later segments get fewer
-// parameters.  A structured update of X costs about `mix` of a parameter's tensor work (2 TT k-step mixes vs the DMMAs).
-QSB_DEVICE void qsb_cta_segments_fwd(const QsbDevProgram& P, int nseg, int* seg) {
-  if ((int)threadIdx.x <= nseg) {
-    const int s = threadIdx.x;
-    int j = 0;
-    if (s == nseg) j = P.n_ops;
-    else if (s > 0) {
-      const int lo = (int)(((long long)s * P.n_params + nseg - 1) / nseg);
-      for (j = 0; j < P.n_ops; ++j) {
-        const qsb_op op = P.ops[j];
-        if (qsb_num_params(op.opcode) > 0 && op.param_off >= lo) break;
+  constexpr int N = G::N, KS = G::KS, TT = G::TT, K2 = G::K2;
+  const int lane = threadIdx.x & 31, warp = qsb_warp_index(), nwarps = blockDim.x >> 5;
+  const int g = lane >> 2, t = lane & 3;
+  int pidx = 0;
+  for (int j = 0; j < P.n_ops; ++j) {
+    const qsb_op op = P.ops[j];
+    const int np = qsb_num_params(op.opcode);
+    if (np == 0) continue;
+    if (pidx % nwarps == warp) {
+      const double* sp = snap + (size_t)pidx * 2 * N * N;
+      const int b = NQ - 1 - op.q0;  // the gate's bit of the row index; physical bit 2 of k = 4 ks + t takes its place
+      QsbFrag<KS, TT> X;
+#pragma unroll
+      for (int ks = 0; ks < KS; ++ks) {
+        int k = 4 * ks + t;
+        if (b != 2 && (((k >> 2) ^ (k >> b)) & 1)) k ^= 4 | (1 << b);
+#pragma unroll
+        for (int o = 0; o < TT; ++o) {
+          const double2 v = QSB_LD2(sp + 2 * ((8 * o + g) * N + k));
+          X.re[ks][o] = v.x; X.im[ks][o] = v.y;
+        }
       }
+      for (int k = 0; k < np; ++k)
+        qsb_q_param<NQ, 1>(X, gtab + 4 * (op.reserved + 1 + k), slab + (size_t)(op.param_off + k) * K2, lane);
     }
-    seg[s] = j;
+    ++pidx;
   }
+  qsb_q_crow<NQ>(vsm, slab + (size_t)P.n_params * K2);
+  __syncthreads();
 }
 
 template <int NQ>
@@ -561,7 +714,7 @@ QSB_GLOBAL __launch_bounds__(QsbQGeom<NQ>::WARPS * 32) qsb_k_lm3(QsbSolveArgs a)
   double* trig = wk + a.max_params;         // 2 * maxP
   double* part = trig + 2 * a.max_params;   // 16
   cplx* gtab = (cplx*)(part + 16);  // [max_ops + max_params][4]; 16-byte aligned: 8 maxP + 16 doubles precede it
-  int* seg = (int*)(gtab + (size_t)4 * (a.max_ops + a.max_params));  // NW + 1 (<= 12 ints), then [12] = queue slot, [13] = ok flag
+  int* seg = (int*)(gtab + (size_t)4 * (a.max_ops + a.max_params));  // 16 ints: [12] = queue slot, [13] = ok flag
   qsb_op* sops = (qsb_op*)(seg + 16);       // the program's ops, staged once per instance
   double* Ls = (double*)(sops + a.max_ops); // packed Cholesky factor; during the sweep the same bytes hold V
   Ls = (double*)(((uintptr_t)Ls + 15) & ~(uintptr_t)15);
@@ -569,10 +722,12 @@ QSB_GLOBAL __launch_bounds__(QsbQGeom<NQ>::WARPS * 32) qsb_k_lm3(QsbSolveArgs a)
   const size_t tri = (size_t)(a.max_params + 1) * (a.max_params + 2) / 2;
   double* Winv = Ls + (((tri > (size_t)2 * N * N ? tri : (size_t)2 * N * N) + 1) & ~(size_t)1);  // [ceil(maxP / 16)][256]
   double* zs = Winv + (size_t)((a.max_params + QSB_CH_NB - 1) / QSB_CH_NB) * QSB_CH3_WSZ;  // 32
+  double* Dk = zs + 32;                                                                    // 2 * QSB_CH4_DSZ
   int* okflag = seg + 13;
   const int lane = threadIdx.x & 31, warp = qsb_warp_index();
   double* Rg = a.scratch + (size_t)blockIdx.x * a.scratch_per_cta;
-  double* A = Rg + (size_t)(a.max_params + 1) * K2;
+  double* A = Rg + (size_t)(a.max_params + 1) * K2;                               // packed Gram matrix
+  double* snap = A + (((size_t)(a.max_params + 1) * (a.max_params + 2) / 2 + 1) & ~(size_t)1);  // [max_pops][2 N^2]
   for (;;) {
     __syncthreads();
     if (threadIdx.x == 0) seg[12] = atomicAdd(&a.ctl[QSB_CTL_NEXT], 1);
@@ -585,16 +740,15 @@ QSB_GLOBAL __launch_bounds__(QsbQGeom<NQ>::WARPS * 32) qsb_k_lm3(QsbSolveArgs a)
     __syncthreads();
     for (int e = threadIdx.x; e < prog.n_ops * 6; e += blockDim.x) ((int32_t*)sops)[e] = ((const int32_t*)prog.ops)[e];
     prog.ops = sops;  // every sweep of this solve reads the ops from shared memory
-    const bool kzero = qsb_syrk_needs_zero(rows, NW);
+    const bool kzero = qsb_syrk_ksplit3(rows, NW) == 2;
     const double* x0 = a.x0 + a.param_off[inst];
     const int max_iters = a.max_iters > 0 ? a.max_iters : 100 * (P > 0 ? P : 1);
     for (int k = threadIdx.x; k < P; k += blockDim.x) x[k] = x0[k];
-    qsb_cta_segments_fwd(prog, NW, seg);
     int iters = 0, status = 0;
     cplx tr;
-    double F = qsb_cta_half_norm_body<NQ>(prog, x, a.target, trig, gtab, part, &tr);  // also fills trig / gtab for x
+    double F = qsb_cta_eval_rows<NQ>(prog, x, a.target, trig, gtab, part, snap, vsm, &tr);  // tables, snapshots and V of x
     if (P > 0) {
-      { QSB_PROF_BEGIN(); qsb_cta_qrows<NQ>(prog, a.target, gtab, seg, vsm, Rg); QSB_PROF_END(0); }
+      { QSB_PROF_BEGIN(); qsb_cta_qrows_snap<NQ>(prog, gtab, snap, vsm, Rg); QSB_PROF_END(0); }
       iters = 1;
       {
         QSB_PROF_BEGIN();
@@ -631,13 +785,13 @@ QSB_GLOBAL __launch_bounds__(QsbQGeom<NQ>::WARPS * 32) qsb_k_lm3(QsbSolveArgs a)
           if (gm <= a.gtol) { status = 1; break; }
         }
         bool chol_ok;
-        { QSB_PROF_BEGIN(); chol_ok = qsb_chol3(A, rows, d2, mu, P, Ls, Winv, wk, okflag, a.prof); QSB_PROF_END(2); }
+        { QSB_PROF_BEGIN(); chol_ok = qsb_chol4(A, rows, d2, mu, P, Ls, Dk, Winv, okflag, a.prof); QSB_PROF_END(2); }
         if (!chol_ok) {
           mu *= nu; nu *= 2.0;
           if (++rejects > 60 || mu > 1e30) { status = 5; break; }
           continue;
         }
-        { QSB_PROF_BEGIN(); qsb_ch3_back(Ls, P, Winv, zs, h); QSB_PROF_END(3); }
+        { QSB_PROF_BEGIN(); qsb_ch4_back(Ls, P, Winv, zs, h); QSB_PROF_END(3); }
         cplx p1 = cmk(0, 0), p2 = cmk(0, 0);
         for (int k = threadIdx.x; k < P; k += blockDim.x) {
           xn[k] = x[k] + h[k];
@@ -649,7 +803,7 @@ QSB_GLOBAL __launch_bounds__(QsbQGeom<NQ>::WARPS * 32) qsb_k_lm3(QsbSolveArgs a)
         p2 = qsb_block_sum(p2, red);
         const double hnorm = sqrt(p1.x), xnorm = sqrt(p1.y), pred = 0.5 * p2.x;
         double Fn;
-        { QSB_PROF_BEGIN(); Fn = qsb_cta_half_norm_body<NQ>(prog, xn, a.target, trig, gtab, part, &tr); QSB_PROF_END(4); }  // tables now belong to xn
+        { QSB_PROF_BEGIN(); Fn = qsb_cta_eval_rows<NQ>(prog, xn, a.target, trig, gtab, part, snap, vsm, &tr); QSB_PROF_END(4); }  // tables, snapshots, V now belong to xn
         const double dF = F - Fn;
         const double rho = (pred > 0.0) ? dF / pred : -1.0;
         if (rho > 1e-4 && Fn == Fn) {
@@ -664,7 +818,7 @@ QSB_GLOBAL __launch_bounds__(QsbQGeom<NQ>::WARPS * 32) qsb_k_lm3(QsbSolveArgs a)
           if (conv_f) { status = 2; break; }
           if (conv_x) { status = 3; break; }
           if (iters >= max_iters) { status = 0; break; }
-          { QSB_PROF_BEGIN(); qsb_cta_qrows<NQ>(prog, a.target, gtab, seg, vsm, Rg); QSB_PROF_END(0); }
+          { QSB_PROF_BEGIN(); qsb_cta_qrows_snap<NQ>(prog, gtab, snap, vsm, Rg); QSB_PROF_END(0); }
           ++iters;
           {
             QSB_PROF_BEGIN();
@@ -689,7 +843,7 @@ QSB_GLOBAL __launch_bounds__(QsbQGeom<NQ>::WARPS * 32) qsb_k_lm3(QsbSolveArgs a)
       }
     }
     // final distance 1 - |Tr(U T^dagger)| / N at x   (comparison.matrix_distance_squared, comparison.py:8-22)
-    qsb_cta_half_norm_body<NQ>(prog, x, a.target, trig, gtab, part, &tr);
+    qsb_cta_eval_rows<NQ>(prog, x, a.target, trig, gtab, part, nullptr, nullptr, &tr);
     double* ox = a.out_x + a.param_off[inst];
     for (int k = threadIdx.x; k < P; k += blockDim.x) ox[k] = x[k];
     if (a.prof && threadIdx.x == 0) atomicAdd((unsigned long long*)&a.prof[5], (unsigned long long)iters);
@@ -712,7 +866,7 @@ static inline size_t qsb_lm3_smem_bytes(int nq, int max_ops, int max_params) {
   const size_t N = (size_t)1 << nq;
   const size_t base = 32 * 16 + (size_t)8 * max_params * 8 + 16 * 8 + 8 + (size_t)64 * (max_ops + max_params) + 16 * 4 + (size_t)24 * max_ops + 16;
   const size_t packed = std::max((size_t)(max_params + 1) * (max_params + 2) / 2, 2 * N * N);
-  return base + (packed + 1 + (size_t)((max_params + QSB_CH_NB - 1) / QSB_CH_NB) * QSB_CH3_WSZ + 32) * 8;
+  return base + (packed + 1 + (size_t)((max_params + QSB_CH_NB - 1) / QSB_CH_NB) * QSB_CH3_WSZ + 32 + 2 * QSB_CH4_DSZ) * 8;
 }
 
 // ---------------------------------------------------------------------------- QSB_RUN_LMSYS, unitary target
@@ -720,8 +874,8 @@ static inline size_t qsb_lm3_smem_bytes(int nq, int max_ops, int max_params) {
 // and a Gram product over rows of N^2 (not 2 N^2) reals; nothing of size N^2 P leaves the CTA's L2-resident slab.
 // One CTA per instance.  out_a[inst] = r^T r, out_b[param_off ..] = g, out_c[sum P_i^2 ..] = A (row-major P x P).
 template <int NQ>
-QSB_GLOBAL __launch_bounds__(QsbQGeom<NQ>::WARPS * 32) qsb_k_lmsys3(QsbBatchArgs a, double* scratch, size_t scratch_per_cta,
-                                                                    const long long* sq_off) {
+QSB_GLOBAL __launch_bounds__(QsbQGeom<NQ>::WARPS * 32, (NQ <= 4 ? 2 : 1)) qsb_k_lmsys3(QsbBatchArgs a, double* scratch, size_t scratch_per_cta,
+                                                                    const long long* sq_off) {  // scratch per CTA: slab, packed Gram, snapshots
   using G = QsbQGeom<NQ>;
   constexpr int N = G::N, K2 = G::K2, NW = G::WARPS;
   QSB_DYN_SMEM(smem_raw);
@@ -734,6 +888,7 @@ QSB_GLOBAL __launch_bounds__(QsbQGeom<NQ>::WARPS * 32) qsb_k_lmsys3(QsbBatchArgs
   const int lane = threadIdx.x & 31, warp = qsb_warp_index();
   double* Rg = scratch + (size_t)blockIdx.x * scratch_per_cta;
   double* A = Rg + (size_t)(a.max_params + 1) * K2;
+  double* snap = A + (((size_t)(a.max_params + 1) * (a.max_params + 2) / 2 + 1) & ~(size_t)1);
   const long long p_base = a.param_off[a.first], s_base = sq_off[a.first];
   int staged = -1;
   for (int li = blockIdx.x; li < a.count; li += gridDim.x) {
@@ -748,10 +903,9 @@ QSB_GLOBAL __launch_bounds__(QsbQGeom<NQ>::WARPS * 32) qsb_k_lmsys3(QsbBatchArgs
     }
     prog.ops = sops;
     __syncthreads();
-    qsb_cta_segments_fwd(prog, NW, seg);
-    const double F = qsb_cta_half_norm_body<NQ>(prog, a.params + a.param_off[inst], a.target, trig, gtab, part, nullptr);
-    qsb_cta_qrows<NQ>(prog, a.target, gtab, seg, vsm, Rg);
-    if (qsb_syrk_needs_zero(rows, NW)) { for (int e = threadIdx.x; e < rows * (rows + 1) / 2; e += blockDim.x) A[e] = 0.0; __syncthreads(); }
+    const double F = qsb_cta_eval_rows<NQ>(prog, a.params + a.param_off[inst], a.target, trig, gtab, part, snap, vsm, nullptr);
+    qsb_cta_qrows_snap<NQ>(prog, gtab, snap, vsm, Rg);
+    if (qsb_syrk_ksplit3(rows, NW) == 2) { for (int e = threadIdx.x; e < rows * (rows + 1) / 2; e += blockDim.x) A[e] = 0.0; __syncthreads(); }
     qsb_syrk_packed(Rg, rows, K2, A, warp, NW, lane);
     __syncthreads();
     double* og = a.out_b + (a.param_off[inst] - p_base);

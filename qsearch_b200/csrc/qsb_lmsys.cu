@@ -22,7 +22,7 @@ static int qsb_launch_lmsys_nq(qsb_batch* b, const QsbBatchArgs& args, cudaStrea
   const int threads = body ? QsbQGeom<NQ>::WARPS * 32 : QSB_LM_WARPS * 32;
   const int resident = body ? qsb_resident_ctas(qsb_k_lmsys3<NQ>, threads, smem) : qsb_resident_ctas(qsb_k_lmsys<NQ>, threads, smem);
   const int grid = std::max(1, std::min(args.count, sm_count * resident));
-  size_t per_cta = (maxP + 1) * (body ? 1 : 2) * NN + (maxP + 1) * (maxP + 1);
+  size_t per_cta = (maxP + 1) * (body ? 1 : 2) * NN + (maxP + 1) * (maxP + 1) + (body ? 2 + (size_t)b->max_pops * 2 * NN : 0);
   per_cta = (per_cta + 1) & ~(size_t)1;
   const size_t need = (size_t)grid * per_cta * sizeof(double);
   if (need > b->solver_scratch_bytes) {

@@ -38,7 +38,7 @@ static int launch_solver_nq(const SolveJob& job, qsb_batch* b, QsbSolveArgs& arg
   if (body_lm) {
     if constexpr (NQ >= 3) threads = QsbQGeom<NQ>::WARPS * 32;
     smem = qsb_lm3_smem_bytes(NQ, b->max_ops, (int)maxP);
-    per_cta = (maxP + 1) * NN + (maxP + 1) * (maxP + 1);
+    per_cta = (maxP + 1) * NN + (maxP + 1) * (maxP + 2) / 2 + 2 + (size_t)b->max_pops * 2 * NN;  // slab, packed Gram, snapshots
   } else if (tensor_lm) {
     threads = QSB_LM_WARPS * 32;
     args.chol_smem = qsb_lm2_smem_bytes(b->max_ops, (int)maxP, true) <= 224 * 1024;

@@ -125,12 +125,14 @@ def test_edge_cases_constants_empty_and_mixed_batches():
                                         unitaries.qft(16)) == 5
 
 
-def test_lm_system_run_kind():
-    """QSB_RUN_LMSYS (r'r, J_r'r, J_r'J_r per instance, J_r never leaving the device) against the oracle."""
+@pytest.mark.parametrize("n", [3, 4, 5])
+def test_lm_system_run_kind(n):
+    """QSB_RUN_LMSYS (r'r, J_r'r, J_r'J_r per instance, J_r never leaving the device) against the oracle: the body-frame
+    form of qsb_lm3.cuh (unitary target) in all three row-per-lane geometries."""
     from oracle import qs_oracle as O
     from qsearch_b200 import _lib, lowering, workloads
     lib = emulated_library()
-    circuits, params, targets = workloads.microbench_workload(3, 2, 2, depth=3)
+    circuits, params, targets = workloads.microbench_workload(n, 2, 2, depth=3)
     gps = [lowering.lower(c) for c in circuits]
     poi = np.repeat(np.arange(2, dtype="int32"), 2)
     T = targets["haar"]
