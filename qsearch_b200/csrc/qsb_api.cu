@@ -58,12 +58,22 @@ extern "C" int qsb_init(int n_devices, const int* device_ids, qsb_ctx** out_ctx)
   for (int id : ids) {
     QsbDevice d;
     d.id = id;
-    QSB_CUDA(cudaSetDevice(id));
-    QSB_CUDA(cudaDeviceGetAttribute(&d.sm_count, cudaDevAttrMultiProcessorCount, id));
-    QSB_CUDA(cudaStreamCreateWithFlags(&d.stream, cudaStreamNonBlocking));
-    QSB_CUDA(cudaStreamCreateWithFlags(&d.copy_stream, cudaStreamNonBlocking));
-    QSB_CUDA(cudaEventCreate(&d.ev0));
-    QSB_CUDA(cudaEventCreate(&d.ev1));
+    cudaError_t e;
+    if ((e = cudaSetDevice(id)) != cudaSuccess || (e = cudaDeviceGetAttribute(&d.sm_count, cudaDevAttrMultiProcessorCount, id)) != cudaSuccess ||
+        (e = cudaStreamCreateWithFlags(&d.stream, cudaStreamNonBlocking)) != cudaSuccess ||
+        (e = cudaStreamCreateWithFlags(&d.copy_stream, cudaStreamNonBlocking)) != cudaSuccess ||
+        (e = cudaEventCreate(&d.ev0)) != cudaSuccess || (e = cudaEventCreate(&d.ev1)) != cudaSuccess) {
+      const int rc = qsb_cuda_fail(e, "qsb_init (device setup)");
+      const std::string keep = qsb_get_error();
+      if (d.stream) cudaStreamDestroy(d.stream);
+      if (d.copy_stream) cudaStreamDestroy(d.copy_stream);
+      if (d.ev0) cudaEventDestroy(d.ev0);
+      qsb_shutdown(ctx);  // the devices set up before this one
+      qsb_set_error(keep);
+      return rc;
+    }
+    d.solve_mu = new std::mutex();
+    d.pool = new QsbPool();
     ctx->devs.push_back(d);
   }
   *out_ctx = ctx;
@@ -79,6 +89,9 @@ extern "C" int qsb_shutdown(qsb_ctx* ctx) {
     cudaEventDestroy(d.ev1);
     cudaStreamDestroy(d.stream);
     cudaStreamDestroy(d.copy_stream);
+    if (d.solve_scratch.p) cudaFree(d.solve_scratch.p);
+    if (d.pool) { for (auto& fb : d.pool->free_blocks) cudaFree(fb.second); delete d.pool; }
+    delete d.solve_mu;
   }
   delete ctx;
   return QSB_OK;
@@ -187,25 +200,28 @@ extern "C" int qsb_program_create(qsb_ctx* ctx, int n_qubits, int n_ops, const q
     }
   }
   ops = p->ops.data();
+  // on any CUDA failure: release what the devices visited so far hold, and the host object (no leak, no half-built handle)
+  auto fail = [&](cudaError_t e, const char* what) {
+    const int rc = qsb_cuda_fail(e, what);
+    const std::string keep = qsb_get_error();
+    qsb_program_destroy(ctx, p);
+    qsb_set_error(keep);
+    return rc;
+  };
+#define QSB_P(call) do { cudaError_t _e = (call); if (_e != cudaSuccess) return fail(_e, #call); } while (0)
   for (auto& d : ctx->devs) {
-    qsb_op* dops = nullptr;
-    double* dc = nullptr;
-    double* dps = nullptr;
-    int32_t* dsm = nullptr;
-    QSB_CUDA(cudaSetDevice(d.id));
-    QSB_CUDA(cudaMalloc((void**)&dops, sizeof(qsb_op) * std::max(1, n_ops)));
-    QSB_CUDA(cudaMalloc((void**)&dc, sizeof(double) * std::max<size_t>(1, const_len)));
-    if (n_ops) QSB_CUDA(cudaMemcpy(dops, ops, sizeof(qsb_op) * n_ops, cudaMemcpyHostToDevice));
-    if (const_len) QSB_CUDA(cudaMemcpy(dc, const_pool, sizeof(double) * const_len, cudaMemcpyHostToDevice));
-    QSB_CUDA(cudaMalloc((void**)&dps, sizeof(double) * pscale.size()));
-    QSB_CUDA(cudaMemcpy(dps, pscale.data(), sizeof(double) * pscale.size(), cudaMemcpyHostToDevice));
-    p->d_ops.push_back(dops);
-    p->d_consts.push_back(dc);
-    QSB_CUDA(cudaMalloc((void**)&dsm, sizeof(int32_t) * slotmap.size()));
-    QSB_CUDA(cudaMemcpy(dsm, slotmap.data(), sizeof(int32_t) * slotmap.size(), cudaMemcpyHostToDevice));
-    p->d_pscale.push_back(dps);
-    p->d_slotmap.push_back(dsm);
+    QSB_P(cudaSetDevice(d.id));
+    p->d_ops.push_back(nullptr); p->d_consts.push_back(nullptr); p->d_pscale.push_back(nullptr); p->d_slotmap.push_back(nullptr);
+    QSB_P(cudaMalloc((void**)&p->d_ops.back(), sizeof(qsb_op) * std::max(1, n_ops)));
+    QSB_P(cudaMalloc((void**)&p->d_consts.back(), sizeof(double) * std::max<size_t>(1, const_len)));
+    QSB_P(cudaMalloc((void**)&p->d_pscale.back(), sizeof(double) * pscale.size()));
+    QSB_P(cudaMalloc((void**)&p->d_slotmap.back(), sizeof(int32_t) * slotmap.size()));
+    if (n_ops) QSB_P(cudaMemcpy(p->d_ops.back(), ops, sizeof(qsb_op) * n_ops, cudaMemcpyHostToDevice));
+    if (const_len) QSB_P(cudaMemcpy(p->d_consts.back(), const_pool, sizeof(double) * const_len, cudaMemcpyHostToDevice));
+    QSB_P(cudaMemcpy(p->d_pscale.back(), pscale.data(), sizeof(double) * pscale.size(), cudaMemcpyHostToDevice));
+    QSB_P(cudaMemcpy(p->d_slotmap.back(), slotmap.data(), sizeof(int32_t) * slotmap.size(), cudaMemcpyHostToDevice));
   }
+#undef QSB_P
   *out_prog = p;
   return QSB_OK;
 }
@@ -243,6 +259,61 @@ bool qsb_target_is_unitary(const double* T, int nq) {
 }
 
 // ---------------------------------------------------------------------------- device-resident batches
+static size_t pool_round(size_t bytes) {
+  if (bytes < 256) return 256;
+  if (bytes <= ((size_t)1 << 20)) return (bytes + 255) & ~(size_t)255;
+  return (bytes + (((size_t)1 << 21) - 1)) & ~(((size_t)1 << 21) - 1);  // 2 MiB granules above 1 MiB
+}
+static const size_t QSB_POOL_LIMIT = (size_t)8 << 30;  // cached (idle) bytes per device
+
+int qsb_pool_alloc(const QsbDevice& d, void** out, size_t bytes) {
+  const size_t want = pool_round(bytes);
+  {
+    std::lock_guard<std::mutex> g(d.pool->mu);
+    auto& fb = d.pool->free_blocks;
+    for (size_t i = 0; i < fb.size(); ++i)
+      if (fb[i].first == want) {
+        *out = fb[i].second;
+        d.pool->cached_bytes -= want;
+        fb[i] = fb.back(); fb.pop_back();
+        return QSB_OK;
+      }
+  }
+  cudaError_t e = cudaMalloc(out, want);
+  if (e != cudaSuccess) {  // give the cache back and retry once
+    cudaGetLastError();
+    {
+      std::lock_guard<std::mutex> g(d.pool->mu);
+      for (auto& b : d.pool->free_blocks) cudaFree(b.second);
+      d.pool->free_blocks.clear(); d.pool->cached_bytes = 0;
+    }
+    e = cudaMalloc(out, want);
+  }
+  if (e != cudaSuccess) {
+    *out = nullptr;
+    return qsb_fail(QSB_ERR_NOMEM, std::string("device allocation of ") + std::to_string(want) + " bytes failed: " + cudaGetErrorString(e));
+  }
+  return QSB_OK;
+}
+
+void qsb_pool_free(const QsbDevice& d, void* p, size_t bytes) {
+  if (!p) return;
+  const size_t have = pool_round(bytes);
+  std::lock_guard<std::mutex> g(d.pool->mu);
+  if (d.pool->cached_bytes + have > QSB_POOL_LIMIT) { cudaFree(p); return; }
+  d.pool->free_blocks.emplace_back(have, p);
+  d.pool->cached_bytes += have;
+}
+
+int qsb_pool_reserve(const QsbDevice& d, QsbBuf& b, size_t bytes) {
+  if (bytes <= b.bytes) return QSB_OK;
+  if (b.p) { qsb_pool_free(d, b.p, b.bytes); b.p = nullptr; b.bytes = 0; }
+  int rc = qsb_pool_alloc(d, &b.p, bytes);
+  if (rc) return rc;
+  b.bytes = bytes;
+  return QSB_OK;
+}
+
 int qsb_buf_reserve(QsbBuf& b, size_t bytes) {
   if (bytes <= b.bytes) return QSB_OK;
   if (b.p) { cudaFree(b.p); b.p = nullptr; b.bytes = 0; }
@@ -295,11 +366,15 @@ extern "C" int qsb_batch_create(qsb_ctx* ctx, int slot, int n_programs, const qs
   auto fail = [&](int code) { qsb_batch_destroy(b); return code; };
   if (cudaSetDevice(d.id) != cudaSuccess) return fail(qsb_fail(QSB_ERR_CUDA, "cudaSetDevice failed"));
 #define QSB_B(call) do { cudaError_t _e = (call); if (_e != cudaSuccess) { rc = qsb_cuda_fail(_e, #call); return fail(rc); } } while (0)
-  QSB_B(cudaMalloc((void**)&b->d_progs, sizeof(QsbDevProgram) * n_programs));
-  QSB_B(cudaMalloc((void**)&b->d_prog_idx, sizeof(int32_t) * std::max(1, n_instances)));
-  QSB_B(cudaMalloc((void**)&b->d_param_off, sizeof(long long) * ((size_t)n_instances + 1)));
-  QSB_B(cudaMalloc((void**)&b->d_params, sizeof(double) * std::max<long long>(1, off)));
-  QSB_B(cudaMalloc((void**)&b->d_target, sizeof(double) * 2 * ((size_t)1 << (2 * b->n_qubits))));
+  b->sz_progs = sizeof(QsbDevProgram) * n_programs;
+  b->sz_prog_idx = sizeof(int32_t) * std::max(1, n_instances);
+  b->sz_param_off = sizeof(long long) * ((size_t)n_instances + 1);
+  b->sz_params = sizeof(double) * std::max<long long>(1, off);
+  b->sz_target = sizeof(double) * 2 * ((size_t)1 << (2 * b->n_qubits));
+  if ((rc = qsb_pool_alloc(d, (void**)&b->d_progs, b->sz_progs)) || (rc = qsb_pool_alloc(d, (void**)&b->d_prog_idx, b->sz_prog_idx)) ||
+      (rc = qsb_pool_alloc(d, (void**)&b->d_param_off, b->sz_param_off)) || (rc = qsb_pool_alloc(d, (void**)&b->d_params, b->sz_params)) ||
+      (rc = qsb_pool_alloc(d, (void**)&b->d_target, b->sz_target)))
+    return fail(rc);
   QSB_B(cudaMemcpy(b->d_progs, dp.data(), sizeof(QsbDevProgram) * n_programs, cudaMemcpyHostToDevice));
   if (n_instances) QSB_B(cudaMemcpy(b->d_prog_idx, prog_of_instance, sizeof(int32_t) * n_instances, cudaMemcpyHostToDevice));
   QSB_B(cudaMemcpy(b->d_param_off, b->param_off.data(), sizeof(long long) * ((size_t)n_instances + 1), cudaMemcpyHostToDevice));
@@ -312,8 +387,12 @@ extern "C" int qsb_batch_destroy(qsb_batch* b) {
   if (!b) return QSB_OK;
   cudaSetDevice(b->ctx->devs[b->slot].id);
   cudaStreamSynchronize(b->ctx->devs[b->slot].stream);
-  cudaFree(b->d_progs); cudaFree(b->d_prog_idx); cudaFree(b->d_param_off); cudaFree(b->d_sq_off); cudaFree(b->d_params); cudaFree(b->d_target);
-  cudaFree(b->out_a.p); cudaFree(b->out_b.p); cudaFree(b->out_c.p); cudaFree(b->solver_scratch);
+  const QsbDevice& d = b->ctx->devs[b->slot];  // the stream is idle: the blocks can be handed to the next batch
+  qsb_pool_free(d, b->d_progs, b->sz_progs); qsb_pool_free(d, b->d_prog_idx, b->sz_prog_idx); qsb_pool_free(d, b->d_param_off, b->sz_param_off);
+  qsb_pool_free(d, b->d_params, b->sz_params); qsb_pool_free(d, b->d_target, b->sz_target);
+  qsb_pool_free(d, b->out_a.p, b->out_a.bytes); qsb_pool_free(d, b->out_b.p, b->out_b.bytes); qsb_pool_free(d, b->out_c.p, b->out_c.bytes);
+  cudaFree(b->d_sq_off); cudaFree(b->solver_scratch);
+  if (b->ev0) { cudaEventDestroy(b->ev0); cudaEventDestroy(b->ev1); }
   delete b;
   return QSB_OK;
 }
@@ -383,17 +462,20 @@ extern "C" int qsb_batch_run(qsb_batch* b, int what, int first, int count, float
   size_t a, bb, c;
   out_sizes(b, what, first, count, &a, &bb, &c);
   int rc;
-  if ((rc = qsb_buf_reserve(b->out_a, a * sizeof(double)))) return rc;
-  if ((rc = qsb_buf_reserve(b->out_b, bb * sizeof(double)))) return rc;
-  if ((rc = qsb_buf_reserve(b->out_c, c * sizeof(double)))) return rc;
+  if ((rc = qsb_pool_reserve(d, b->out_a, a * sizeof(double)))) return rc;
+  if ((rc = qsb_pool_reserve(d, b->out_b, bb * sizeof(double)))) return rc;
+  if ((rc = qsb_pool_reserve(d, b->out_c, c * sizeof(double)))) return rc;
   b->last_first = first; b->last_count = count; b->last_what = what;
   if (count == 0) { if (elapsed_ms) *elapsed_ms = 0.f; return QSB_OK; }
-  if (elapsed_ms) QSB_CUDA(cudaEventRecord(d.ev0, d.stream));
+  if (elapsed_ms) {
+    if (!b->ev0) { QSB_CUDA(cudaEventCreate(&b->ev0)); QSB_CUDA(cudaEventCreate(&b->ev1)); }
+    QSB_CUDA(cudaEventRecord(b->ev0, d.stream));
+  }
   if ((rc = qsb_batch_enqueue(b, what, first, count))) return rc;
   if (elapsed_ms) {
-    QSB_CUDA(cudaEventRecord(d.ev1, d.stream));
-    QSB_CUDA(cudaEventSynchronize(d.ev1));
-    QSB_CUDA(cudaEventElapsedTime(elapsed_ms, d.ev0, d.ev1));
+    QSB_CUDA(cudaEventRecord(b->ev1, d.stream));
+    QSB_CUDA(cudaEventSynchronize(b->ev1));
+    QSB_CUDA(cudaEventElapsedTime(elapsed_ms, b->ev0, b->ev1));
     QSB_CUDA(cudaGetLastError());
   }
   return QSB_OK;

@@ -3,9 +3,24 @@
 #include <cstdint>
 #include <mutex>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "qsb_device.cuh"
+
+struct QsbBuf {
+  void* p = nullptr;
+  size_t bytes = 0;
+};
+
+// Per-device cache of freed device blocks: the host-buffer calls and the solvers build a short-lived batch per call, and a
+// cudaMalloc / cudaFree pair per buffer per call (cudaFree synchronises the device) showed up as 0.1-0.8x first calls and
+// run-to-run spread.  Blocks are reused for requests of the same rounded size.
+struct QsbPool {
+  std::mutex mu;
+  std::vector<std::pair<size_t, void*>> free_blocks;
+  size_t cached_bytes = 0;
+};
 
 struct QsbDevice {
   int id = 0;
@@ -13,6 +28,11 @@ struct QsbDevice {
   cudaStream_t stream = nullptr;       // compute
   cudaStream_t copy_stream = nullptr;  // device->host copies of the host-buffer calls (overlap with the next chunk)
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  // solver scratch (slabs, Gram matrices, snapshots: up to a few hundred MB) kept across qsb_solve_* calls instead of a
+  // cudaMalloc / cudaFree pair per frontier expansion; solve_mu serialises the solves of one device
+  QsbBuf solve_scratch;
+  std::mutex* solve_mu = nullptr;
+  QsbPool* pool = nullptr;
 };
 
 struct qsb_ctx {
@@ -33,11 +53,6 @@ struct qsb_program {
   std::vector<int32_t*> d_slotmap;
 };
 
-struct QsbBuf {
-  void* p = nullptr;
-  size_t bytes = 0;
-};
-
 struct qsb_batch {
   qsb_ctx* ctx = nullptr;
   int slot = 0;
@@ -55,10 +70,12 @@ struct qsb_batch {
   long long* d_sq_off = nullptr;     // prefix sums of P_i^2 (QSB_RUN_LMSYS output offsets), built on first use
   double* d_params = nullptr;
   double* d_target = nullptr;
+  size_t sz_progs = 0, sz_prog_idx = 0, sz_param_off = 0, sz_params = 0, sz_target = 0;  // bytes requested from the pool
   QsbBuf out_a, out_b, out_c;  // grown on demand
   int last_first = 0, last_count = 0, last_what = 0;
   void* solver_scratch = nullptr;
   size_t solver_scratch_bytes = 0;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;  // timed runs: own pair, so two threads timing batches of one device do not race
 };
 
 // number of ops of a program that have parameters (= snapshots of a forward pass); host side
@@ -75,7 +92,10 @@ static inline int qsb_count_param_ops(const qsb_op* ops, int n_ops) {
 
 void qsb_set_error(const std::string& msg);
 const std::string& qsb_get_error();
-int qsb_buf_reserve(QsbBuf& b, size_t bytes);
+int qsb_buf_reserve(QsbBuf& b, size_t bytes);  // cudaMalloc-backed, for long-lived buffers
+int qsb_pool_alloc(const QsbDevice& d, void** out, size_t bytes);   // the device of d must be current
+void qsb_pool_free(const QsbDevice& d, void* p, size_t bytes);
+int qsb_pool_reserve(const QsbDevice& d, QsbBuf& b, size_t bytes);  // grow-only buffer on the pool
 bool qsb_target_is_unitary(const double* T, int n_qubits);
 int qsb_fail(int code, const std::string& msg);
 int qsb_cuda_fail(cudaError_t e, const char* what);

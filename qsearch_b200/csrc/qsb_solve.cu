@@ -98,9 +98,10 @@ static int launch_solver_nq(const SolveJob& job, qsb_batch* b, QsbSolveArgs& arg
   per_cta = (per_cta + 1) & ~(size_t)1;  // 16-byte alignment of every CTA's slab (vector stores of the Jacobian rows)
   int grid = std::max(1, std::min(args.count, d.sm_count * ctas));
   if (tensor_lm && !body_lm) grid = std::max(1, std::min(args.count, d.sm_count * ctas / args.cluster)) * args.cluster;
-  rc = qsb_buf_reserve(b->out_c, (size_t)(grid / args.cluster) * per_cta * sizeof(double));  // solver scratch (per cluster / CTA)
+  QsbBuf& scratch = job.ctx->devs[b->slot].solve_scratch;  // kept across calls (solve_shard holds the device's solve_mu)
+  rc = qsb_buf_reserve(scratch, (size_t)(grid / args.cluster) * per_cta * sizeof(double));  // per cluster / CTA
   if (rc) return rc;
-  args.scratch = (double*)b->out_c.p;
+  args.scratch = (double*)scratch.p;
   args.scratch_per_cta = per_cta;
   if (body_lm) {
     if constexpr (NQ >= 3) QSB_LAUNCH((qsb_k_lm3<NQ>), grid, threads, smem, d.stream, args);
@@ -154,9 +155,10 @@ static int launch_solver_nq(const SolveJob& job, qsb_batch* b, QsbSolveArgs& arg
     ctas = std::max(1, std::min(std::min(by_threads, by_smem), 16));
   }
   const int grid = std::max(1, std::min(args.count, d.sm_count * ctas));
-  rc = qsb_buf_reserve(b->out_c, (size_t)grid * 2 * sizeof(double));
+  QsbBuf& scratch = job.ctx->devs[b->slot].solve_scratch;
+  rc = qsb_buf_reserve(scratch, (size_t)grid * 2 * sizeof(double));
   if (rc) return rc;
-  args.scratch = (double*)b->out_c.p;
+  args.scratch = (double*)scratch.p;
   args.scratch_per_cta = 2;
   if (warp_lbfgs) {
     if constexpr (NQ >= 3) QSB_LAUNCH((qsb_k_lbfgs2<NQ>), grid, threads, smem, d.stream, args);
@@ -176,6 +178,7 @@ int qsb_launch_solver_lm5(const SolveJob& job, qsb_batch* b, QsbSolveArgs& args,
 #else
 static int solve_shard(const SolveJob& job, int slot, int i0, int i1, const std::vector<long long>& poff) {
   if (i1 <= i0) return QSB_OK;
+  std::lock_guard<std::mutex> device_lock(*job.ctx->devs[slot].solve_mu);
   qsb_batch* b = nullptr;
   int rc = qsb_batch_create(job.ctx, slot, job.n_programs, job.progs, i1 - i0, job.prog_of_instance + i0, &b);
   if (rc) return rc;
@@ -185,9 +188,9 @@ static int solve_shard(const SolveJob& job, int slot, int i0, int i1, const std:
   if ((rc = qsb_batch_set_params(b, job.x0 + poff[i0], np))) return done(rc);
   if ((rc = qsb_batch_set_target(b, job.target))) return done(rc);
   // outputs: out_a = x [np] then f [n]; out_b = iters [n] + status [n] as int32
-  if ((rc = qsb_buf_reserve(b->out_a, (np + n + 1) * sizeof(double)))) return done(rc);
+  if ((rc = qsb_pool_reserve(job.ctx->devs[slot], b->out_a, (np + n + 1) * sizeof(double)))) return done(rc);
   const size_t n_ctl = (size_t)QSB_CTL_SOLVED + job.n_programs;
-  if ((rc = qsb_buf_reserve(b->out_b, ((size_t)(2 * n + 2) + n_ctl) * sizeof(int32_t)))) return done(rc);
+  if ((rc = qsb_pool_reserve(job.ctx->devs[slot], b->out_b, ((size_t)(2 * n + 2) + n_ctl) * sizeof(int32_t)))) return done(rc);
   const QsbDevice& d = job.ctx->devs[slot];
   QsbSolveArgs args;
   args.progs = b->d_progs; args.prog_idx = b->d_prog_idx; args.param_off = b->d_param_off; args.x0 = b->d_params;
@@ -265,11 +268,24 @@ static int solve_dispatch(SolveJob job) {
   job.target_unitary = job.method == QSB_SOLVE_LM && qsb_target_is_unitary(job.target, job.progs[0]->n_qubits);
   const int used = std::min((int)job.ctx->devs.size(), job.n_instances);
   if (used == 1) return solve_shard(job, 0, 0, job.n_instances, poff);
+  // Contiguous shards of equal COST, not equal count: an LM iteration is dominated by the Gram
+  // product, (P + 1)^2 N^2 / 2, so an instance weighs (P + 1)^2 (all instances of a batch share N).  LEAP children have
+  // equal P; the beams of SearchCompiler and the multistart axis mix depths.
+  std::vector<double> cum((size_t)job.n_instances + 1, 0.0);
+  for (int i = 0; i < job.n_instances; ++i) { const double p1 = (double)(poff[i + 1] - poff[i]) + 1.0; cum[i + 1] = cum[i] + p1 * p1; }
+  std::vector<int> cut((size_t)used + 1, 0);
+  cut[used] = job.n_instances;
+  for (int s = 1; s < used; ++s) {
+    const double want = cum[job.n_instances] * s / used;
+    int i = (int)(std::lower_bound(cum.begin(), cum.end(), want) - cum.begin());
+    if (i > 0 && want - cum[i - 1] < cum[i] - want) --i;  // nearer boundary
+    cut[s] = std::min(std::max(i, cut[s - 1] + 1), job.n_instances - (used - s));  // every shard keeps at least one instance
+  }
   std::vector<int> rcs(used, QSB_OK);
   std::vector<std::string> errs(used);
   std::vector<std::thread> th;
   for (int s = 0; s < used; ++s) {
-    int i0 = (int)((long long)job.n_instances * s / used), i1 = (int)((long long)job.n_instances * (s + 1) / used);
+    const int i0 = cut[s], i1 = cut[s + 1];
     th.emplace_back([&, s, i0, i1] { rcs[s] = solve_shard(job, s, i0, i1, poff); if (rcs[s]) errs[s] = qsb_get_error(); });
   }
   for (auto& t : th) t.join();

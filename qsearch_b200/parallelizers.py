@@ -11,33 +11,46 @@ from .solvers import finite_or_inf, rides_on_device
 
 
 SM_PER_DEVICE = 148      # B200
-SMS_PER_INSTANCE = 4     # leave a few SMs per (child, start) instance for the solver's thread-block clusters
-MAX_BEAMS = 8
+MAX_BEAMS = 8            # nodes popped per expansion at most; beyond that the search order drifts from best-first
+MAX_STARTS = 8           # start vectors per child at most (the frontier's wall time is its slowest instance)
+
+
+def _num_devices():
+    try:
+        return _lib.get_library().num_devices
+    except Exception:
+        return 1
+
+
+def _branching(opts):
+    import math
+    try:
+        return max(1, opts.gateset.branching_factor(int(round(math.log2(opts.target.shape[0])))))
+    except Exception:
+        return 1
 
 
 def default_num_tasks(opts):
     """The reference sets num_tasks = number of worker processes and derives beams = num_tasks // branching_factor
     (parallelizers.py:74, compiler.py:89-93), i.e. it pops as many nodes per expansion as its workers can solve
-    concurrently.  The GPU equivalent of "workers" is SMs: one expansion should fill the visible GPUs with
-    beams x branching x starts instances at a few SMs each (measured on QFT5/Yorktown: 6 beams x 6 children finish
-    in 157 s where 1 beam x 4 starts does not finish in 400 s, profiles/r1/k_qft5_qft4_beams_vs_starts.log)."""
-    import math
-    try:
-        ndev = _lib.get_library().num_devices
-    except Exception:
-        ndev = 1
-    bf = 1
-    try:
-        bf = max(1, opts.gateset.branching_factor(int(round(math.log2(opts.target.shape[0])))))
-    except Exception:
-        pass
-    starts = 1
-    try:
-        starts = max(1, int(getattr(opts.solver, "starts", None) or getattr(opts.solver, "num_threads", 1)))
-    except Exception:
-        pass
-    beams = (ndev * SM_PER_DEVICE) // (SMS_PER_INSTANCE * bf * starts)
+    concurrently.  The GPU equivalent of a worker is an SM: the batched LM solver runs one (child, start) instance per
+    SM, so one expansion should put beams x branching x starts instances on the SMs of all visible GPUs.  Beams are
+    capped at MAX_BEAMS; what is left goes to start vectors (`frontier_starts`)."""
+    bf = _branching(opts)
+    beams = (_num_devices() * SM_PER_DEVICE) // bf
     return bf * max(1, min(MAX_BEAMS, beams))
+
+
+def frontier_starts(opts, n_children):
+    """Start vectors per child of one expansion: whatever the solver asks for explicitly (LeastSquares_Jac_Solver(starts=k),
+    k > 1, or options.frontier_starts), else as many as fill the SMs of all visible GPUs once, at most MAX_STARTS."""
+    if "frontier_starts" in opts and opts.frontier_starts:
+        return max(1, int(opts.frontier_starts))
+    own = getattr(opts.solver, "starts", None)
+    if own is None or own > 1:
+        return None  # the solver decides (multistart solvers, explicit starts)
+    slots = _num_devices() * SM_PER_DEVICE
+    return max(1, min(MAX_STARTS, slots // max(1, n_children)))
 
 
 class Parallelizer:
@@ -67,7 +80,7 @@ class GpuParallelizer(Parallelizer):
         solver = options.solver
         steps = [t[0] for t in tuples]
         if hasattr(solver, "solve_batch"):
-            res = solver.solve_batch(steps, options)
+            res = solver.solve_batch(steps, options, starts=frontier_starts(options, len(steps)), frontier=True)
             if rides_on_device(options):
                 values = res.distance
             else:  # a user objective with its own evaluation function: evaluate it like the reference (compiler.py:147)

@@ -60,10 +60,11 @@ def _tolerances(options):
 
 class BatchResult:
     """Best start per circuit of one batched solve."""
-    __slots__ = ("x", "distance", "iterations", "status", "matrices")
+    __slots__ = ("x", "distance", "iterations", "status", "matrices", "all_iterations", "all_status")
 
-    def __init__(self, x, distance, iterations, status, matrices):
+    def __init__(self, x, distance, iterations, status, matrices, all_iterations=None, all_status=None):
         self.x, self.distance, self.iterations, self.status, self.matrices = x, distance, iterations, status, matrices
+        self.all_iterations, self.all_status = all_iterations, all_status  # every (circuit, start) instance of the launch
 
 
 class Solver:
@@ -75,15 +76,18 @@ class Solver:
         res = self.solve_batch([circuit], options, None if x0 is None else [np.asarray(x0, dtype="float64")])
         return (res.matrices[0], res.x[0])
 
-    def _start_points(self, gp, options, rng):
-        return rng.random((self.starts, gp.n_params)) * (2 * np.pi)
+    def _start_points(self, gp, options, rng, starts=None):
+        return rng.random((int(starts) if starts else self.starts, gp.n_params)) * (2 * np.pi)
 
-    def _solve_opts(self, options):
+    def _solve_opts(self, options, frontier=False):
         return _tolerances(options)
 
-    def solve_batch(self, circuits, options, x0s=None, want_matrices=True):
+    def solve_batch(self, circuits, options, x0s=None, want_matrices=True, starts=None, frontier=False):
         """Solve every circuit from `starts` start vectors each, in one launch; keep the best start per circuit.
-        x0s: optional list (one entry per circuit) of a vector or an array [k, P] of start vectors."""
+        x0s: optional list (one entry per circuit) of a vector or an array [k, P] of start vectors.
+        starts: overrides the solver's own number of random starts per circuit (the parallelizer sizes it to the GPUs).
+        frontier: the batch is one expansion of a search, which only waits for its slowest instance: the solver may
+        apply its batch-level stop rules (LeastSquares_Jac_Solver: straggler cap, sibling stop)."""
         lib = _lib.get_library()
         T = _target_of(options)
         gps = [program_for(c) for c in circuits]
@@ -93,7 +97,7 @@ class Solver:
             if x0s is not None and x0s[ci] is not None:
                 pts = np.atleast_2d(np.asarray(x0s[ci], dtype="float64"))
             else:
-                pts = self._start_points(gp, options, rng)
+                pts = self._start_points(gp, options, rng, starts)
             for p in pts:
                 if p.size != gp.n_params:
                     raise ValueError("start vector of length {} for a circuit with {} parameters".format(p.size, gp.n_params))
@@ -101,7 +105,7 @@ class Solver:
                 chunks.append(p)
                 owner.append(ci)
         flat = np.concatenate(chunks) if chunks else np.zeros(0)
-        x, f, iters, status = lib.solve(self.method, gps, poi, flat, T, **self._solve_opts(options))
+        x, f, iters, status = lib.solve(self.method, gps, poi, flat, T, **self._solve_opts(options, frontier))
         owner = np.asarray(owner)
         offs = np.concatenate([[0], np.cumsum([gps[c].n_params for c in owner])]).astype(np.int64)
         best_x, best_f, best_it, best_st = [], [], [], []
@@ -116,7 +120,7 @@ class Solver:
         mats = None
         if want_matrices and gps:
             mats = lib.eval_matrix(gps, np.arange(len(gps), dtype="int32"), np.concatenate(best_x) if best_x else np.zeros(0))
-        return BatchResult(best_x, best_f, best_it, best_st, mats)
+        return BatchResult(best_x, best_f, best_it, best_st, mats, np.asarray(iters), np.asarray(status))
 
     def __eq__(self, other):
         return type(self) == type(other) and self.__dict__ == other.__dict__
@@ -128,18 +132,28 @@ class Solver:
 class LeastSquares_Jac_Solver(Solver):
     """Batched Levenberg-Marquardt on the device (qsb_solve_lm)."""
     method = "lm"
+    # batch-level stop rules used when the batch is a frontier expansion (qsb_solver_opts, include/qsb200.h): an
+    # instance is stopped once it has used FRONTIER_STRAGGLER x the Jacobian evaluations of the slowest instance among the
+    # half of the batch that finished first, or once another start of its circuit reached options.threshold
+    FRONTIER_STRAGGLER = 2.0
 
-    def __init__(self, starts=1, max_iters=0):
+    def __init__(self, starts=1, max_iters=0, straggler_factor=None, sibling_stop=None):
         self.starts = int(starts)
         self.max_iters = int(max_iters)
+        self.straggler_factor = straggler_factor  # None: off for plain solves, FRONTIER_STRAGGLER for frontier batches
+        self.sibling_stop = sibling_stop          # None: off for plain solves, options.threshold for frontier batches
 
-    def _solve_opts(self, options):
+    def _solve_opts(self, options, frontier=False):
         if not _has_residuals(options):
             # the reference's least-squares solver silently ignores the objective here (solvers.py:150); fail loudly
             raise ValueError("LeastSquares_Jac_Solver needs an objective with a residual form; {} has none".format(
                 type(options.objective).__name__))
         o = _tolerances(options)
         o["max_iters"] = self.max_iters
+        thr = options.threshold if "threshold" in options else 1e-10
+        sf, ss = self.straggler_factor, self.sibling_stop
+        o["straggler_factor"] = float(sf) if sf is not None else (self.FRONTIER_STRAGGLER if frontier else 0.0)
+        o["sibling_stop"] = float(ss) if ss is not None else (float(thr) if frontier else 0.0)
         return o
 
     @property
@@ -156,7 +170,7 @@ class BFGS_Jac_Solver(Solver):
         self.memory_size = int(memory_size)
         self.max_iters = int(max_iters)
 
-    def _solve_opts(self, options):
+    def _solve_opts(self, options, frontier=False):
         if not rides_on_device(options):
             # the reference's BFGS minimises objective.gen_error_jac (solvers.py:142); the device kernel minimises the
             # Hilbert-Schmidt distance against objective.device_target - refuse anything else instead of ignoring it
@@ -191,17 +205,17 @@ class NaiveMultiStart_Solver(Solver):
     def distance_metric(self):
         return (self.inner_solver or LeastSquares_Jac_Solver()).distance_metric
 
-    def solve_batch(self, circuits, options, x0s=None, want_matrices=True):
+    def solve_batch(self, circuits, options, x0s=None, want_matrices=True, starts=None, frontier=False):
         inner = self._inner(options)
         gps = [program_for(c) for c in circuits]
         rng = np.random.default_rng(options.seed) if "seed" in options and options.seed is not None else np.random.default_rng()
-        starts = []
+        pts_per_circuit = []
         for ci, gp in enumerate(gps):
             pts = rng.random((self.num_threads, gp.n_params)) * (2 * np.pi)
             if x0s is not None and x0s[ci] is not None:
                 pts[0] = np.asarray(x0s[ci], dtype="float64")
-            starts.append(pts)
-        return inner.solve_batch(circuits, options, starts, want_matrices)
+            pts_per_circuit.append(pts)
+        return inner.solve_batch(circuits, options, pts_per_circuit, want_matrices, frontier=frontier)
 
 
 def aposmm_start_indices(x_on_cube, f, mu=1e-4):
@@ -239,7 +253,7 @@ class MultiStart_Solver(NaiveMultiStart_Solver):
     than `num_threads` points qualify, fewer solves are started, like the reference (:88)."""
     n_samples = 100
 
-    def solve_batch(self, circuits, options, x0s=None, want_matrices=True):
+    def solve_batch(self, circuits, options, x0s=None, want_matrices=True, starts=None, frontier=False):
         inner = self._inner(options)
         lib = _lib.get_library()
         T = _target_of(options)
@@ -249,10 +263,10 @@ class MultiStart_Solver(NaiveMultiStart_Solver):
         poi = np.repeat(np.arange(len(gps), dtype="int32"), self.n_samples)
         vals = lib.eval_distance(gps, poi, np.concatenate([(2 * np.pi * s).ravel() for s in cubes]) if gps else np.zeros(0), T)
         vals = vals.reshape(len(gps), self.n_samples)
-        starts = []
+        pts_per_circuit = []
         for ci in range(len(gps)):
             if gps[ci].n_params == 0:
-                starts.append(np.zeros((1, 0)))
+                pts_per_circuit.append(np.zeros((1, 0)))
                 continue
             order = aposmm_start_indices(cubes[ci], vals[ci])[: self.num_threads]
             if len(order) == 0:
@@ -261,8 +275,8 @@ class MultiStart_Solver(NaiveMultiStart_Solver):
             if x0s is not None and x0s[ci] is not None:
                 pts = np.vstack([np.asarray(x0s[ci], dtype="float64")[None, :], pts[:-1]]) if len(pts) > 1 else \
                     np.asarray(x0s[ci], dtype="float64")[None, :]
-            starts.append(pts)
-        return inner.solve_batch(circuits, options, starts, want_matrices)
+            pts_per_circuit.append(pts)
+        return inner.solve_batch(circuits, options, pts_per_circuit, want_matrices, frontier=frontier)
 
 
 def default_solver(options=None):

@@ -51,3 +51,31 @@ def microbench_workload(n, n_circuits=100, n_vectors=1000, depth=10):
     params = microbench_params(rng, n_circuits, n_vectors, P)
     targets = {"qft": unitaries.qft(1 << n), "haar": haar_unitary(1 << n, SEED_BASE + 100 + n)}
     return circuits, params, targets
+
+
+YORKTOWN = [(0, 1), (0, 2), (1, 2), (2, 3), (2, 4), (3, 4)]  # examples/qft5_ibm_yorktown.py:21
+
+
+def frontier_workload(n, n_parents=None, depth=None, starts=4, seed=0):
+    """One frontier expansion as the search produces it (compiler.py:136-146, leap_compiler.py:202-212): `n_parents`
+    (default: 48 children) seeded parent circuits of `depth` layers, each extended by every search layer of the gateset
+    (n = 4: QubitCNOTLinear, 3 layers; n = 5: the Yorktown adjacency list, 6 layers), `starts` uniform start vectors per
+    child.  Returns (children, x0s [per child: (starts, P)], targets): targets["unreachable"] = qft(2^n) (no child reaches
+    it at this depth: the regime the search spends its time in), targets["reachable"] = (child 0, seeded parameters)."""
+    from . import gates, gatesets, unitaries
+    rng = np.random.default_rng(SEED_BASE + 7000 + 10 * n + seed)
+    g = gatesets.QubitCNOTLinear() if n <= 4 else gatesets.QubitCNOTAdjacencyList(YORKTOWN)
+    layers = g.search_layers(n)
+    if depth is None:
+        depth = 10 if n <= 4 else 12
+    if n_parents is None:
+        n_parents = max(1, 48 // len(layers))
+    children = []
+    for _ in range(n_parents):
+        c = gates.ProductGate(g.initial_layer(n))
+        for _ in range(depth - 1):
+            c = c.appending(layers[int(rng.integers(len(layers)))][0])
+        children += [c.appending(layer) for layer, _ in layers]
+    x0s = [rng.random((starts, c.num_inputs)) * (2 * np.pi) for c in children]
+    x_star = rng.random(children[0].num_inputs) * (2 * np.pi)
+    return children, x0s, {"unreachable": unitaries.qft(1 << n), "reachable": (children[0], x_star)}

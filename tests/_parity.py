@@ -114,3 +114,26 @@ def check_every_leaf_type(lib, n, tol=TOL):
         assert np.abs(J[i * P:(i + 1) * P] - np.array(Jo)).max() < tol
         assert np.abs(r[i] - O.matrix_residuals(T, Uo)).max() < tol
         assert np.abs(Jr[i * P:(i + 1) * P].T - O.matrix_residuals_jac(T, Uo, Jo)).max() < tol
+
+
+def check_zero_overlap(lib, n):
+    """S = Tr(T^dagger U) == 0 exactly: all-zero angles make the U3 layer the identity and T = X (x) I
+    is traceless.  f = 1 and the gradient is +inf in every component, the native backend's convention
+    (qsrs/src/utils.rs:144-146; the Python backend divides by zero, comparison.py:53).  Both HS kernel families."""
+    from qsearch_b200 import gates, _lib
+    c = gates.ProductGate(gates.KroneckerGate(*[gates.U3Gate() for _ in range(n)]))
+    gp = lowering.lower(c)
+    X = np.array([[0, 1], [1, 0]], dtype="complex128")
+    T = np.kron(X, np.eye(1 << (n - 1)))
+    x = np.zeros((1, c.num_inputs))
+    for kind in (0, 1):
+        b = lib.batch([gp], np.zeros(1, dtype="int32"))
+        b.set_kernel(kind)
+        b.set_params(x)
+        b.set_target(T)
+        b.run(_lib.RUN_HS)
+        f, g, _ = b.fetch()
+        b.close()
+        assert f[0] == 1.0
+        assert np.all(np.isposinf(g)), g
+    assert lib.eval_distance([gp], [0], x, T)[0] == 1.0

@@ -216,3 +216,52 @@ def test_captured_constants_are_keyed_by_their_exact_bytes():
         assert np.abs(Ua - Ub).max() > 1e-11
     finally:
         __import__("qsearch_b200")._lib.use_library(prev)
+
+
+def test_zero_overlap_gradient_convention():
+    lib = emulated_library()
+    for n in (2, 3):
+        _parity.check_zero_overlap(lib, n)
+
+
+def test_general_lm_kernel_for_a_non_unitary_target():
+    """The body-frame LM needs a unitary target; anything else (nothing in the reference forbids it) must take the general
+    kernel and still minimise |U T^dagger - I|: here T = 0.8 x a reachable unitary, whose minimiser is the same circuit."""
+    from oracle import qs_oracle as O
+    from qsearch_b200 import gates, gatesets, lowering
+    lib = emulated_library()
+    rng = np.random.default_rng(31)
+    g = gatesets.QubitCNOTLinear()
+    c = gates.ProductGate(g.initial_layer(3)).appending(g.search_layers(3)[0][0]).appending(g.search_layers(3)[1][0])
+    x_star = rng.random(c.num_inputs) * 2 * np.pi
+    T = 0.8 * O.matrix(c, x_star)
+    gp = lowering.lower(c)
+    x0 = x_star[None, :] + 0.05 * rng.standard_normal((2, c.num_inputs))
+    x, f, iters, status = lib.solve("lm", [gp], np.zeros(2, dtype="int32"), x0, T)
+    for k, xk in enumerate(x.reshape(2, -1)):
+        assert abs(O.matrix_distance_squared(T, O.matrix(c, xk)) - f[k]) < 1e-12
+        r = O.matrix_residuals(T, O.matrix(c, xk))
+        assert abs(0.5 * r @ r - 0.5 * 8 * 0.2 ** 2) < 1e-9  # U T^dagger = 0.8 I at the optimum: |0.8 I - I|^2 / 2
+
+
+def test_batch_stop_rules():
+    """qsb_solver_opts.straggler_factor / sibling_stop: off by default (every start runs to its own convergence); with a
+    sibling threshold the other starts of a solved circuit stop (status 7) and the best result is unchanged."""
+    from oracle import qs_oracle as O
+    from qsearch_b200 import gates, gatesets, lowering
+    lib = emulated_library()
+    rng = np.random.default_rng(17)
+    g = gatesets.QubitCNOTLinear()
+    c = gates.ProductGate(g.initial_layer(3)).appending(g.search_layers(3)[0][0]).appending(g.search_layers(3)[1][0])
+    T = O.matrix(c, rng.random(c.num_inputs) * 2 * np.pi)
+    gp = lowering.lower(c)
+    K = 24
+    x0 = rng.random((K, c.num_inputs)) * 2 * np.pi
+    poi = np.zeros(K, dtype="int32")
+    x, f, iters, status = lib.solve("lm", [gp], poi, x0, T)
+    assert set(np.unique(status)) <= {1, 2, 3, 4, 5} and f.min() < 1e-10
+    x2, f2, iters2, status2 = lib.solve("lm", [gp], poi, x0, T, sibling_stop=1e-10, straggler_factor=2.0)
+    assert f2.min() < 1e-10
+    assert (status2 == 7).sum() + (status2 == 6).sum() > 0 and iters2.sum() < iters.sum()
+    for k in range(K):  # whatever stopped an instance, the reported distance is the distance at the returned parameters
+        assert abs(O.matrix_distance_squared(T, O.matrix(c, x2.reshape(K, -1)[k])) - f2[k]) < 1e-12

@@ -245,3 +245,74 @@ def test_lm_system_run_kind(lib, n):
         assert abs(rr[i] - r @ r) < 1e-11
         assert np.abs(g[i * P:(i + 1) * P] - Jr.T @ r).max() < 1e-11
         assert np.abs(A[i * P * P:(i + 1) * P * P].reshape(P, P) - Jr.T @ Jr).max() < 1e-11
+
+
+def test_zero_overlap_gradient_convention(lib):
+    for n in (3, 4, 5):
+        _parity.check_zero_overlap(lib, n)
+
+
+def test_inserting_programs_against_oracle(lib):
+    """ProductGate.inserting (gates.py:1022-1030): the circuits the re-optimising post-processor builds
+    (post_processing.py:250) lower to programs whose parameter order shifts behind the insertion point."""
+    rng = np.random.default_rng(8)
+    g = gatesets.QubitCNOTLinear()
+    base = gates.ProductGate(g.initial_layer(4))
+    layers = g.search_layers(4)
+    for k in range(5):
+        base = base.appending(layers[k % len(layers)][0])
+    circuits = [base.inserting(layers[(k + 1) % len(layers)][0], depth=k + 1) for k in range(4)]
+    circuits.append(gates.ProductGate(*base._subgates[:2], *base._subgates[4:]))  # a window cut out (post_processing.py:247)
+    xs = [rng.random((2, c.num_inputs)) * 2 * np.pi for c in circuits]
+    assert _parity.check_against_oracle(lib, circuits, xs, unitaries.qft(16)) == 10
+
+
+def test_body_frame_lm_agrees_with_the_general_kernel(lib, monkeypatch):
+    """qsb_k_lm3 (body-frame normal equations, unitary target) and qsb_k_lm2 (explicit J_r) are the same Gauss-Newton model:
+    same convergence on reachable targets, and on an unreachable one the same local minima from the same starts."""
+    rng = np.random.default_rng(77)
+    for n, depth in ((3, 4), (4, 5), (5, 4)):
+        g = gatesets.QubitCNOTRing()
+        c = gates.ProductGate(g.initial_layer(n))
+        layers = g.search_layers(n)
+        for _ in range(depth):
+            c = c.appending(layers[int(rng.integers(len(layers)))][0])
+        gp = lowering.lower(c)
+        K = 12
+        x0 = rng.random((K, gp.n_params)) * 2 * np.pi
+        poi = np.zeros(K, dtype="int32")
+        for T in (O.matrix(c, rng.random(c.num_inputs) * 2 * np.pi), unitaries.qft(1 << n)):
+            monkeypatch.setenv("QSB_LM_KERNEL", "lm3")
+            x3, f3, it3, st3 = lib.solve("lm", [gp], poi, x0, T)
+            monkeypatch.setenv("QSB_LM_KERNEL", "lm2")
+            x2, f2, it2, st2 = lib.solve("lm", [gp], poi, x0, T)
+            monkeypatch.delenv("QSB_LM_KERNEL")
+            assert abs(f3.min() - f2.min()) < 1e-8, (n, f3.min(), f2.min())
+            assert np.median(np.abs(f3 - f2)) < 1e-6  # most starts end in the same minimum (trajectories differ in rounding only)
+            for k in range(K):
+                assert abs(O.matrix_distance_squared(T, O.matrix(c, x3.reshape(K, -1)[k])) - f3[k]) < 1e-12
+
+
+def test_batch_stop_rules(lib):
+    """Straggler cap and sibling stop (qsb_solver_opts): fewer iterations, same best value, consistent outputs."""
+    rng = np.random.default_rng(5)
+    g = gatesets.QubitCNOTLinear()
+    layers = g.search_layers(4)
+    base = gates.ProductGate(g.initial_layer(4))
+    for _ in range(5):
+        base = base.appending(layers[int(rng.integers(len(layers)))][0])
+    children = [base.appending(l) for l, _ in layers]
+    T = O.matrix(children[1], rng.random(children[1].num_inputs) * 2 * np.pi)  # child 1 is reachable
+    gps = [lowering.lower(c) for c in children]
+    K = 32
+    poi = np.repeat(np.arange(len(gps), dtype="int32"), K)
+    x0 = np.concatenate([rng.random(gps[i].n_params) * 2 * np.pi for i in poi])
+    x, f, it, st = lib.solve("lm", gps, poi, x0, T)
+    x2, f2, it2, st2 = lib.solve("lm", gps, poi, x0, T, straggler_factor=2.0, sibling_stop=1e-10)
+    assert set(np.unique(st)) <= {0, 1, 2, 3, 4, 5}
+    assert f.reshape(3, K)[1].min() < 1e-10 and f2.reshape(3, K)[1].min() < 1e-10
+    assert (st2 == 7).sum() > 0 and np.all(poi[st2 == 7] == 1)  # only starts of the solved child are stopped as siblings
+    assert it2.sum() < it.sum() and it2.max() <= it.max()
+    off = np.concatenate([[0], np.cumsum([gps[i].n_params for i in poi])])
+    for k in range(0, len(poi), 7):
+        assert abs(O.matrix_distance_squared(T, O.matrix(children[poi[k]], x2[off[k]:off[k + 1]])) - f2[k]) < 1e-12

@@ -71,3 +71,25 @@ def test_qft4_leap():
     res = q.LeapCompiler().compile(opts)
     n = check(res, T)
     assert res["cut_depths"][-1] == n and n <= 30  # README.md:31: 13 with the plain search; LEAP trades length for time
+
+
+def test_leap_reoptimizing_post_processor_on_the_device():
+    """post_processing.py:108-295 on the batched device solver: a padded 3-qubit LEAP-style result (Toffoli solved on a
+    12-layer circuit; the README count is 8) gets shorter and still implements the target."""
+    from qsearch_b200 import post_processing
+    T = unitaries.toffoli
+    g = gatesets.QubitCNOTLinear()
+    layers = g.search_layers(3)
+    circ = gates.ProductGate(g.initial_layer(3))
+    for k in range(12):
+        circ = circ.appending(layers[k % len(layers)][0])
+    opts = q.Options(target=T, seed=4, gateset=g)
+    opts.set_defaults(**q.defaults.standard_defaults)
+    opts.set_smart_defaults(**q.defaults.standard_smart_defaults)
+    res = solvers.LeastSquares_Jac_Solver(starts=16).solve_batch([circ], opts)
+    assert res.distance[0] < 1e-10
+    padded = {"structure": circ, "parameters": res.x[0], "cut_depths": [0, 4, 8, 12]}
+    out = post_processing.LEAPReoptimizing_PostProcessor().post_process_circuit(
+        padded, q.Options(target=T, seed=4, gateset=g, reoptimize_size=5))
+    assert cnots(out["structure"]) < 12
+    assert O.matrix_distance_squared(T, O.matrix(out["structure"], out["parameters"])) < 1e-10

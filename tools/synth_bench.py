@@ -25,6 +25,9 @@ CASES = {
     "or": (lambda: unitaries.logical_or, gatesets.QubitCNOTLinear, "search"),
     "toffoli_ring": (lambda: unitaries.toffoli, gatesets.QubitCNOTRing, "search"),
     "qft3_ring": (lambda: unitaries.qft(8), gatesets.QubitCNOTRing, "search"),
+    "fredkin_ring": (lambda: unitaries.fredkin, gatesets.QubitCNOTRing, "search"),
+    "peres_ring": (lambda: unitaries.peres, gatesets.QubitCNOTRing, "search"),
+    "or_ring": (lambda: unitaries.logical_or, gatesets.QubitCNOTRing, "search"),
     "qft4_leap": (lambda: unitaries.qft(16), gatesets.QubitCNOTLinear, "leap"),
     "qft4_search": (lambda: unitaries.qft(16), gatesets.QubitCNOTLinear, "search"),
     "qft5_yorktown_leap": (lambda: unitaries.qft(32), lambda: gatesets.QubitCNOTAdjacencyList(YORKTOWN), "leap"),
@@ -40,6 +43,9 @@ def main():
     ap.add_argument("--min-depth", type=int, default=3)
     ap.add_argument("--timeout", type=float, default=600)
     ap.add_argument("--beams", type=int, default=-1)
+    ap.add_argument("--fstarts", type=int, default=0, help="options.frontier_starts (0: sized to the GPUs by the parallelizer)")
+    ap.add_argument("--straggler", type=float, default=-1.0, help="LM straggler_factor for frontier batches (-1: solver default)")
+    ap.add_argument("--seed0", type=int, default=1000)
     ap.add_argument("--reopt", type=int, default=0, help="run LEAPReoptimizing_PostProcessor with this window size on LEAP results")
     a = ap.parse_args()
     lib = _lib.get_library()
@@ -48,8 +54,13 @@ def main():
         mk_t, mk_gs, kind = CASES[name]
         T = mk_t()
         for rep in range(a.reps):
-            solver = solvers.LeastSquares_Jac_Solver(starts=a.starts) if a.solver == "lm" else solvers.BFGS_Jac_Solver(starts=a.starts)
-            opts = q.Options(target=T, gateset=mk_gs(), solver=solver, seed=1000 + rep, timeout=a.timeout)
+            if a.solver == "lm":
+                solver = solvers.LeastSquares_Jac_Solver(starts=a.starts, straggler_factor=None if a.straggler < 0 else a.straggler)
+            else:
+                solver = solvers.BFGS_Jac_Solver(starts=a.starts)
+            opts = q.Options(target=T, gateset=mk_gs(), solver=solver, seed=a.seed0 + rep, timeout=a.timeout)
+            if a.fstarts > 0:
+                opts.frontier_starts = a.fstarts
             if a.beams > 0:
                 opts.beams = a.beams
             if kind == "leap":
@@ -67,7 +78,7 @@ def main():
                 extra = {"reopt_window": a.reopt, "reopt_wall_s": round(time.perf_counter() - t1, 3),
                          "cnots_before": repr(res["structure"]).count("CNOTGate"), "reopt_stats": post.get("stats")}
                 res = dict(res, structure=post["structure"], parameters=post["parameters"], distance=post.get("distance", res["distance"]))
-            print(json.dumps({"case": name, "rep": rep, "solver": a.solver, "starts": a.starts, "beams": a.beams, "wall_s": round(dt, 3),
+            print(json.dumps({"case": name, "rep": rep, "solver": a.solver, "starts": a.starts, "fstarts": a.fstarts, "straggler": a.straggler, "beams": a.beams, "devices": lib.num_devices, "wall_s": round(dt, 3),
                               "cnots": repr(res["structure"]).count("CNOTGate"), "distance": float(res["distance"]),
                               "stats": res["stats"], "launches": lib.launch_count() - l0, **extra}), flush=True)
 
