@@ -170,6 +170,23 @@ int qsb_solve_lbfgs(qsb_ctx* ctx, int n_programs, const qsb_program* const* prog
                     const qsb_solver_opts* opts, double* out_x, double* out_f, int32_t* out_iters,
                     int32_t* out_status);
 
+/* ---- allocation-free variant of QSB_RUN_LMSYS --------------------------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Computes, for n_instances parameter vectors of ONE program, what qsb_batch_run(QSB_RUN_LMSYS) + qsb_batch_fetch return:
+ *   out_rr [n] = r'r,   out_g [n][P] = J_r'r,   out_A [n][P][P] = J_r'J_r (row-major).
+ * params [n][P], target [N][N][2] (must be unitary) and the outputs are caller-owned and may be HOST or DEVICE memory
+ * (copied with cudaMemcpyDefault).  The call allocates nothing on the device: its whole working set is one static
+ * __device__ array of QSB_STATIC_SCRATCH_BYTES that every GPU which loads the library holds until the process exits.
+ * Limits (QSB_ERR_UNSUPPORTED with a message otherwise): one-qubit-leaf + CNOT programs on 3..5 qubits; staged inputs +
+ * outputs <= 16 MiB, i.e. about 8 (P^2 + 2 P + 1) n bytes (n = 4, P = 62: ~500 instances); per-instance scratch <= 48 MiB.
+ * Every call shares the array and it keeps the previous call's contents (the kernel zeroes what it accumulates into).
+ * Calls on one device are serialised inside this library and the call returns after the stream has drained; work that
+ * reaches the same GPU from another process or library copy while a call runs would race on the array. */
+#define QSB_STATIC_SCRATCH_BYTES ((size_t)64 << 20)
+int qsb_eval_lm_system_static(qsb_ctx* ctx, int device_slot, const qsb_program* prog, int n_instances,
+                              const double* params, const double* target, double* out_rr, double* out_g, double* out_A);
+
 /* ---- device micro-benchmarks (FP64 pipe / DMMA peak measured on the box; bench.py records them) ---------- */
 int qsb_measure_fp64_peak(qsb_ctx* ctx, int device_slot, int use_dmma, double* out_tflops);
 

@@ -94,6 +94,7 @@ class Library:
         d.qsb_solve_lm.argtypes = solve
         d.qsb_solve_lbfgs.argtypes = solve
         d.qsb_measure_fp64_peak.argtypes = [_vp, ctypes.c_int, ctypes.c_int, _c_dp]
+        d.qsb_eval_lm_system_static.argtypes = [_vp, ctypes.c_int, _vp, ctypes.c_int, _c_dp, _c_dp, _c_dp, _c_dp, _c_dp]
 
     def check(self, rc):
         if rc != 0:
@@ -274,6 +275,22 @@ class Library:
             self.check(fn(self.ctx, len(gps), handles, len(poi), poi.ctypes.data_as(_c_ip), _dp(x0), T.ctypes.data_as(_c_dp),
                           ctypes.byref(opts), _dp(x), _dp(f), iters.ctypes.data_as(_c_ip), status.ctypes.data_as(_c_ip)))
         return x, f, iters, status
+
+    def eval_lm_system_static(self, gp, params, target, slot=0):
+        """qsb_eval_lm_system_static: (r'r [n], J_r'r [n, P], J_r'J_r [n, P, P]) of n parameter vectors of ONE program, computed
+        without any device allocation (static scratch array, include/qsb200.h)."""
+        keys, hs = self._acquire([gp])
+        try:
+            V = np.ascontiguousarray(np.atleast_2d(_f64(params)))
+            n, P = V.shape
+            if P != gp.n_params:
+                raise ValueError("expected {} parameters per vector, got {}".format(gp.n_params, P))
+            T = np.ascontiguousarray(target, dtype="complex128")
+            rr, g, A = np.empty(n), np.empty((n, P)), np.empty((n, P, P))
+            self.check(self.dll.qsb_eval_lm_system_static(self.ctx, slot, hs[0], n, _dp(V), T.ctypes.data_as(_c_dp), _dp(rr), _dp(g), _dp(A)))
+        finally:
+            self._release(keys)
+        return rr, g, A
 
     def measure_fp64_peak(self, slot=0, use_dmma=False):
         out = ctypes.c_double()

@@ -30,6 +30,7 @@ UNITS = [
     ("solve_lbfgs", "qsb_solve.cu", ["-DQSB_SOLVE_TU=1"]),
     ("solve_lm5", "qsb_solve.cu", ["-DQSB_SOLVE_TU=2"]),
     ("peak", "qsb_peak.cu", []),
+    ("noalloc", "qsb_noalloc.cu", []),
 ]
 
 

@@ -27,7 +27,7 @@
 #define __forceinline__ inline
 #define __restrict__
 #define __launch_bounds__(...)
-#define __align__(n) alignas(n)
+#define __align__(n) __attribute__((aligned(n)))
 
 struct double2 { double x, y; };
 static inline double2 make_double2(double x, double y) { return double2{x, y}; }
@@ -162,6 +162,7 @@ static inline cudaError_t cudaEventElapsedTime(float* ms, cudaEvent_t a, cudaEve
   *ms = std::chrono::duration<float, std::milli>(b->t - a->t).count(); return 0;
 }
 static inline cudaError_t cudaGetLastError() { return 0; }
+template <class T> static inline cudaError_t cudaGetSymbolAddress(void** p, T& sym) { *p = (void*)&sym; return 0; }  // emulated: host address
 static inline const char* cudaGetErrorString(cudaError_t) { return "emulated"; }
 template <class F> static inline cudaError_t cudaFuncSetAttribute(F, int, int) { return 0; }
 static inline cudaError_t cudaMemGetInfo(size_t* f, size_t* t) { *f = *t = (size_t)8 << 30; return 0; }
