@@ -72,6 +72,108 @@ def cpu_arm(n, n_evals, procs, target_name="qft"):
     return n_evals / dt, dt
 
 
+# ----------------------------------------------------------------------------- solve form: CPU arm (scipy LM on the oracle)
+QSRS_CAVEAT = ("CPU arm = NumPy restatement of the reference's NumPy backend (kind 'port'); the reference's own Rust backend "
+               "qsrs, which cannot be built offline, claims 'up to a 20x speedup' over it (qsrs/README.md:5): divide CPU "
+               "ratios by up to 20 for a qsrs-equivalent figure")
+
+
+def _solve_target(n, which):
+    children, x0s, targets = workloads.frontier_workload(n)
+    if which == "unreachable":
+        return children, x0s, targets["unreachable"]
+    from oracle import qs_oracle as O
+    c0, x_star = targets["reachable"]
+    return children, x0s, O.matrix(c0, x_star)
+
+
+def _cpu_solve_work(job):
+    """One reference-style solve: scipy.optimize.least_squares(method='lm') on the oracle's residuals / residual Jacobian
+    (qsearch/solvers.py:155-157: the call LeastSquares_Jac_Solver makes)."""
+    from threadpoolctl import threadpool_limits
+    import scipy.optimize
+    from oracle import qs_oracle as O
+    n, which, ci, si = job
+    with threadpool_limits(1):
+        children, x0s, T = _solve_target(n, which)
+        c = children[ci]
+        t0 = time.perf_counter()
+        res = scipy.optimize.least_squares(lambda x: O.matrix_residuals(T, O.matrix(c, x)), x0s[ci][si],
+                                           jac=lambda x: O.matrix_residuals_jac(T, *O.mat_jac(c, x)), method="lm")
+        dt = time.perf_counter() - t0
+    return dt, int(res.njev), float(O.matrix_distance_squared(T, O.matrix(c, res.x)))
+
+
+def cpu_solve_arm(n, procs):
+    """One solve per host core (bounded sample of the solve-form workload), all cores busy at once."""
+    children, _, _ = workloads.frontier_workload(n)
+    jobs = [(n, "unreachable" if k % 2 == 0 else "reachable", (k // 2 * 5) % len(children) if k % 2 == 0 else 0, k % 4) for k in range(procs)]
+    ctx = mp.get_context("fork")
+    t0 = time.perf_counter()
+    with ctx.Pool(procs) as pool:
+        out = pool.map(_cpu_solve_work, jobs)
+    wall = time.perf_counter() - t0
+    njev = sum(o[1] for o in out)
+    return {"solves_per_s": len(jobs) / wall, "solves": len(jobs), "wall_s": wall, "cores": procs, "jac_evals": njev,
+            "us_per_lm_iteration_per_core": 1e6 * sum(o[0] for o in out) / max(1, njev),
+            "solver": "scipy.optimize.least_squares(method='lm') on oracle/qs_oracle.py, one solve per core", "caveat": QSRS_CAVEAT}
+
+
+def solve_form(lib, n, dist, world, cpu_solve):
+    """Frontier-shaped batch (48 children x 4 starts; once against an unreachable target, once against a reachable one)
+    through Solver.solve_batch end to end: host start vectors in, (xopt, distance) out."""
+    import qsearch_b200 as q
+    from qsearch_b200 import solvers, _lib as L
+    prev = L.use_library(lib)
+    try:
+        out = {}
+        for frontier in (False, True):
+            tot_t, tot_inst, tot_it, max_it, best = 0.0, 0, 0, 0, []
+            for which in ("unreachable", "reachable"):
+                children, x0s, T = _solve_target(n, which)
+                opts = q.Options(target=T, threshold=1e-10)
+                solver = solvers.LeastSquares_Jac_Solver(starts=4)
+                solver.solve_batch(children[:2], opts, x0s[:2], want_matrices=False, frontier=frontier)  # warm-up: module load, buffers
+                barrier(dist)
+                t0 = time.perf_counter()
+                res = solver.solve_batch(children, opts, x0s, want_matrices=False, frontier=frontier)
+                dt = all_max(dist, time.perf_counter() - t0)
+                tot_t += dt
+                tot_inst += len(res.all_iterations)
+                tot_it += int(res.all_iterations.sum())
+                max_it += int(res.all_iterations.max())
+                best.append(float(min(res.distance)))
+            key = "frontier_rules" if frontier else "reference_semantics"
+            out[key] = {"solves_per_s": world * tot_inst / tot_t, "instances": tot_inst, "wall_s": tot_t, "lm_iterations": tot_it,
+                        "us_per_lm_iteration_latency": 1e6 * tot_t / max(1, max_it),
+                        "instance_iterations_per_s": world * tot_it / tot_t, "best_distance": best}
+        out["what"] = ("n={}: 48 children x 4 starts, once against qft (unreachable) and once against a reachable target, through "
+                       "LeastSquares_Jac_Solver.solve_batch (host x0 in, xopt / distance out). reference_semantics: every start runs to "
+                       "its own convergence; frontier_rules: straggler cap 2x + sibling stop, as GpuParallelizer runs it".format(n))
+        if cpu_solve is not None:
+            out["cpu"] = cpu_solve
+            out["speedup_vs_cpu"] = out["reference_semantics"]["solves_per_s"] / cpu_solve["solves_per_s"]
+        return out
+    finally:
+        L.use_library(prev)
+
+
+def load_ncu_digest(n):
+    """Hot-kernel ncu figures of the newest round that has them (profiles/r*/hot_kernel_ncu.json, written from one
+    `ncu --set full` capture by tools/ncu_digest.py --json)."""
+    import glob
+    for path in sorted(glob.glob(os.path.join(ROOT, "profiles", "r*", "hot_kernel_ncu.json")), reverse=True):
+        try:
+            d = json.load(open(path))
+            if str(n) in d:
+                e = dict(d[str(n)])
+                e["file"] = os.path.relpath(path, ROOT)
+                return e
+        except Exception:
+            pass
+    return None
+
+
 # ----------------------------------------------------------------------------- helpers
 class ClockSampler:
     def __init__(self, gpu_index):
@@ -173,7 +275,7 @@ def run_reference(args, rank, world):
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": workload_config(args, n, G, P),
             "cpu_baseline": {"value": value, "unit": "evals/s", "cores": procs, "kind": "port",
-                             "sample": "{} LM-form evals per step over {} forked workers (BLAS threads = 1)".format(per_step, procs)},
+                             "sample": "{} LM-form evals per step over {} forked workers (BLAS threads = 1). {}".format(per_step, procs, QSRS_CAVEAT)},
             "e2e": {"value": value, "unit": "evals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
 
@@ -187,8 +289,11 @@ def run_ours(args, rank, world, local_rank):
         n_evals = max(procs * 4, int(args.cpu_evals))
         v, dt = cpu_arm(n, n_evals, procs)
         cpu = {"value": v, "unit": "evals/s", "cores": procs, "kind": "port",
-               "sample": "{} LM-form evals of the same workload in {:.1f} s on {} forked workers, oracle/qs_oracle.py "
-                         "(NumPy restatement of the reference path; qsrs is not buildable offline)".format(n_evals, dt, procs)}
+               "sample": "{} LM-form evals of the same workload in {:.1f} s on {} forked workers, oracle/qs_oracle.py. {}".format(
+                   n_evals, dt, procs, QSRS_CAVEAT)}
+    cpu_solve = None
+    if rank == 0 and world == 1 and not args.no_cpu and not args.no_solve:
+        cpu_solve = cpu_solve_arm(n, os.cpu_count() or 1)
     dist = dist_setup(world)
 
     from qsearch_b200 import _lib
@@ -259,17 +364,8 @@ def run_ours(args, rank, world, local_rank):
     sel = slice(0, e_inst)
     out_r = lib.pinned_empty((e_inst, 2 * N * N))      # page-locked host buffers (qsb_host_alloc)
     out_J = lib.pinned_empty((e_inst * P, 2 * N * N))
-    # warm-up: page faults of the output buffers, device buffers, host threads.  On a fresh box the first calls of a process
-    # run at 0.1-0.8x of the steady rate for a while (profiles/r1/as_e2e_ab.log), so warm up until two consecutive calls
-    # agree within 5 % (at least max(3, W) calls, at most 16)
-    prev = None
-    for w in range(16):
-        tw = time.perf_counter()
+    for _ in range(max(3, args.warmup)):  # page faults of the pinned output buffers, device buffers, host threads
         lib.eval_residuals_jac(gps, poi[sel], flat[sel], T, out_r, out_J)
-        tw = time.perf_counter() - tw
-        if w + 1 >= max(3, args.warmup) and prev is not None and abs(tw - prev) <= 0.05 * max(tw, prev):
-            break
-        prev = tw
     barrier(dist)
     t0 = time.perf_counter()
     e_steps = max(1, min(args.steps, 3))
@@ -283,16 +379,50 @@ def run_ours(args, rank, world, local_rank):
     f, g = lib.eval_hs_grad(gps, poi, flat, T)
     t_hs_e2e = all_max(dist, time.perf_counter() - t0)
 
+    sf = None
+    if not args.no_solve:
+        sf = solve_form(lib, n, dist, world, cpu_solve)
     if rank != 0:
         return
     F = flops_lm(n, G, P)
     peaks = load_peaks()
     hbm_peak = peaks.get("hbm_gbs", 6650.0)
-    achieved_tf = (n_inst / (kern_ms * 1e-3)) * F / 1e12
-    # what the warp kernel really issues on the FP64 tensor pipe: P half-size complex products (N x N/2 x N, rank-one form
-    # of the derivative) + one dense product for U T^dagger = (4 P + 8) N^3 flop per eval
-    executed_dmma_tf = (n_inst / (kern_ms * 1e-3)) * (4.0 * P + 8.0) * (N ** 3) / 1e12
-    ncu_traffic = {4: 255610.0, 5: 1068462.0}.get(n)  # dram read+write bytes per eval: profiles/r1/an_ncu_full_resid_n{4,5}_warp.txt
+    evals_per_s_gpu = n_inst / (kern_ms * 1e-3)  # one GPU
+    algorithmic_tf = evals_per_s_gpu * F / 1e12
+    # Two roofs are close for this kernel: the HBM write of (r, J_r) and the FP64 pipe (DMMA + DFMA share
+    # it).  `roofline` reports the BINDING one = the larger executed fraction; the other and the algorithmic-flop figure of
+    # SURVEY 8d (which the kernel does not execute: rank-one derivative products, structured updates) are side keys.
+    hbm_achieved = out_bytes / (kern_ms * 1e-3) / 1e9
+    hbm_frac = hbm_achieved / hbm_peak
+    ncu = load_ncu_digest(n)
+    # executed FP64 flops per eval: DMMA (512 flop each) + DFMA (64) + DMUL/DADD (32), instruction counts from the ncu capture;
+    # without a digest fall back to the tensor-pipe part the source fixes: (4 P + 8) N^3
+    if ncu and ncu.get("fp64_flop_per_eval"):
+        exec_flop, exec_src = float(ncu["fp64_flop_per_eval"]), ncu["file"]
+    else:
+        exec_flop, exec_src = (4.0 * P + 8.0) * (N ** 3), "source: (4 P + 8) N^3 DMMA flop per eval (no ncu digest found)"
+    fp64_exec_tf = evals_per_s_gpu * exec_flop / 1e12
+    fp64_peak_best = max(fp64_peak, dmma_peak)
+    fp64_frac = fp64_exec_tf / fp64_peak_best if fp64_peak_best else 0.0
+    if hbm_frac >= fp64_frac:
+        roof = {"bound": "hbm", "achieved": hbm_achieved, "peak": hbm_peak, "unit": "GB/s", "frac": hbm_frac,
+                "peak_source": "MEASURED_PEAKS.json hbm_gbs (copy bandwidth, driver-measured)" if "hbm_gbs" in peaks else "fallback 6650 GB/s (B200_PROFILING.md)"}
+    else:
+        roof = {"bound": "tensor", "achieved": fp64_exec_tf, "peak": fp64_peak_best, "unit": "TFLOP/s", "frac": fp64_frac,
+                "peak_source": "builder-measured FP64 pipe peak (qsb_measure_fp64_peak in this run; FP64 is not in MEASURED_PEAKS.json)"}
+    roof.update({
+        "traffic": int(ncu["dram_bytes_per_eval"] * n_inst) if ncu and ncu.get("dram_bytes_per_eval") else None,
+        "algorithmic_bytes": int(out_bytes + n_inst * P * 8),
+        "hbm": {"achieved": hbm_achieved, "peak": hbm_peak, "unit": "GB/s", "frac": hbm_frac, "bytes_per_eval": out_bytes / n_inst},
+        "fp64_executed": {"achieved": fp64_exec_tf, "peak": fp64_peak_best, "unit": "TFLOP/s", "frac": fp64_frac,
+                          "flop_per_eval": exec_flop, "source": exec_src, "dfma_peak": fp64_peak, "dmma_peak": dmma_peak,
+                          "peak_source": "builder-measured in this run (qsb_measure_fp64_peak); FP64 is not in MEASURED_PEAKS.json"},
+        "algorithmic": {"tflops": algorithmic_tf, "ratio_to_fp64_peak": algorithmic_tf / fp64_peak_best if fp64_peak_best else None,
+                        "flop_per_eval": F,
+                        "note": "SURVEY 8d dense prefix/suffix flop count; NOT a hardware fraction: the kernel executes "
+                                "rank-one half-size products and 2x2-structured updates instead (parity-tested), so this exceeds 1"},
+        "ncu": ncu,
+    })
     line = {
         "metric": "objective+Jacobian evals/sec", "value": value, "unit": "evals/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": kern_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -301,32 +431,21 @@ def run_ours(args, rank, world, local_rank):
         "e2e": {"value": e2e_value, "unit": "evals/s", "h2d_bytes_per_step": int(e_inst * P * 8 + 2 * N * N * 8),
                 "d2h_bytes_per_step": int(e_inst * (P + 1) * 2 * N * N * 8),
                 "note": "qsb_eval_residuals_jac with host buffers, {} instances per step (r and J_r copied back: "
-                        "PCIe-bound by the {:.2f} MB of Jacobian per eval)".format(e_inst, (P + 1) * 2 * N * N * 8 / 1e6)},
-        "roofline": {"bound": "tensor", "achieved": achieved_tf, "peak": dmma_peak, "unit": "TFLOP/s",
-                     "frac": achieved_tf / dmma_peak if dmma_peak else None,
-                     "traffic": int(ncu_traffic * n_inst) if ncu_traffic else None,
-                     "peak_source": "FP64 tensor pipe (DMMA m8n8k4) micro-benchmark run by this command (qsb_measure_fp64_peak); "
-                                    "FP64 is not in MEASURED_PEAKS.json (bf16 and HBM only)",
-                     "dfma_peak": fp64_peak,
-                     "flops": "achieved = ALGORITHMIC flops (dense prefix/suffix formulation, SURVEY 8d: 8N^3(2(G-1)+2P) + 8N^3(P+1)) per "
-                              "second; gate structure lets the kernel execute fewer, so frac can exceed 1. Executed on the tensor pipe: "
-                              "(4 P + 8) N^3 flop per eval (see executed); DFMA work shares the same FP64 pipe",
-                     "executed": {"dmma_tflops": executed_dmma_tf, "frac_of_dmma_peak": executed_dmma_tf / dmma_peak if dmma_peak else None,
-                                  "ncu_dmma_pipe_active_pct": {4: 44.9, 5: 54.2}.get(n),
-                                  "ncu_fp64_dfma_pipe_active_pct": {4: 21.9, 5: 19.3}.get(n)},
-                     "traffic_note": "ncu dram bytes per eval (one --set full capture, profiles/r1) x instances of this launch",
-                     "hbm": {"achieved": out_bytes / (kern_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
-                             "frac": out_bytes / (kern_ms * 1e-3) / 1e9 / hbm_peak,
-                             "bytes_per_eval": out_bytes / n_inst}},
+                        "PCIe-bound by the {:.2f} MB of Jacobian per eval); the call the search itself makes is solve_form".format(
+                            e_inst, (P + 1) * 2 * N * N * 8 / 1e6)},
+        "roofline": roof,
         "hs_form": {"value": world * n_inst / (hs_ms * 1e-3), "unit": "evals/s", "ms_per_step": hs_ms,
                     "e2e_value": world * n_inst / t_hs_e2e, "algorithmic_flop_per_eval": flops_hs(n, G, P)},
         "lm_system_form": {"value": world * n_sys / (sys_ms * 1e-3), "unit": "evals/s", "instances": n_sys,
-                           "what": "r'r, J_r'r, J_r'J_r per instance (QSB_RUN_LMSYS: DMMA Jacobian + DMMA SYRK, J_r never written to HBM)",
-                           "algorithmic_flop_per_eval": F + 2 * 2 * N * N * (P + 1) * (P + 1)},
+                           "what": "r'r, J_r'r, J_r'J_r per instance (QSB_RUN_LMSYS, body-frame form for the unitary target: forward-only "
+                                   "sweep + Gram product over N^2-real rows; nothing of size N^2 P leaves the SM's L1/L2)"},
         "parity_max_abs_err": worst,
     }
+    if sf is not None:
+        line["solve_form"] = sf
     if cpu is not None:
         line["cpu_baseline"] = cpu
+        line["vs_cpu_baseline"] = {"device_resident": value / cpu["value"], "e2e": e2e_value / cpu["value"], "note": QSRS_CAVEAT}
     print(json.dumps(line), flush=True)
 
 
@@ -342,14 +461,14 @@ def main():
     ap.add_argument("--e2e-instances", type=int, default=16384)
     ap.add_argument("--cpu-evals", type=float, default=0)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-solve", action="store_true", help="skip the solve_form key (frontier-shaped batched solves)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))
     local_rank = int(os.environ.get("LOCAL_RANK", 0))
-    if args.cpu_evals <= 0:  # about 10-20 s of CPU work: ~100 evals/s/core for n=4 in NumPy
-        args.cpu_evals = (1200 if args.qubits <= 4 else 700) * max(1, (os.cpu_count() or 1)) / 8 * 1.0
-        args.cpu_evals = max(args.cpu_evals, 8 * (os.cpu_count() or 1))
+    if args.cpu_evals <= 0:  # 10-15 s of CPU work: ~120 (n=4) / ~75 (n=5) LM-form evals/s/core in NumPy
+        args.cpu_evals = (1500 if args.qubits <= 4 else 900) * max(1, (os.cpu_count() or 1))
     if args.impl == "reference":
         run_reference(args, rank, world)
     else:
