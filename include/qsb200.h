@@ -45,7 +45,12 @@ enum qsb_opcode {
   QSB_OP_ZXZXZ = 8, /* ZXZXZGate  gates.py:208  3 params */
   QSB_OP_CONST1 = 9, /* constant 2x2 on qubit q0; const_off -> 8 doubles in the pool */
   QSB_OP_CNOT = 10,  /* CNOT(control q0, target q1): CNOTGate :604 / NonadjacentCNOTGate :696 (a row permutation) */
-  QSB_OP_CONSTK = 11 /* constant 2^k x 2^k on contiguous qubits q0..q0+k-1 (k = q1); const_off -> 2*4^k doubles */
+  QSB_OP_CONSTK = 11, /* constant 2^k x 2^k on contiguous qubits q0..q0+k-1 (k = q1); const_off -> 2*4^k doubles */
+  /* two-qubit rotations exp(-i x/2 P (x) P) on qubits (q0, q1): the native backend's RXX / RYY / RZZ gates
+   * (qsrs/src/circuits.rs:457-633; no Python twin in qsearch/gates.py).  1 param each. */
+  QSB_OP_RXX = 12, /* circuits.rs:457-514 */
+  QSB_OP_RYY = 13, /* circuits.rs:516-578 */
+  QSB_OP_RZZ = 14  /* circuits.rs:580-633 */
 };
 
 typedef struct qsb_op {

@@ -88,6 +88,27 @@ def _zxzxz(v):  # gates.py:219-254 : Rz(v2) SX Rz(v1) SX Rz(v0)
     return chain(*z), [chain(d[0], z[1], z[2]), chain(z[0], d[1], z[2]), chain(z[0], z[1], d[2])]
 
 
+def _rxx(v):  # qsrs/src/circuits.rs:457-514 (GateRXX::mat / mat_jac; no Python twin in qsearch/gates.py)
+    c, s = np.cos(v[0] / 2), -1j * np.sin(v[0] / 2)
+    dc, ds = -np.sin(v[0] / 2) / 2, -1j * np.cos(v[0] / 2) / 2
+    def m(c, s):
+        return np.array([[c, 0, 0, s], [0, c, s, 0], [0, s, c, 0], [s, 0, 0, c]], dtype="complex128")
+    return m(c, s), [m(dc, ds)]
+
+
+def _ryy(v):  # qsrs/src/circuits.rs:516-578 (GateRYY)
+    c, ns, ps = np.cos(v[0] / 2), -1j * np.sin(v[0] / 2), 1j * np.sin(v[0] / 2)
+    dc, dns, dps = -np.sin(v[0] / 2) / 2, -1j * np.cos(v[0] / 2) / 2, 1j * np.cos(v[0] / 2) / 2
+    def m(c, ns, ps):
+        return np.array([[c, 0, 0, ps], [0, c, ns, 0], [0, ns, c, 0], [ps, 0, 0, c]], dtype="complex128")
+    return m(c, ns, ps), [m(dc, dns, dps)]
+
+
+def _rzz(v):  # qsrs/src/circuits.rs:580-633 (GateRZZ)
+    pos, neg = np.exp(0.5j * v[0]), np.exp(-0.5j * v[0])
+    return np.diag([neg, pos, pos, neg]).astype("complex128"), [np.diag([-0.5j * neg, 0.5j * pos, 0.5j * pos, -0.5j * neg]).astype("complex128")]
+
+
 _PARAM_LEAVES = {
     "XGate": lambda v: (_rx(v[0]), [_rx_d(v[0])]),
     "YGate": lambda v: (_ry(v[0]), [_ry_d(v[0])]),
@@ -97,6 +118,9 @@ _PARAM_LEAVES = {
     "U1Gate": _u1,
     "XZXZGate": _xzxz,
     "ZXZXZGate": _zxzxz,
+    "RXXGate": _rxx,
+    "RYYGate": _ryy,
+    "RZZGate": _rzz,
 }
 
 

@@ -120,7 +120,7 @@ extern "C" int qsb_ctx_launch_count(const qsb_ctx* ctx, uint64_t* out) {
 // ---------------------------------------------------------------------------- programs
 static int op_params(int opcode) {
   switch (opcode) {
-    case QSB_OP_RX: case QSB_OP_RY: case QSB_OP_RZ: case QSB_OP_U1: return 1;
+    case QSB_OP_RX: case QSB_OP_RY: case QSB_OP_RZ: case QSB_OP_U1: case QSB_OP_RXX: case QSB_OP_RYY: case QSB_OP_RZZ: return 1;
     case QSB_OP_U2: case QSB_OP_XZXZ: return 2;
     case QSB_OP_U3: case QSB_OP_ZXZXZ: return 3;
     default: return 0;
@@ -157,6 +157,14 @@ extern "C" int qsb_program_create(qsb_ctx* ctx, int n_qubits, int n_ops, const q
         if (o.q0 < 0 || o.q0 >= n_qubits || o.q1 < 0 || o.q1 >= n_qubits || o.q0 == o.q1)
           return qsb_fail(QSB_ERR_INVALID, "op " + std::to_string(j) + ": bad CNOT qubits");
         break;
+      case QSB_OP_RXX: case QSB_OP_RYY: case QSB_OP_RZZ:
+        if (o.q0 < 0 || o.q0 >= n_qubits || o.q1 < 0 || o.q1 >= n_qubits || o.q0 == o.q1)
+          return qsb_fail(QSB_ERR_INVALID, "op " + std::to_string(j) + ": bad two-qubit rotation qubits");
+        if (o.param_off < 0 || o.param_off + 1 > n_params) return qsb_fail(QSB_ERR_INVALID, "op " + std::to_string(j) + ": parameter range out of bounds");
+        if (seen[o.param_off]) return qsb_fail(QSB_ERR_INVALID, "parameter used by two ops");
+        seen[o.param_off] = 1;
+        fast = false;  // interpreter kernels only (the warp kernels are specialised to one-qubit leaves + CNOT)
+        break;
       case QSB_OP_CONSTK: {
         int k = o.q1;
         if (k < 1 || o.q0 < 0 || o.q0 + k > n_qubits) return qsb_fail(QSB_ERR_INVALID, "op " + std::to_string(j) + ": bad CONSTK range");
@@ -179,7 +187,7 @@ extern "C" int qsb_program_create(qsb_ctx* ctx, int n_qubits, int n_ops, const q
   for (int j = 0; j < n_ops; ++j) {
     const qsb_op& o = ops[j];
     switch (o.opcode) {
-      case QSB_OP_RX: case QSB_OP_RY: case QSB_OP_RZ: pscale[o.param_off] = 0.5; break;
+      case QSB_OP_RX: case QSB_OP_RY: case QSB_OP_RZ: case QSB_OP_RXX: case QSB_OP_RYY: case QSB_OP_RZZ: pscale[o.param_off] = 0.5; break;
       case QSB_OP_U3: pscale[o.param_off] = 0.5; break;
       case QSB_OP_XZXZ: pscale[o.param_off] = pscale[o.param_off + 1] = 0.5; break;
       case QSB_OP_ZXZXZ: pscale[o.param_off] = pscale[o.param_off + 1] = pscale[o.param_off + 2] = 0.5; break;
@@ -194,7 +202,7 @@ extern "C" int qsb_program_create(qsb_ctx* ctx, int n_qubits, int n_ops, const q
       qsb_op& o = p->ops[j];
       const int np = op_params(o.opcode);
       o.reserved = j + used;
-      if (o.opcode != QSB_OP_CNOT && o.opcode != QSB_OP_CONSTK)
+      if (o.opcode != QSB_OP_CNOT && o.opcode != QSB_OP_CONSTK && o.opcode != QSB_OP_RXX && o.opcode != QSB_OP_RYY && o.opcode != QSB_OP_RZZ)
         for (int w = 0; w <= np; ++w) slotmap[o.reserved + w] = (j << 2) | w;
       used += np;
     }

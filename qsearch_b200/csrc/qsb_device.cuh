@@ -56,9 +56,11 @@ QSB_DEVICE cplx cfma_conj(cplx a, cplx b, cplx acc) {
   return acc;
 }
 
+QSB_DEVICE bool qsb_is_rpp(int opcode) { return opcode == QSB_OP_RXX || opcode == QSB_OP_RYY || opcode == QSB_OP_RZZ; }
+
 QSB_DEVICE int qsb_num_params(int opcode) {
   switch (opcode) {
-    case QSB_OP_RX: case QSB_OP_RY: case QSB_OP_RZ: case QSB_OP_U1: return 1;
+    case QSB_OP_RX: case QSB_OP_RY: case QSB_OP_RZ: case QSB_OP_U1: case QSB_OP_RXX: case QSB_OP_RYY: case QSB_OP_RZZ: return 1;
     case QSB_OP_U2: case QSB_OP_XZXZ: return 2;
     case QSB_OP_U3: case QSB_OP_ZXZXZ: return 3;
     default: return 0;
@@ -69,7 +71,7 @@ QSB_DEVICE int qsb_num_params(int opcode) {
 // Cache the sin/cos a parameterised op needs (6 doubles), so every thread can rebuild g / dg cheaply.
 QSB_DEVICE void qsb_trig(int opcode, const double* x, double* t) {
   switch (opcode) {
-    case QSB_OP_RX: case QSB_OP_RY: case QSB_OP_RZ:
+    case QSB_OP_RX: case QSB_OP_RY: case QSB_OP_RZ: case QSB_OP_RXX: case QSB_OP_RYY: case QSB_OP_RZZ:
       sincos(0.5 * x[0], &t[1], &t[0]);  // t0 = cos(x/2), t1 = sin(x/2)
       break;
     case QSB_OP_U1:

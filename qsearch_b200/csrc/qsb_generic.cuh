@@ -121,11 +121,43 @@ QSB_DEVICE void qsb_constk(cplx* M, int q0, int k, const double* C, bool dagger,
   }
 }
 
+// Two-qubit rotation R = exp(-i x/2 P(x)P) = c I - i s P(x)P on qubits (q0, q1), P = X, Y or Z (circuits.rs:457-633):
+// P(x)P is a signed permutation of the index, so R mixes index pairs (k, k ^ m0 ^ m1) [XX, YY] or is diagonal [ZZ]:
+//   XX: (PP v)[k] = v[k ^ m]      YY: (PP v)[k] = -(-1)^(b0 + b1) v[k ^ m]      ZZ: (PP v)[k] = (-1)^(b0 + b1) v[k]
+// dst = scale (c src - i s PP src).  With (c, s, scale) = (-s, c, 1/2) this is dR/dx = -i/2 PP R = R(x + pi) / 2; with
+// s -> -s the inverse.  left: rows of M are the index; right: M <- M R, columns (PP is symmetric for XX, YY, ZZ).
+// Out of place when dst != src; in place each thread owns a whole pair.
+QSB_DEVICE void qsb_rpp_pair(int opcode, bool odd, cplx a, cplx b, double c, double s, cplx& oa, cplx& ob) {
+  cplx pa, pb;  // (PP v)[k0], (PP v)[k1]
+  if (opcode == QSB_OP_RXX) { pa = b; pb = a; }
+  else if (opcode == QSB_OP_RYY) { const double f = odd ? 1.0 : -1.0; pa = cscale(b, f); pb = cscale(a, f); }
+  else { const double f = odd ? -1.0 : 1.0; pa = cscale(a, f); pb = cscale(b, f); }
+  // c v - i s p:  re = c v.re + s p.im,  im = c v.im - s p.re
+  oa = cmk(fma(c, a.x, s * pa.y), fma(c, a.y, -s * pa.x));
+  ob = cmk(fma(c, b.x, s * pb.y), fma(c, b.y, -s * pb.x));
+}
+
+template <int NQ>
+QSB_DEVICE void qsb_rpp(cplx* dst, const cplx* src, int opcode, int q0, int q1, double c, double s, double scale, bool right) {
+  constexpr int N = 1 << NQ;
+  const int m0 = 1 << (NQ - 1 - q0), m1 = 1 << (NQ - 1 - q1), sh = NQ - 1 - q0;
+  c *= scale; s *= scale;
+  for (int idx = threadIdx.x; idx < N * N / 2; idx += blockDim.x) {
+    const int o = idx & (N - 1), k0 = qsb_insert_zero_bit(idx >> NQ, sh), k1 = k0 ^ m0 ^ m1;  // k0 has bit q0 clear
+    const int e0 = right ? o * N + k0 : k0 * N + o, e1 = right ? o * N + k1 : k1 * N + o;
+    const cplx a = src[e0], b = src[e1];
+    cplx oa, ob;
+    qsb_rpp_pair(opcode, (k0 & m1) != 0, a, b, c, s, oa, ob);  // parity of (b0 + b1) at k0 (b0 = 0); k1 has the same parity
+    dst[e0] = oa; dst[e1] = ob;
+  }
+}
+
 // Apply op j to M from the left (dagger: its inverse).  All threads call; caller synchronises afterwards.
 template <int NQ>
 QSB_DEVICE void qsb_apply_left(cplx* M, const qsb_op& op, const double* trig, const double* consts, bool dagger) {
   if (op.opcode == QSB_OP_CNOT) { qsb_left_cnot<NQ>(M, op.q0, op.q1); return; }
   if (op.opcode == QSB_OP_CONSTK) { qsb_constk<NQ>(M, op.q0, op.q1, consts + op.const_off, dagger, false); return; }
+  if (qsb_is_rpp(op.opcode)) { qsb_rpp<NQ>(M, M, op.opcode, op.q0, op.q1, trig[0], dagger ? -trig[1] : trig[1], 1.0, false); return; }
   cplx g[4];
   qsb_op2x2(op, trig, consts, dagger, g);
   qsb_left_2x2<NQ>(M, op.q0, g);
@@ -135,6 +167,7 @@ template <int NQ>
 QSB_DEVICE void qsb_apply_right(cplx* M, const qsb_op& op, const double* trig, const double* consts) {
   if (op.opcode == QSB_OP_CNOT) { qsb_right_cnot<NQ>(M, op.q0, op.q1); return; }
   if (op.opcode == QSB_OP_CONSTK) { qsb_constk<NQ>(M, op.q0, op.q1, consts + op.const_off, false, true); return; }
+  if (qsb_is_rpp(op.opcode)) { qsb_rpp<NQ>(M, M, op.opcode, op.q0, op.q1, trig[0], trig[1], 1.0, true); return; }
   cplx g[4];
   qsb_op2x2(op, trig, consts, false, g);
   qsb_right_2x2<NQ>(M, op.q0, g);
@@ -239,7 +272,9 @@ QSB_DEVICE void qsb_jac_instance(cplx* X, cplx* S, cplx* Y, double* trig, const 
     for (int k = 0; k < np; ++k) {
       cplx dg[4];
       qsb_gate2x2(op.opcode, tj, 1 + k, dg);
-      {  // Y = (dg (x) I) X, out of place
+      if (qsb_is_rpp(op.opcode)) {  // Y = dR X = R(x + pi) X / 2, out of place
+        qsb_rpp<NQ>(Y, X, op.opcode, op.q0, op.q1, -tj[1], tj[0], 0.5, false);
+      } else {  // Y = (dg (x) I) X, out of place
         const int sh = NQ - 1 - op.q0, s = 1 << sh;
         for (int idx = threadIdx.x; idx < NN / 2; idx += blockDim.x) {
           int c = idx & (N - 1), r0 = qsb_insert_zero_bit(idx >> NQ, sh), r1 = r0 | s;
@@ -317,10 +352,27 @@ QSB_DEVICE double qsb_hs_instance(cplx* X, cplx* L, cplx* red, cplx* wpart, cplx
       __syncthreads();
       continue;
     }
+    cplx pk[3] = {cmk(0, 0), cmk(0, 0), cmk(0, 0)};
+    if (qsb_is_rpp(op.opcode)) {  // two-qubit rotation: peel X, correlate L with dR X = R(x + pi) X / 2, peel L; pairs (k0, k0 ^ m0 ^ m1)
+      const int m0 = 1 << (NQ - 1 - op.q0), m1 = 1 << (NQ - 1 - op.q1), sh0 = NQ - 1 - op.q0;
+      const double c = tj[0], sn = tj[1];
+      for (int idx = threadIdx.x; idx < NN / 2; idx += blockDim.x) {
+        const int o = idx & (N - 1), k0 = qsb_insert_zero_bit(idx >> NQ, sh0), k1 = k0 ^ m0 ^ m1;
+        const bool odd = (k0 & m1) != 0;
+        cplx ra, rb, ya, yb, la2, lb2;
+        qsb_rpp_pair(op.opcode, odd, X[k0 * N + o], X[k1 * N + o], c, -sn, ra, rb);  // R_j pair
+        X[k0 * N + o] = ra; X[k1 * N + o] = rb;
+        qsb_rpp_pair(op.opcode, odd, ra, rb, -0.5 * sn, 0.5 * c, ya, yb);
+        const cplx la = L[k0 * N + o], lb = L[k1 * N + o];
+        pk[0] = cfma_conj(la, ya, pk[0]);
+        pk[0] = cfma_conj(lb, yb, pk[0]);
+        qsb_rpp_pair(op.opcode, odd, la, lb, c, -sn, la2, lb2);
+        L[k0 * N + o] = la2; L[k1 * N + o] = lb2;
+      }
+    } else {
     cplx gd[4], dg[3][4];
     qsb_op2x2(op, tj, P.consts, true, gd);
     for (int k = 0; k < np; ++k) qsb_gate2x2(op.opcode, tj, 1 + k, dg[k]);
-    cplx pk[3] = {cmk(0, 0), cmk(0, 0), cmk(0, 0)};
     const int sh = NQ - 1 - op.q0, s = 1 << sh;
     for (int idx = threadIdx.x; idx < NN / 2; idx += blockDim.x) {
       int c = idx & (N - 1), r0 = qsb_insert_zero_bit(idx >> NQ, sh), r1 = r0 | s;
@@ -335,6 +387,7 @@ QSB_DEVICE double qsb_hs_instance(cplx* X, cplx* L, cplx* red, cplx* wpart, cplx
       }
       L[r0 * N + c] = cfma(gd[1], lb, cmul(gd[0], la));
       L[r1 * N + c] = cfma(gd[3], lb, cmul(gd[2], la));
+    }
     }
     for (int k = 0; k < np; ++k) {
       for (int m = 16; m > 0; m >>= 1) {

@@ -80,73 +80,40 @@ class XGate(_Param1Q):
     """Rx(v0) (reference: gates.py:132-149)."""
     num_inputs = 1
 
-    def assemble(self, v, i=0):
-        return [("gate", "X", (v[0],), (i,))]
-
 
 class YGate(_Param1Q):
     """Ry(v0) (reference: gates.py:151-168)."""
     num_inputs = 1
-
-    def assemble(self, v, i=0):
-        return [("gate", "Y", (v[0],), (i,))]
 
 
 class ZGate(_Param1Q):
     """Rz(v0) (reference: gates.py:170-187)."""
     num_inputs = 1
 
-    def assemble(self, v, i=0):
-        return [("gate", "Z", (v[0],), (i,))]
-
 
 class ZXZXZGate(_Param1Q):
     """Rz(v2) SX Rz(v1) SX Rz(v0) (reference: gates.py:208-268)."""
     num_inputs = 3
-
-    def assemble(self, v, i=0):
-        v = np.array(v) % (2 * np.pi)
-        seq = [("gate", "Z", (v[0],), (i,)), ("gate", "SX", (), (i,)), ("gate", "Z", (v[1],), (i,)),
-               ("gate", "SX", (), (i,)), ("gate", "Z", (v[2],), (i,))]
-        return [("block", seq)]
 
 
 class XZXZGate(_Param1Q):
     """Rz(v1) SX Rz(v0) SX (reference: gates.py:270-316)."""
     num_inputs = 2
 
-    def assemble(self, v, i=0):
-        v = np.array(v) % (2 * np.pi)
-        seq = [("gate", "SX", (), (i,)), ("gate", "Z", (v[0],), (i,)), ("gate", "SX", (), (i,)),
-               ("gate", "Z", (v[1],), (i,))]
-        return [("block", seq)]
-
 
 class U3Gate(_Param1Q):
     """IBM U3(theta, phi, lambda) (reference: gates.py:318-356)."""
     num_inputs = 3
-
-    def assemble(self, v, i=0):
-        v = np.array(v) % (2 * np.pi)
-        return [("gate", "U3", (v[0], v[1], v[2]), (i,))]
 
 
 class U2Gate(_Param1Q):
     """IBM U2(phi, lambda) (reference: gates.py:358-385)."""
     num_inputs = 2
 
-    def assemble(self, v, i=0):
-        v = np.array(v) % (2 * np.pi)
-        return [("gate", "U3", (np.pi / 2, v[0], v[1]), (i,))]
-
 
 class U1Gate(_Param1Q):
     """IBM U1(lambda) = diag(1, e^{i lambda}) (reference: gates.py:387-409)."""
     num_inputs = 1
-
-    def assemble(self, v, i=0):
-        v = np.array(v) % (2 * np.pi)
-        return [("gate", "U3", (0, 0, v[0]), (i,))]
 
 
 class SingleQutritGate(Gate):
@@ -173,9 +140,6 @@ class IdentityGate(_Const):
         self._d = d
         self._const = np.array(np.eye(d ** qudits), dtype="complex128")
 
-    def assemble(self, v, i=0):
-        return []
-
     def __repr__(self):
         if self.qudits == 1 and self._d == 2:
             return "IdentityGate()"
@@ -185,41 +149,48 @@ class IdentityGate(_Const):
 class SXGate(_Const):
     _const = unitaries.sqrt_x
 
-    def assemble(self, v, i=0):
-        return [("gate", "SX", (), (i,))]
+
+class _Param2Q(Gate):
+    qudits = 2
+    num_inputs = 1
+
+
+class RXXGate(_Param2Q):
+    """exp(-i v0/2 X(x)X) on two adjacent qubits.  The reference's native backend knows this gate by the class NAME
+    "RXXGate" (object_to_gate, qsrs/src/lib.rs:216; matrix and derivative qsrs/src/circuits.rs:457-514) but qsearch/gates.py
+    ships no Python class of that name; this one supplies the structure so that such circuits can be built and lowered."""
+
+
+class RYYGate(_Param2Q):
+    """exp(-i v0/2 Y(x)Y) (qsrs/src/lib.rs:217, qsrs/src/circuits.rs:516-578)."""
+
+
+class RZZGate(_Param2Q):
+    """exp(-i v0/2 Z(x)Z) (qsrs/src/lib.rs:218, qsrs/src/circuits.rs:580-633)."""
 
 
 class _Const2Q(_Const):
     qudits = 2
-    _asm = "CUSTOM"
-
-    def assemble(self, v, i=0):
-        return [("gate", self._asm, (), (i, i + 1))]
 
 
 class CNOTGate(_Const2Q):
     _const = unitaries.cnot
-    _asm = "CNOT"
 
 
 class CZGate(_Const2Q):
     _const = unitaries.cz
-    _asm = "CZ"
 
 
 class ISwapGate(_Const2Q):
     _const = unitaries.iswap
-    _asm = "ISWAP"
 
 
 class XXGate(_Const2Q):
     _const = unitaries.xx
-    _asm = "XX"
 
 
 class CNOTRootGate(_Const2Q):
     _const = unitaries.sqrt_cnot
-    _asm = "sqrt(CNOT)"
 
 
 class NonadjacentCNOTGate(_Const):
@@ -232,9 +203,6 @@ class NonadjacentCNOTGate(_Const):
 
     def const_matrix(self):
         return unitaries.arbitrary_cnot(self.qudits, self.control, self.target)
-
-    def assemble(self, v, i=0):
-        return [("gate", "CNOT", (), (self.control, self.target))]
 
     def validate_structure(self):
         return self.control < self.qudits and self.target < self.qudits and self.control != self.target
@@ -254,10 +222,6 @@ class UGate(_Const):
         self.gateparams = gateparams
         self.gateindices = gateindices
         self._const = self.U
-
-    def assemble(self, v, i=0):
-        idx = self.gateindices if self.gateindices is not None else tuple(i + j for j in range(self.qudits))
-        return [("gate", self.gatename, self.gateparams, idx)]
 
     def __repr__(self):
         return "UGate({}, {}, {}, {}, {})".format(
@@ -280,9 +244,6 @@ class CUGate(_Const):
         self.flipped = flipped
         self.qudits = 2
 
-    def assemble(self, v, i=0):
-        return [("gate", self.gatename, self.gateparams, (i + 1, i) if self.flipped else (i, i + 1))]
-
     def __repr__(self):
         return "CUGate({}, {}{})".format(repr(self._U), repr(self.gatename), ", flipped=True" if self.flipped else "")
 
@@ -298,14 +259,6 @@ class KroneckerGate(Gate):
 
     def appending(self, gate):
         return KroneckerGate(*self._subgates, gate)
-
-    def assemble(self, v, i=0):
-        out, k = [], 0
-        for g in self._subgates:
-            out += g.assemble(v[k:k + g.num_inputs], i)
-            k += g.num_inputs
-            i += g.qudits
-        return [("block", out)]
 
     def _parts(self):
         return self._subgates
@@ -331,13 +284,6 @@ class ProductGate(Gate):
     def inserting(self, *gates, depth=-1):
         # same slicing convention as the reference (gates.py:1022-1030)
         return ProductGate(*self._subgates[:depth], *gates, *self._subgates[depth:])
-
-    def assemble(self, v, i=0):
-        out, k = [], 0
-        for g in self._subgates:
-            out += g.assemble(v[k:k + g.num_inputs], i)
-            k += g.num_inputs
-        return out
 
     def validate_structure(self):
         return all(g.qudits == self.qudits and g.validate_structure() for g in self._subgates)

@@ -8,7 +8,8 @@ walk but emits a *flat* program of elementary ops acting on the full register (i
 * ``ProductGate``  -> its sub-programs one after another (later subgates multiply on the left, gates.py:959);
 * ``KroneckerGate`` -> its sub-programs at increasing qubit offsets (they commute, so order is free; depth-first
   order keeps the parameter order of gates.py:861-864);
-* parameterised one-qubit leaves -> one op carrying (qubit, first parameter index);
+* parameterised one-qubit leaves -> one op carrying (qubit, first parameter index); the native backend's two-qubit
+  rotations ``RXXGate`` / ``RYYGate`` / ``RZZGate`` (qsrs/src/lib.rs:216-218) -> one op on (qubit, qubit + 1);
 * ``CNOTGate`` / ``NonadjacentCNOTGate`` -> a permutation op (no constant needed);
 * ``IdentityGate`` -> nothing;
 * any other zero-parameter gate -> a constant op with its matrix in the program's constant pool.
@@ -20,8 +21,11 @@ import numpy as np
 OP_DTYPE = np.dtype([("opcode", "<i4"), ("q0", "<i4"), ("q1", "<i4"), ("param_off", "<i4"),
                      ("const_off", "<i4"), ("reserved", "<i4")])
 
-OP_RX, OP_RY, OP_RZ, OP_U1, OP_U2, OP_U3, OP_XZXZ, OP_ZXZXZ, OP_CONST1, OP_CNOT, OP_CONSTK = range(1, 12)
+OP_RX, OP_RY, OP_RZ, OP_U1, OP_U2, OP_U3, OP_XZXZ, OP_ZXZXZ, OP_CONST1, OP_CNOT, OP_CONSTK, OP_RXX, OP_RYY, OP_RZZ = range(1, 15)
 MAX_QUBITS = 5
+
+# two-qubit rotations of the native backend (qsrs/src/lib.rs:216-218): one op on qubits (q, q + 1), 1 parameter
+_PARAM_LEAVES_2Q = {"RXXGate": OP_RXX, "RYYGate": OP_RYY, "RZZGate": OP_RZZ}
 
 _PARAM_LEAVES = {
     "XGate": (OP_RX, 1), "YGate": (OP_RY, 1), "ZGate": (OP_RZ, 1), "U1Gate": (OP_U1, 1), "U2Gate": (OP_U2, 2),
@@ -91,6 +95,11 @@ class _Builder:
             if gate.num_inputs != np_:
                 raise ValueError("Unknown gate {}: unexpected parameter count".format(name))
             self.ops.append((opcode, q_off, 0, p_off, 0, 0))
+            return
+        if name in _PARAM_LEAVES_2Q:
+            if gate.num_inputs != 1 or gate.qudits != 2:
+                raise ValueError("Unknown gate {}: unexpected shape".format(name))
+            self.ops.append((_PARAM_LEAVES_2Q[name], q_off, q_off + 1, p_off, 0, 0))
             return
         if name == "CNOTGate":
             self.ops.append((OP_CNOT, q_off, q_off + 1, 0, 0, 0))

@@ -137,3 +137,32 @@ def check_zero_overlap(lib, n):
         assert f[0] == 1.0
         assert np.all(np.isposinf(g)), g
     assert lib.eval_distance([gp], [0], x, T)[0] == 1.0
+
+
+def two_qubit_rotation_circuits(n):
+    """Circuits mixing RXX / RYY / RZZ (qsrs/src/circuits.rs:457-633) with one-qubit leaves and CNOTs on n qubits, every
+    adjacent qubit pair used by every rotation kind."""
+    from qsearch_b200 import gates
+    I, u3 = gates.IdentityGate(), gates.U3Gate
+    def at(g2, q):  # two-qubit gate on (q, q + 1)
+        return gates.KroneckerGate(*([I] * q + [g2] + [I] * (n - q - 2)))
+    layers = [gates.KroneckerGate(*[u3() for _ in range(n)])]
+    kinds = [gates.RXXGate, gates.RYYGate, gates.RZZGate]
+    for q in range(n - 1):
+        for k, cls in enumerate(kinds):
+            layers.append(at(cls(), q))
+            if (q + k) % 2 == 0:
+                layers.append(gates.KroneckerGate(*[gates.XZXZGate() if i == (q + k) % n else I for i in range(n)]))
+        layers.append(at(gates.CNOTGate(), q))
+    full = gates.ProductGate(*layers)
+    short = gates.ProductGate(layers[0], at(gates.RYYGate(), n - 2), at(gates.RZZGate(), 0), at(gates.RXXGate(), 0))
+    return [full, short]
+
+
+def check_two_qubit_rotations(lib, n, tol=TOL):
+    from qsearch_b200 import unitaries
+    rng = np.random.default_rng(40 + n)
+    circuits = two_qubit_rotation_circuits(n)
+    xs = [rng.random((2, c.num_inputs)) * 2 * np.pi for c in circuits]
+    xs[1][1, :] = 0.0
+    return check_against_oracle(lib, circuits, xs, unitaries.qft(1 << n), tol)

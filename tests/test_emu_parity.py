@@ -265,3 +265,26 @@ def test_batch_stop_rules():
     assert (status2 == 7).sum() + (status2 == 6).sum() > 0 and iters2.sum() < iters.sum()
     for k in range(K):  # whatever stopped an instance, the reported distance is the distance at the returned parameters
         assert abs(O.matrix_distance_squared(T, O.matrix(c, x2.reshape(K, -1)[k])) - f2[k]) < 1e-12
+
+
+def test_two_qubit_rotations_against_oracle():
+    """the native backend's RXX / RYY / RZZ leaves through every run kind of the interpreter."""
+    lib = emulated_library()
+    assert _parity.check_two_qubit_rotations(lib, 2) == 4
+    assert _parity.check_two_qubit_rotations(lib, 3) == 4
+
+
+def test_solvers_on_a_circuit_with_two_qubit_rotations():
+    from oracle import qs_oracle as O
+    from qsearch_b200 import lowering
+    lib = emulated_library()
+    c = _parity.two_qubit_rotation_circuits(2)[0]
+    rng = np.random.default_rng(3)
+    T = O.matrix(c, rng.random(c.num_inputs) * 2 * np.pi)
+    gp = lowering.lower(c)
+    x0 = rng.random((4, gp.n_params)) * 2 * np.pi
+    for method in ("lm", "lbfgs"):
+        x, f, iters, status = lib.solve(method, [gp], np.zeros(4, dtype="int32"), x0, T)
+        assert f.min() < 1e-10, (method, f)
+        k = int(np.argmin(f))
+        assert abs(O.matrix_distance_squared(T, O.matrix(c, x.reshape(4, -1)[k])) - f[k]) < 1e-12

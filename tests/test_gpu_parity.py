@@ -319,3 +319,22 @@ def test_batch_stop_rules(lib):
     off = np.concatenate([[0], np.cumsum([gps[i].n_params for i in poi])])
     for k in range(0, len(poi), 7):
         assert abs(O.matrix_distance_squared(T, O.matrix(children[poi[k]], x2[off[k]:off[k + 1]])) - f2[k]) < 1e-12
+
+
+@pytest.mark.parametrize("n", [2, 3, 4, 5])
+def test_two_qubit_rotations_against_oracle(lib, n):
+    """RXX / RYY / RZZ (qsrs/src/circuits.rs:457-633) on the device: every run kind against the oracle, 1e-12."""
+    assert _parity.check_two_qubit_rotations(lib, n) == 4
+
+
+def test_solvers_on_a_circuit_with_two_qubit_rotations(lib):
+    c = _parity.two_qubit_rotation_circuits(3)[0]
+    rng = np.random.default_rng(3)
+    T = O.matrix(c, rng.random(c.num_inputs) * 2 * np.pi)
+    gp = lowering.lower(c)
+    x0 = rng.random((16, gp.n_params)) * 2 * np.pi
+    for method in ("lm", "lbfgs"):
+        x, f, iters, status = lib.solve(method, [gp], np.zeros(16, dtype="int32"), x0, T)
+        assert f.min() < 1e-10, (method, f)
+        k = int(np.argmin(f))
+        assert abs(O.matrix_distance_squared(T, O.matrix(c, x.reshape(16, -1)[k])) - f[k]) < 1e-12

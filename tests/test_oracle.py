@@ -91,3 +91,23 @@ def test_aposmm_start_selection_matches_the_reference():
     z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "aposmm.npz"))
     for k in range(int(z["n_cases"])):
         assert np.array_equal(aposmm_start_indices(z["x_%d" % k], z["f_%d" % k]), z["start_%d" % k]), k
+
+
+def test_two_qubit_rotations_known_answers():
+    """RXX / RYY / RZZ exist only in the reference's Rust backend (qsrs/src/circuits.rs:457-633), which cannot be built here,
+    so the oracle's restatement is pinned by known answers instead of reference-generated fixtures: exp(-i x/2 P(x)P) by
+    scipy's matrix exponential, and the derivative by central differences."""
+    import scipy.linalg
+    from oracle import qs_oracle as O
+    from qsearch_b200 import gates
+    paulis = {"RXXGate": np.array([[0, 1], [1, 0]]), "RYYGate": np.array([[0, -1j], [1j, 0]]), "RZZGate": np.diag([1.0, -1.0])}
+    for name, Pm in paulis.items():
+        g = getattr(gates, name)()
+        PP = np.kron(Pm, Pm)
+        for x in (0.0, 0.3, 2.1, 5.9):
+            U, J = O.mat_jac(g, [x])
+            assert np.abs(U - scipy.linalg.expm(-0.5j * x * PP)).max() < 1e-14
+            assert np.abs(O.matrix(g, [x]) - U).max() == 0
+            fd = (O.matrix(g, [x + 1e-6]) - O.matrix(g, [x - 1e-6])) / 2e-6
+            assert len(J) == 1 and np.abs(J[0] - fd).max() < 1e-9
+            assert np.abs(J[0] - (-0.5j) * PP @ U).max() < 1e-14
