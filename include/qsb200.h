@@ -194,6 +194,9 @@ int qsb_eval_lm_system_static(qsb_ctx* ctx, int device_slot, const qsb_program* 
 
 /* ---- device micro-benchmarks (FP64 pipe / DMMA peak measured on the box; bench.py records them) ---------- */
 int qsb_measure_fp64_peak(qsb_ctx* ctx, int device_slot, int use_dmma, double* out_tflops);
+/* store-only HBM bandwidth in GB/s over a 4 GiB buffer (mode 0: 16-byte coalesced stores from a kernel; 1: cudaMemsetAsync):
+ * the roof of a kernel that, like the LM-form evaluation, writes its output and reads almost nothing */
+int qsb_measure_hbm_write(qsb_ctx* ctx, int device_slot, int mode, double* out_gbs);
 
 #ifdef __cplusplus
 }

@@ -94,6 +94,7 @@ class Library:
         d.qsb_solve_lm.argtypes = solve
         d.qsb_solve_lbfgs.argtypes = solve
         d.qsb_measure_fp64_peak.argtypes = [_vp, ctypes.c_int, ctypes.c_int, _c_dp]
+        d.qsb_measure_hbm_write.argtypes = [_vp, ctypes.c_int, ctypes.c_int, _c_dp]
         d.qsb_eval_lm_system_static.argtypes = [_vp, ctypes.c_int, _vp, ctypes.c_int, _c_dp, _c_dp, _c_dp, _c_dp, _c_dp]
 
     def check(self, rc):
@@ -291,6 +292,11 @@ class Library:
         finally:
             self._release(keys)
         return rr, g, A
+
+    def measure_hbm_write(self, slot=0, mode=0):
+        out = ctypes.c_double()
+        self.check(self.dll.qsb_measure_hbm_write(self.ctx, slot, int(mode), ctypes.byref(out)))
+        return out.value
 
     def measure_fp64_peak(self, slot=0, use_dmma=False):
         out = ctypes.c_double()

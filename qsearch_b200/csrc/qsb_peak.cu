@@ -67,3 +67,73 @@ extern "C" int qsb_measure_fp64_peak(qsb_ctx* ctx, int slot, int use_dmma, doubl
   *out_tflops = best;
   return QSB_OK;
 }
+
+// ---------------------------------------------------------------------------- write-only HBM bandwidth
+// The LM-form kernel only WRITES to HBM (258 KB of r and J_r per instance against 0.5 KB read), while the copy figure in
+// MEASURED_PEAKS.json is half reads, half writes.  These two streams measure what a store-only stream reaches on the box:
+// mode 0: 16-byte stores, fully coalesced, grid-stride (a kernel like the product's own epilogue); mode 1: cudaMemsetAsync.
+QSB_GLOBAL qsb_k_store_stream(double2* out, size_t n16, double v) {
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += stride) out[i] = make_double2(v, v + (double)i);
+}
+
+// mode 2: the store pattern of the LM-form epilogue at n = 4 (qsb_jac_param, RESID): a warp owns a 16 x 16 tile of doubles
+// (2 KB, rows of 128 B); lane (g, t) holds columns {2t, 2t+1} of two 8-wide column tiles, so one store instruction writes
+// eight 64-byte half rows and the other halves follow in the next instruction.  mode 3: the same bytes staged through shared
+// memory and written as 512 contiguous bytes per instruction.
+QSB_GLOBAL qsb_k_store_tiles(double* out, size_t n_tiles, double v, int staged) {
+#ifndef QSB_EMU
+  __shared__ __align__(16) double stage[8][256];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, t = lane & 3;
+  const size_t wstride = (size_t)gridDim.x * (blockDim.x >> 5);
+  for (size_t tile = (size_t)blockIdx.x * (blockDim.x >> 5) + warp; tile < n_tiles; tile += wstride) {
+    double* o = out + tile * 256;
+    if (!staged) {
+#pragma unroll
+      for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+        for (int nt = 0; nt < 2; ++nt)
+          *reinterpret_cast<double2*>(o + (8 * mt + g) * 16 + 8 * nt + 2 * t) = make_double2(v + mt, v + nt);
+    } else {
+#pragma unroll
+      for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+        for (int nt = 0; nt < 2; ++nt)
+          *reinterpret_cast<double2*>(&stage[warp][(8 * mt + g) * 16 + 8 * nt + 2 * t]) = make_double2(v + mt, v + nt);
+      __syncwarp();
+#pragma unroll
+      for (int i = 0; i < 4; ++i) *reinterpret_cast<double2*>(o + 64 * i + 2 * lane) = *reinterpret_cast<const double2*>(&stage[warp][64 * i + 2 * lane]);
+      __syncwarp();
+    }
+  }
+#endif
+}
+
+extern "C" int qsb_measure_hbm_write(qsb_ctx* ctx, int slot, int mode, double* out_gbs) {
+  if (!ctx || !out_gbs || slot < 0 || slot >= (int)ctx->devs.size()) return qsb_fail(QSB_ERR_INVALID, "bad argument");
+  const QsbDevice& d = ctx->devs[slot];
+  QSB_CUDA(cudaSetDevice(d.id));
+#ifdef QSB_EMU
+  const size_t bytes = (size_t)1 << 20;
+#else
+  const size_t bytes = (size_t)4 << 30;  // 4 GiB >> 126 MB of L2
+#endif
+  double2* buf = nullptr;
+  QSB_CUDA(cudaMalloc((void**)&buf, bytes));
+  double best = 0;
+  for (int rep = 0; rep < 5; ++rep) {
+    QSB_CUDA(cudaEventRecord(d.ev0, d.stream));
+    if (mode == 1) QSB_CUDA(cudaMemsetAsync(buf, rep, bytes, d.stream));
+    else if (mode >= 2) QSB_LAUNCH(qsb_k_store_tiles, d.sm_count * 8, 256, 0, d.stream, (double*)buf, bytes / 2048, (double)rep, mode == 3 ? 1 : 0);
+    else QSB_LAUNCH(qsb_k_store_stream, d.sm_count * 16, 256, 0, d.stream, buf, bytes / 16, (double)rep);
+    QSB_CUDA(cudaEventRecord(d.ev1, d.stream));
+    QSB_CUDA(cudaEventSynchronize(d.ev1));
+    float ms = 0;
+    QSB_CUDA(cudaEventElapsedTime(&ms, d.ev0, d.ev1));
+    QSB_CUDA(cudaGetLastError());
+    if (rep >= 1) best = std::max(best, (double)bytes / (ms * 1e-3) / 1e9);
+  }
+  cudaFree(buf);
+  *out_gbs = best;
+  return QSB_OK;
+}
