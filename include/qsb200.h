@@ -160,7 +160,8 @@ typedef struct qsb_solver_opts {
   double sibling_stop;        /* > 0: stop an instance once another instance of the SAME program finished with a distance
                                  below this value (out_status 7): the other starts of a solved child are not needed */
   double straggler_min_iters; /* the straggler rule never fires before this many evaluations (<= 0: 32) */
-  double reserved;
+  double gram_tf32;           /* > 0 (body-frame LM kernel only): form J_r'J_r, which only steers the optimiser, from TF32-rounded rows on
+                                 the TF32 tensor path; J_r'r, the objective and every returned value stay fp64.  0: everything fp64 */
 } qsb_solver_opts;
 
 /* One independent solve per instance, parameters stay on the device for the whole solve.

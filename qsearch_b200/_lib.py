@@ -31,7 +31,7 @@ class SolverOpts(ctypes.Structure):
     _fields_ = [("max_iters", ctypes.c_int32), ("lbfgs_memory", ctypes.c_int32), ("ftol", ctypes.c_double),
                 ("xtol", ctypes.c_double), ("gtol", ctypes.c_double), ("stop_value", ctypes.c_double),
                 ("straggler_factor", ctypes.c_double), ("sibling_stop", ctypes.c_double),
-                ("straggler_min_iters", ctypes.c_double), ("reserved", ctypes.c_double)]
+                ("straggler_min_iters", ctypes.c_double), ("gram_tf32", ctypes.c_double)]
 
 
 def _dp(a):
@@ -262,12 +262,13 @@ class Library:
 
     # ------------------------------------------------------------------ solvers
     def solve(self, method, gps, prog_of_instance, x0, target, max_iters=0, ftol=0.0, xtol=0.0, gtol=0.0,
-              stop_value=0.0, lbfgs_memory=10, straggler_factor=0.0, sibling_stop=0.0, straggler_min_iters=0.0):
+              stop_value=0.0, lbfgs_memory=10, straggler_factor=0.0, sibling_stop=0.0, straggler_min_iters=0.0,
+              gram_tf32=0.0):
         with self._pack(gps, prog_of_instance, x0) as (handles, poi, x0, sizes):
             T = np.ascontiguousarray(target, dtype="complex128")
             opts = SolverOpts(max_iters=max_iters, lbfgs_memory=lbfgs_memory, ftol=ftol, xtol=xtol, gtol=gtol,
                               stop_value=stop_value, straggler_factor=straggler_factor, sibling_stop=sibling_stop,
-                              straggler_min_iters=straggler_min_iters)
+                              straggler_min_iters=straggler_min_iters, gram_tf32=gram_tf32)
             x = np.empty_like(x0)
             f = np.empty(len(poi), dtype="float64")
             iters = np.empty(len(poi), dtype="int32")

@@ -29,6 +29,7 @@ UNITS = [
     ("solve_lm", "qsb_solve.cu", ["-DQSB_SOLVE_TU=0"]),
     ("solve_lbfgs", "qsb_solve.cu", ["-DQSB_SOLVE_TU=1"]),
     ("solve_lm5", "qsb_solve.cu", ["-DQSB_SOLVE_TU=2"]),
+    ("solve_lm5t", "qsb_solve.cu", ["-DQSB_SOLVE_TU=3"]),
     ("peak", "qsb_peak.cu", []),
     ("noalloc", "qsb_noalloc.cu", []),
 ]

@@ -223,6 +223,126 @@ QSB_DEVICE void qsb_syrk_packed(const double* R, int rows, int K2, double* A, in
   qsb_syrk_packed_t<2>(R, rows, K2, A, warp, nwarps, lane, qsb_syrk_ksplit3(rows, nwarps));
 }
 
+// ---------------------------------------------------------------------------- Gram product on the TF32 tensor path
+// J_r^T J_r only steers the optimiser (it is the Gauss-Newton model of the Hessian); the gradient J_r^T r, the objective and
+// everything the solver returns stay fp64.  With the rows rounded to TF32 (10-bit mantissa) and fp32 accumulation the LM
+// iteration counts and end points are unchanged within their seed-to-seed noise (NumPy model of this kernel's update rules on
+// reachable and unreachable 3- and 4-qubit problems: 17-30 vs 17-30 iterations, 244-532 vs 281-528; BF16 rows double the
+// count on reachable targets and are not used), while mma.sync.m16n8k8.tf32 runs several times faster than the FP64 DMMA
+// that dominates an iteration at n = 5.  Opt-in (qsb_solver_opts.gram_tf32); the search front-end turns it on.
+#ifdef QSB_EMU
+static inline float qsb_to_tf32(double x) {
+  float f = (float)x;
+  uint32_t u; std::memcpy(&u, &f, 4);
+  u = (u + 0x1000u) & 0xFFFFE000u;
+  std::memcpy(&f, &u, 4);
+  return f;
+}
+// emulated mma.sync.m16n8k8.tf32: c[16x8] += a[16x8] b[8x8]; fragments as in the PTX ISA (g = lane >> 2, t = lane & 3):
+// a0 (g, t) a1 (g+8, t) a2 (g, t+4) a3 (g+8, t+4);  b0 (k = t, n = g) b1 (k = t+4, n = g);  c0 (g, 2t) c1 (g, 2t+1) c2 (g+8, 2t) c3 (g+8, 2t+1)
+static inline void qsb_mma_tf32(float (&c)[4], float a0, float a1, float a2, float a3, float b0, float b1) {
+  auto* st = qsb_emu::cur();
+  const int w = threadIdx.x / 32, l = threadIdx.x % 32, g = l >> 2, t = l & 3;
+  auto pack = [](float x, float y) { uint64_t r; float v[2] = {x, y}; std::memcpy(&r, v, 8); return r; };
+  auto unpack = [](uint64_t r, int i) { float v[2]; std::memcpy(v, &r, 8); return v[i]; };
+  st->warp_buf[w][l] = pack(a0, a1); st->warp_buf2[w][l] = pack(a2, a3);
+  __syncwarp();
+  float A0[8], A1[8];  // rows g and g + 8 of a
+  for (int k = 0; k < 8; ++k) {
+    const uint64_t r = (k < 4) ? st->warp_buf[w][4 * g + k] : st->warp_buf2[w][4 * g + k - 4];
+    A0[k] = unpack(r, 0); A1[k] = unpack(r, 1);
+  }
+  __syncwarp();
+  st->warp_buf[w][l] = pack(b0, b1);
+  __syncwarp();
+  for (int j = 0; j < 2; ++j) {
+    const int n = 2 * t + j;
+    float s0 = c[j], s1 = c[2 + j];
+    for (int k = 0; k < 8; ++k) {
+      const float b = unpack(st->warp_buf[w][4 * n + (k & 3)], k >> 2);
+      s0 = std::fma(A0[k], b, s0); s1 = std::fma(A1[k], b, s1);
+    }
+    c[j] = s0; c[2 + j] = s1;
+  }
+  __syncwarp();
+}
+#else
+__device__ __forceinline__ float qsb_to_tf32(double x) {
+  uint32_t u;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"((float)x));
+  return __uint_as_float(u);
+}
+__device__ __forceinline__ void qsb_mma_tf32(float (&c)[4], float a0, float a1, float a2, float a3, float b0, float b1) {
+  asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};\n"
+               : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+               : "r"(__float_as_uint(a0)), "r"(__float_as_uint(a1)), "r"(__float_as_uint(a2)), "r"(__float_as_uint(a3)),
+                 "r"(__float_as_uint(b0)), "r"(__float_as_uint(b1)));
+}
+#endif
+
+// A[TRI(k, l)] = sum_m R[k][m] R[l][m], l <= k < rows, R = TF32-rounded floats [rows][K2] (K2 a multiple of 16), result fp64
+// packed.  One warp per 32 x 32 block of the lower triangle.  The contraction order is free as long as both operands agree:
+// lane t takes 4 consecutive columns of a 16-column chunk as one 16-byte load and feeds them to two MMAs.
+QSB_DEVICE void qsb_gram_tf32(const float* R, int rows, int K2, double* A, int warp, int nwarps, int lane) {
+  const int g = lane >> 2, t = lane & 3;
+  const int nb = (rows + 31) / 32, ntasks = nb * (nb + 1) / 2;
+  for (int task = warp; task < ntasks; task += nwarps) {
+    int bk = (int)((sqrt(8.0 * task + 1.0) - 1.0) * 0.5);
+    while ((bk + 1) * (bk + 2) / 2 <= task) ++bk;
+    while (bk * (bk + 1) / 2 > task) --bk;
+    const int bl = task - bk * (bk + 1) / 2;
+    const float* pa[2][2];
+    const float* pb[4];
+#pragma unroll
+    for (int i = 0; i < 2; ++i)
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        int r = 32 * bk + 16 * i + 8 * h + g;
+        if (r > rows - 1) r = rows - 1;
+        pa[i][h] = R + (size_t)r * K2 + 4 * t;
+      }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      int r = 32 * bl + 8 * j + g;
+      if (r > rows - 1) r = rows - 1;
+      pb[j] = R + (size_t)r * K2 + 4 * t;
+    }
+    float acc[2][4][4];
+#pragma unroll
+    for (int i = 0; i < 2; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+#pragma unroll
+        for (int e = 0; e < 4; ++e) acc[i][j][e] = 0.f;
+#pragma unroll 2
+    for (int m0 = 0; m0 < K2; m0 += 16) {
+      float4 av[2][2], bv[4];
+#pragma unroll
+      for (int i = 0; i < 2; ++i)
+#pragma unroll
+        for (int h = 0; h < 2; ++h) av[i][h] = *reinterpret_cast<const float4*>(pa[i][h] + m0);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) bv[j] = *reinterpret_cast<const float4*>(pb[j] + m0);
+#pragma unroll
+      for (int i = 0; i < 2; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          qsb_mma_tf32(acc[i][j], av[i][0].x, av[i][1].x, av[i][0].y, av[i][1].y, bv[j].x, bv[j].y);
+          qsb_mma_tf32(acc[i][j], av[i][0].z, av[i][1].z, av[i][0].w, av[i][1].w, bv[j].z, bv[j].w);
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < 2; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const int k = 32 * bk + 16 * i + 8 * (e >> 1) + g, l = 32 * bl + 8 * j + 2 * t + (e & 1);
+          if (k < rows && l <= k) A[QSB_TRI(k, l)] = (double)acc[i][j][e];
+        }
+  }
+}
+
 // ---------------------------------------------------------------------------- factorisation
 // Same augmented, packed, right-looking Cholesky as qsb_chol_packed (qsb_lm2.cuh): B = [A + mu diag(d2), g ; g^T, .],
 // rows = P + 1, row P ends up as y with L y = g.  What changed, phase by phase (cycles at P = 62, profiles/r2):
@@ -466,8 +586,9 @@ QSB_DEVICE void qsb_ch4_back(const double* Ls, int P, const double* Winv, double
 // One parameter whose qubit sits at k-step bit KB: packed Q = gamma I + Y^dagger Y, Y = (w^T (x) I) X, into `row`
 // (K2 doubles).  Layout of a row: TT diagonal tiles (Z = Re + Im, 64 doubles each, C-fragment order: lane-major pairs),
 // then the NOFF tiles (mt > nt, index mt (mt - 1) / 2 + nt): sqrt(2) Re (64 doubles), sqrt(2) Im (64 doubles).
-template <int NQ, int KB>
-QSB_DEVICE void qsb_q_param(const QsbFrag<(1 << NQ) / 4, (1 << NQ) / 8>& X, const cplx* slot, double* row, int lane) {
+template <int NQ, int KB, bool TF32 = false>
+QSB_DEVICE void qsb_q_param(const QsbFrag<(1 << NQ) / 4, (1 << NQ) / 8>& X, const cplx* slot, double* row, int lane,
+                            float* row32 = nullptr, const double* crow = nullptr, double* gk = nullptr) {
   using G = QsbQGeom<NQ>;
   constexpr int KS = G::KS, TT = G::TT, NOFF = G::NOFF, NO1 = NOFF > 0 ? NOFF : 1;
   const int g = lane >> 2, t = lane & 3;
@@ -515,6 +636,31 @@ QSB_DEVICE void qsb_q_param(const QsbFrag<(1 << NQ) / 4, (1 << NQ) / 8>& X, cons
     }
   }
   const double r2 = 1.4142135623730951;
+  if (TF32) {
+    // TF32 Gram mode: the row is stored as TF32-rounded floats (same packed order) and its inner product with the -C row,
+    // g_k = (J_r^T r)[k], is taken here from the fp64 accumulators: the gradient never sees the reduced precision
+    double dot = 0.0;
+#pragma unroll
+    for (int tt = 0; tt < TT; ++tt) {
+      const double2 c = *reinterpret_cast<const double2*>(crow + tt * 64 + 2 * lane);
+      dot = fma(zd[tt][0], c.x, fma(zd[tt][1], c.y, dot));
+      *reinterpret_cast<float2*>(row32 + tt * 64 + 2 * lane) = make_float2(qsb_to_tf32(zd[tt][0]), qsb_to_tf32(zd[tt][1]));
+    }
+    if (NOFF > 0) {
+#pragma unroll
+      for (int o = 0; o < NOFF; ++o) {
+        const int off = TT * 64 + o * 128 + 2 * lane;
+        const double2 c0 = *reinterpret_cast<const double2*>(crow + off), c1 = *reinterpret_cast<const double2*>(crow + off + 64);
+        const double a0 = r2 * hr[o][0], a1 = r2 * hr[o][1], b0 = r2 * hi[o][0], b1 = r2 * hi[o][1];
+        dot = fma(a0, c0.x, fma(a1, c0.y, fma(b0, c1.x, fma(b1, c1.y, dot))));
+        *reinterpret_cast<float2*>(row32 + off) = make_float2(qsb_to_tf32(a0), qsb_to_tf32(a1));
+        *reinterpret_cast<float2*>(row32 + off + 64) = make_float2(qsb_to_tf32(b0), qsb_to_tf32(b1));
+      }
+    }
+    for (int m = 16; m > 0; m >>= 1) dot += __shfl_xor_sync(QSB_FULL, dot, m);
+    if (lane == 0) *gk = dot;
+    return;
+  }
 #pragma unroll
   for (int tt = 0; tt < TT; ++tt) *reinterpret_cast<double2*>(row + tt * 64 + 2 * lane) = make_double2(zd[tt][0], zd[tt][1]);
   if (NOFF > 0) {
@@ -665,12 +811,18 @@ QSB_DEVICE double qsb_cta_eval_rows(const QsbDevProgram& P, const double* x, con
 // SAME parameter vector (gtab = its body-frame table).  The ops that have parameters are dealt round-robin to the warps;
 // a warp loads the snapshot in front of its op as a DMMA B fragment with the op's qubit mapped to k-step bit 0 (the rows
 // come from memory, so any row order is free), which leaves ONE code path for every qubit.  Ends with a block barrier.
-template <int NQ>
-QSB_DEVICE void qsb_cta_qrows_snap(const QsbDevProgram& P, const cplx* gtab, const double* snap, const cplx* vsm, double* slab) {
+template <int NQ, bool TF32 = false>
+QSB_DEVICE void qsb_cta_qrows_snap(const QsbDevProgram& P, const cplx* gtab, const double* snap, const cplx* vsm, double* slab,
+                                   double* gvec = nullptr) {
   using G = QsbQGeom<NQ>;
   constexpr int N = G::N, KS = G::KS, TT = G::TT, K2 = G::K2;
   const int lane = threadIdx.x & 31, warp = qsb_warp_index(), nwarps = blockDim.x >> 5;
   const int g = lane >> 2, t = lane & 3;
+  // TF32 mode: rows are floats in the first half of the fp64 slab's bytes (row k at slab32 + k K2); the -C row keeps its fp64
+  // place (row P of the fp64 layout, beyond the float rows) and is needed by every row's gradient entry, so it comes first
+  double* crow = slab + (size_t)P.n_params * K2;
+  float* slab32 = reinterpret_cast<float*>(slab);
+  if (TF32) { qsb_q_crow<NQ>(vsm, crow); __syncthreads(); }
   int pidx = 0;
   for (int j = 0; j < P.n_ops; ++j) {
     const qsb_op op = P.ops[j];
@@ -690,16 +842,19 @@ QSB_DEVICE void qsb_cta_qrows_snap(const QsbDevProgram& P, const cplx* gtab, con
           X.re[ks][o] = v.x; X.im[ks][o] = v.y;
         }
       }
-      for (int k = 0; k < np; ++k)
-        qsb_q_param<NQ, 1>(X, gtab + 4 * (op.reserved + 1 + k), slab + (size_t)(op.param_off + k) * K2, lane);
+      for (int k = 0; k < np; ++k) {
+        const int pk = op.param_off + k;
+        if (TF32) qsb_q_param<NQ, 1, true>(X, gtab + 4 * (op.reserved + 1 + k), nullptr, lane, slab32 + (size_t)pk * K2, crow, gvec + pk);
+        else qsb_q_param<NQ, 1, false>(X, gtab + 4 * (op.reserved + 1 + k), slab + (size_t)pk * K2, lane);
+      }
     }
     ++pidx;
   }
-  qsb_q_crow<NQ>(vsm, slab + (size_t)P.n_params * K2);
+  if (!TF32) qsb_q_crow<NQ>(vsm, crow);
   __syncthreads();
 }
 
-template <int NQ>
+template <int NQ, bool TF32>
 QSB_GLOBAL __launch_bounds__(QsbQGeom<NQ>::WARPS * 32) qsb_k_lm3(QsbSolveArgs a) {
   using G = QsbQGeom<NQ>;
   constexpr int N = G::N, K2 = G::K2, NW = G::WARPS;
@@ -741,6 +896,7 @@ QSB_GLOBAL __launch_bounds__(QsbQGeom<NQ>::WARPS * 32) qsb_k_lm3(QsbSolveArgs a)
     for (int e = threadIdx.x; e < prog.n_ops * 6; e += blockDim.x) ((int32_t*)sops)[e] = ((const int32_t*)prog.ops)[e];
     prog.ops = sops;  // every sweep of this solve reads the ops from shared memory
     const bool kzero = qsb_syrk_ksplit3(rows, NW) == 2;
+    constexpr bool tf32 = TF32;
     const double* x0 = a.x0 + a.param_off[inst];
     const int max_iters = a.max_iters > 0 ? a.max_iters : 100 * (P > 0 ? P : 1);
     for (int k = threadIdx.x; k < P; k += blockDim.x) x[k] = x0[k];
@@ -748,12 +904,18 @@ QSB_GLOBAL __launch_bounds__(QsbQGeom<NQ>::WARPS * 32) qsb_k_lm3(QsbSolveArgs a)
     cplx tr;
     double F = qsb_cta_eval_rows<NQ>(prog, x, a.target, trig, gtab, part, snap, vsm, &tr);  // tables, snapshots and V of x
     if (P > 0) {
-      { QSB_PROF_BEGIN(); qsb_cta_qrows_snap<NQ>(prog, gtab, snap, vsm, Rg); QSB_PROF_END(0); }
+      { QSB_PROF_BEGIN(); qsb_cta_qrows_snap<NQ, TF32>(prog, gtab, snap, vsm, Rg, g); QSB_PROF_END(0); }
       iters = 1;
       {
         QSB_PROF_BEGIN();
-        if (kzero) { for (int e = threadIdx.x; e < rows * (rows + 1) / 2; e += blockDim.x) A[e] = 0.0; __syncthreads(); }
-        qsb_syrk_packed(Rg, rows, K2, A, warp, NW, lane);
+        if (tf32) {  // Gram of the P parameter rows on the TF32 path; the augmented row (g, r^T r) is fp64 and already known
+          qsb_gram_tf32(reinterpret_cast<const float*>(Rg), P, K2, A, warp, NW, lane);
+          for (int k = threadIdx.x; k < P; k += blockDim.x) A[QSB_TRI(P, k)] = g[k];
+          if (threadIdx.x == 0) A[QSB_TRI(P, P)] = 2.0 * F;
+        } else {
+          if (kzero) { for (int e = threadIdx.x; e < rows * (rows + 1) / 2; e += blockDim.x) A[e] = 0.0; __syncthreads(); }
+          qsb_syrk_packed(Rg, rows, K2, A, warp, NW, lane);
+        }
         __syncthreads();
         QSB_PROF_END(1);
       }
@@ -818,12 +980,18 @@ QSB_GLOBAL __launch_bounds__(QsbQGeom<NQ>::WARPS * 32) qsb_k_lm3(QsbSolveArgs a)
           if (conv_f) { status = 2; break; }
           if (conv_x) { status = 3; break; }
           if (iters >= max_iters) { status = 0; break; }
-          { QSB_PROF_BEGIN(); qsb_cta_qrows_snap<NQ>(prog, gtab, snap, vsm, Rg); QSB_PROF_END(0); }
+          { QSB_PROF_BEGIN(); qsb_cta_qrows_snap<NQ, TF32>(prog, gtab, snap, vsm, Rg, g); QSB_PROF_END(0); }
           ++iters;
           {
             QSB_PROF_BEGIN();
-            if (kzero) { for (int e = threadIdx.x; e < rows * (rows + 1) / 2; e += blockDim.x) A[e] = 0.0; __syncthreads(); }
-            qsb_syrk_packed(Rg, rows, K2, A, warp, NW, lane);
+            if (tf32) {
+              qsb_gram_tf32(reinterpret_cast<const float*>(Rg), P, K2, A, warp, NW, lane);
+              for (int k = threadIdx.x; k < P; k += blockDim.x) A[QSB_TRI(P, k)] = g[k];
+              if (threadIdx.x == 0) A[QSB_TRI(P, P)] = 2.0 * F;
+            } else {
+              if (kzero) { for (int e = threadIdx.x; e < rows * (rows + 1) / 2; e += blockDim.x) A[e] = 0.0; __syncthreads(); }
+              qsb_syrk_packed(Rg, rows, K2, A, warp, NW, lane);
+            }
             __syncthreads();
             QSB_PROF_END(1);
           }

@@ -1,8 +1,8 @@
 // Host side of the batched solvers (C ABI: qsb_solve_lm / qsb_solve_lbfgs).  One source, three translation units
 // (build.py compiles them in parallel): QSB_SOLVE_TU = 0: Levenberg-Marquardt, 1..4 qubits + qsb_solve_lm;
-// 1: L-BFGS + qsb_solve_lbfgs; 2: Levenberg-Marquardt, 5 qubits.
+// 1: L-BFGS + qsb_solve_lbfgs; 2: Levenberg-Marquardt, 5 qubits; 3: the same with the TF32 Gram product (qsb_k_lm3<5, true>).
 #ifndef QSB_SOLVE_TU
-#error "compile with -DQSB_SOLVE_TU=0|1|2"
+#error "compile with -DQSB_SOLVE_TU=0|1|2|3"
 #endif
 #include <algorithm>
 #include <cstdio>
@@ -25,7 +25,9 @@
 
 #if QSB_SOLVE_TU != 1
 // ---------------------------------------------------------------------------- Levenberg-Marquardt launches
-template <int NQ>
+// TF32: the body-frame kernel with the TF32 Gram product (qsb_solver_opts.gram_tf32); a separate instantiation, so that
+// neither variant pays registers for the other's code
+template <int NQ, bool TF32 = false>
 static int launch_solver_nq(const SolveJob& job, qsb_batch* b, QsbSolveArgs& args, const QsbDevice& d) {
   const size_t NN = (size_t)1 << (2 * NQ);
   const size_t maxP = (size_t)b->max_params;
@@ -83,8 +85,8 @@ static int launch_solver_nq(const SolveJob& job, qsb_batch* b, QsbSolveArgs& arg
   int ctas;
   if (body_lm) {
     if constexpr (NQ >= 3) {
-      if ((rc = qsb_prepare_kernel(qsb_k_lm3<NQ>, smem))) return rc;
-      ctas = qsb_resident_ctas(qsb_k_lm3<NQ>, threads, smem);
+      if ((rc = qsb_prepare_kernel(qsb_k_lm3<NQ, TF32>, smem))) return rc;
+      ctas = qsb_resident_ctas(qsb_k_lm3<NQ, TF32>, threads, smem);
     } else ctas = 1;
   } else if (tensor_lm) {
     if constexpr (NQ >= 3) {
@@ -104,7 +106,7 @@ static int launch_solver_nq(const SolveJob& job, qsb_batch* b, QsbSolveArgs& arg
   args.scratch = (double*)scratch.p;
   args.scratch_per_cta = per_cta;
   if (body_lm) {
-    if constexpr (NQ >= 3) QSB_LAUNCH((qsb_k_lm3<NQ>), grid, threads, smem, d.stream, args);
+    if constexpr (NQ >= 3) QSB_LAUNCH((qsb_k_lm3<NQ, TF32>), grid, threads, smem, d.stream, args);
   } else if (tensor_lm) {
     if constexpr (NQ >= 3) {
 #ifdef QSB_EMU
@@ -173,7 +175,11 @@ static int launch_solver_nq(const SolveJob& job, qsb_batch* b, QsbSolveArgs& arg
 
 #if QSB_SOLVE_TU == 2
 int qsb_launch_solver_lm5(const SolveJob& job, qsb_batch* b, QsbSolveArgs& args, const QsbDevice& d) {
-  return launch_solver_nq<5>(job, b, args, d);
+  return launch_solver_nq<5, false>(job, b, args, d);
+}
+#elif QSB_SOLVE_TU == 3
+int qsb_launch_solver_lm5t(const SolveJob& job, qsb_batch* b, QsbSolveArgs& args, const QsbDevice& d) {
+  return launch_solver_nq<5, true>(job, b, args, d);
 }
 #else
 static int solve_shard(const SolveJob& job, int slot, int i0, int i1, const std::vector<long long>& poff) {
@@ -204,6 +210,7 @@ static int solve_shard(const SolveJob& job, int slot, int i0, int i1, const std:
   args.out_x = (double*)b->out_a.p; args.out_f = args.out_x + np;
   args.out_iters = (int32_t*)b->out_b.p; args.out_status = args.out_iters + n;
   args.ctl = (int*)(args.out_status + n + 2);
+  args.gram_tf32 = job.opts.gram_tf32 > 0 ? 1 : 0;
   args.straggler_c = job.opts.straggler_factor;
   args.sibling_f = job.opts.sibling_stop;
   args.straggler_min = job.opts.straggler_min_iters > 0 ? (int)job.opts.straggler_min_iters : 32;
@@ -220,11 +227,13 @@ static int solve_shard(const SolveJob& job, int slot, int i0, int i1, const std:
   switch (b->n_qubits) {
     case 1: rc = launch_solver_nq<1>(job, b, args, d); break;
     case 2: rc = launch_solver_nq<2>(job, b, args, d); break;
+#if QSB_SOLVE_TU == 0
+    case 3: rc = args.gram_tf32 ? launch_solver_nq<3, true>(job, b, args, d) : launch_solver_nq<3, false>(job, b, args, d); break;
+    case 4: rc = args.gram_tf32 ? launch_solver_nq<4, true>(job, b, args, d) : launch_solver_nq<4, false>(job, b, args, d); break;
+    case 5: rc = args.gram_tf32 ? qsb_launch_solver_lm5t(job, b, args, d) : qsb_launch_solver_lm5(job, b, args, d); break;
+#else
     case 3: rc = launch_solver_nq<3>(job, b, args, d); break;
     case 4: rc = launch_solver_nq<4>(job, b, args, d); break;
-#if QSB_SOLVE_TU == 0
-    case 5: rc = qsb_launch_solver_lm5(job, b, args, d); break;
-#else
     case 5: rc = launch_solver_nq<5>(job, b, args, d); break;
 #endif
     default: rc = qsb_fail(QSB_ERR_UNSUPPORTED, "unsupported qubit count");
@@ -312,4 +321,4 @@ extern "C" int qsb_solve_lbfgs(qsb_ctx* ctx, int n_programs, const qsb_program* 
   return solve_dispatch(j);
 }
 #endif
-#endif  // QSB_SOLVE_TU != 2
+#endif  // QSB_SOLVE_TU < 2

@@ -17,3 +17,4 @@ struct SolveJob {
 
 // Levenberg-Marquardt on 5 qubits lives in its own translation unit (compile time)
 int qsb_launch_solver_lm5(const SolveJob& job, qsb_batch* b, QsbSolveArgs& args, const QsbDevice& d);
+int qsb_launch_solver_lm5t(const SolveJob& job, qsb_batch* b, QsbSolveArgs& args, const QsbDevice& d);  // TF32 Gram product

@@ -43,6 +43,7 @@ struct QsbSolveArgs {
                         // exceeds straggler_c x the largest count among that first half (status 6)
   int straggler_min;    // ... but never before this many evaluations
   double sibling_f;     // > 0: stop an instance once another instance of the same program finished below this distance (status 7)
+  int gram_tf32;        // qsb_k_lm3: J_r^T J_r from TF32-rounded rows on the mma.sync TF32 path (the gradient and the objective stay fp64)
 };
 
 QSB_DEVICE double qsb_block_max(double v, cplx* red) {

@@ -137,11 +137,14 @@ class LeastSquares_Jac_Solver(Solver):
     # half of the batch that finished first, or once another start of its circuit reached options.threshold
     FRONTIER_STRAGGLER = 2.0
 
-    def __init__(self, starts=1, max_iters=0, straggler_factor=None, sibling_stop=None):
+    def __init__(self, starts=1, max_iters=0, straggler_factor=None, sibling_stop=None, gram_tf32=None):
         self.starts = int(starts)
         self.max_iters = int(max_iters)
         self.straggler_factor = straggler_factor  # None: off for plain solves, FRONTIER_STRAGGLER for frontier batches
         self.sibling_stop = sibling_stop          # None: off for plain solves, options.threshold for frontier batches
+        # J_r^T J_r (which only steers the optimiser) from TF32-rounded rows on the TF32 tensor path; the gradient, the
+        # objective and all returned values stay fp64.  None: off for plain solves, on for frontier batches
+        self.gram_tf32 = gram_tf32
 
     def _solve_opts(self, options, frontier=False):
         if not _has_residuals(options):
@@ -154,6 +157,7 @@ class LeastSquares_Jac_Solver(Solver):
         sf, ss = self.straggler_factor, self.sibling_stop
         o["straggler_factor"] = float(sf) if sf is not None else (self.FRONTIER_STRAGGLER if frontier else 0.0)
         o["sibling_stop"] = float(ss) if ss is not None else (float(thr) if frontier else 0.0)
+        o["gram_tf32"] = float(bool(self.gram_tf32)) if self.gram_tf32 is not None else (1.0 if frontier else 0.0)
         return o
 
     @property

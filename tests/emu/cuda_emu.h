@@ -31,6 +31,9 @@
 
 struct double2 { double x, y; };
 static inline double2 make_double2(double x, double y) { return double2{x, y}; }
+struct float2 { float x, y; };
+static inline float2 make_float2(float x, float y) { return float2{x, y}; }
+struct alignas(16) float4 { float x, y, z, w; };
 
 namespace qsb_emu {
 struct Fiber {

@@ -288,3 +288,25 @@ def test_solvers_on_a_circuit_with_two_qubit_rotations():
         assert f.min() < 1e-10, (method, f)
         k = int(np.argmin(f))
         assert abs(O.matrix_distance_squared(T, O.matrix(c, x.reshape(4, -1)[k])) - f[k]) < 1e-12
+
+
+@pytest.mark.parametrize("n", [3, 4])
+def test_tf32_gram_option_of_the_lm_kernel(n):
+    """qsb_solver_opts.gram_tf32: only J_r^T J_r comes from TF32-rounded rows (mma.sync.m16n8k8.tf32; emulated here); the
+    gradient, the objective and the returned distance stay fp64, so a reachable target is still met to rounding and the
+    reported distance is exact at the returned parameters."""
+    from oracle import qs_oracle as O
+    from qsearch_b200 import gates, gatesets, lowering
+    lib = emulated_library()
+    rng = np.random.default_rng(50 + n)
+    g = gatesets.QubitCNOTLinear()
+    c = gates.ProductGate(g.initial_layer(n))
+    for k in range(3):
+        c = c.appending(g.search_layers(n)[k % (n - 1)][0])
+    T = O.matrix(c, rng.random(c.num_inputs) * 2 * np.pi)
+    gp = lowering.lower(c)
+    x0 = rng.random((4, gp.n_params)) * 2 * np.pi
+    x, f, iters, status = lib.solve("lm", [gp], np.zeros(4, dtype="int32"), x0, T, gram_tf32=1.0)
+    assert f.min() < 1e-12
+    for k, xk in enumerate(x.reshape(4, -1)):
+        assert abs(O.matrix_distance_squared(T, O.matrix(c, xk)) - f[k]) < 1e-12

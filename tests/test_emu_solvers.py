@@ -149,3 +149,26 @@ def test_leap_reoptimizing_post_processor(emu):
     n_after = repr(out["structure"]).count("CNOTGate")
     assert n_after < 6
     assert O.matrix_distance_squared(T, O.matrix(out["structure"], out["parameters"])) < 1e-10
+
+
+def test_frontier_sizing_and_stop_rule_plumbing(emu):
+    """GpuParallelizer sizes one expansion to the SMs of the context's devices (role of num_tasks = worker count,
+    qsearch/parallelizers.py:74, compiler.py:89-93) and only frontier batches get the batch-level stop rules."""
+    from qsearch_b200 import parallelizers
+    T = unitaries.qft(8)
+    opts = q.Options(target=T, gateset=gatesets.QubitCNOTLinear())
+    opts.set_defaults(**q.defaults.standard_defaults)
+    opts.set_smart_defaults(**q.defaults.standard_smart_defaults)
+    ndev = emu.num_devices
+    assert parallelizers.default_num_tasks(opts) == 2 * parallelizers.MAX_BEAMS  # branching 2 on a 3-qubit line, beams capped
+    assert parallelizers.frontier_starts(opts, 16) == min(parallelizers.MAX_STARTS, 148 * ndev // 16)
+    assert parallelizers.frontier_starts(opts, 100000) == 1
+    assert parallelizers.frontier_starts(opts.updated(frontier_starts=5), 16) == 5
+    assert parallelizers.frontier_starts(opts.updated(solver=solvers.LeastSquares_Jac_Solver(starts=4)), 16) is None
+    s = solvers.LeastSquares_Jac_Solver()
+    plain, front = s._solve_opts(opts), s._solve_opts(opts, frontier=True)
+    assert plain["straggler_factor"] == 0.0 and plain["sibling_stop"] == 0.0
+    assert front["straggler_factor"] == s.FRONTIER_STRAGGLER and front["sibling_stop"] == opts.threshold
+    assert plain["gram_tf32"] == 0.0 and front["gram_tf32"] == 1.0
+    assert solvers.LeastSquares_Jac_Solver(gram_tf32=False)._solve_opts(opts, frontier=True)["gram_tf32"] == 0.0
+    assert solvers.LeastSquares_Jac_Solver(straggler_factor=0.0)._solve_opts(opts, frontier=True)["straggler_factor"] == 0.0

@@ -338,3 +338,28 @@ def test_solvers_on_a_circuit_with_two_qubit_rotations(lib):
         assert f.min() < 1e-10, (method, f)
         k = int(np.argmin(f))
         assert abs(O.matrix_distance_squared(T, O.matrix(c, x.reshape(16, -1)[k])) - f[k]) < 1e-12
+
+
+@pytest.mark.parametrize("n", [3, 4, 5])
+def test_tf32_gram_option_of_the_lm_kernel(lib, n):
+    """gram_tf32 on the device: same convergence on reachable targets (distance exact at the returned x: fp64 everywhere except
+    the Gauss-Newton matrix), and on an unreachable one minima as good as the fp64 kernel's."""
+    rng = np.random.default_rng(60 + n)
+    g = gatesets.QubitCNOTRing()
+    layers = g.search_layers(n)
+    c = gates.ProductGate(g.initial_layer(n))
+    for _ in range(5):
+        c = c.appending(layers[int(rng.integers(len(layers)))][0])
+    gp = lowering.lower(c)
+    K = 16
+    x0 = rng.random((K, gp.n_params)) * 2 * np.pi
+    poi = np.zeros(K, dtype="int32")
+    T = O.matrix(c, rng.random(c.num_inputs) * 2 * np.pi)
+    x, f, it, st = lib.solve("lm", [gp], poi, x0, T, gram_tf32=1.0)
+    assert f.min() < 1e-10
+    for k in range(K):
+        assert abs(O.matrix_distance_squared(T, O.matrix(c, x.reshape(K, -1)[k])) - f[k]) < 1e-12
+    Tq = unitaries.qft(1 << n)
+    f64 = lib.solve("lm", [gp], poi, x0, Tq)[1]
+    f32 = lib.solve("lm", [gp], poi, x0, Tq, gram_tf32=1.0)[1]
+    assert f32.min() < f64.min() + 1e-4 and np.median(f32) < np.median(f64) + 1e-2

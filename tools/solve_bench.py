@@ -40,6 +40,7 @@ def main():
     ap.add_argument("--reps", type=int, default=1, help="identical repetitions per case (run-to-run spread)")
     ap.add_argument("--straggler", type=float, default=0.0, help="qsb_solver_opts.straggler_factor")
     ap.add_argument("--sibling", type=float, default=0.0, help="qsb_solver_opts.sibling_stop")
+    ap.add_argument("--tf32", type=float, default=0.0, help="qsb_solver_opts.gram_tf32")
     a = ap.parse_args()
     lib = _lib.get_library()
     cases = [("n3 d6 2x4", 3, 6, 2, 4, gatesets.QubitCNOTLinear()),
@@ -55,7 +56,7 @@ def main():
         gps, poi, x0 = case(n, depth, nc, starts, 5, gs)
         T = unitaries.qft(1 << n)
         lib.solve(a.method, gps[:1], poi[:1] * 0, x0[:gps[0].n_params], T)  # warm-up (module load, allocations)
-        kw = dict(straggler_factor=a.straggler, sibling_stop=a.sibling) if a.method == "lm" else {}
+        kw = dict(straggler_factor=a.straggler, sibling_stop=a.sibling, gram_tf32=a.tf32) if a.method == "lm" else {}
         walls = []
         for _ in range(a.reps):
             t0 = time.perf_counter()

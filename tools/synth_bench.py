@@ -46,6 +46,7 @@ def main():
     ap.add_argument("--fstarts", type=int, default=0, help="options.frontier_starts (0: sized to the GPUs by the parallelizer)")
     ap.add_argument("--straggler", type=float, default=-1.0, help="LM straggler_factor for frontier batches (-1: solver default)")
     ap.add_argument("--seed0", type=int, default=1000)
+    ap.add_argument("--tf32", type=int, default=-1, help="LM Gram product on the TF32 path for frontier batches (-1: solver default = on, 0: off)")
     ap.add_argument("--reopt", type=int, default=0, help="run LEAPReoptimizing_PostProcessor with this window size on LEAP results")
     a = ap.parse_args()
     lib = _lib.get_library()
@@ -55,7 +56,8 @@ def main():
         T = mk_t()
         for rep in range(a.reps):
             if a.solver == "lm":
-                solver = solvers.LeastSquares_Jac_Solver(starts=a.starts, straggler_factor=None if a.straggler < 0 else a.straggler)
+                solver = solvers.LeastSquares_Jac_Solver(starts=a.starts, straggler_factor=None if a.straggler < 0 else a.straggler,
+                                                         gram_tf32=None if a.tf32 < 0 else bool(a.tf32))
             else:
                 solver = solvers.BFGS_Jac_Solver(starts=a.starts)
             opts = q.Options(target=T, gateset=mk_gs(), solver=solver, seed=a.seed0 + rep, timeout=a.timeout)
@@ -78,7 +80,7 @@ def main():
                 extra = {"reopt_window": a.reopt, "reopt_wall_s": round(time.perf_counter() - t1, 3),
                          "cnots_before": repr(res["structure"]).count("CNOTGate"), "reopt_stats": post.get("stats")}
                 res = dict(res, structure=post["structure"], parameters=post["parameters"], distance=post.get("distance", res["distance"]))
-            print(json.dumps({"case": name, "rep": rep, "solver": a.solver, "starts": a.starts, "fstarts": a.fstarts, "straggler": a.straggler, "beams": a.beams, "devices": lib.num_devices, "wall_s": round(dt, 3),
+            print(json.dumps({"case": name, "rep": rep, "solver": a.solver, "starts": a.starts, "fstarts": a.fstarts, "straggler": a.straggler, "tf32": a.tf32, "beams": a.beams, "devices": lib.num_devices, "wall_s": round(dt, 3),
                               "cnots": repr(res["structure"]).count("CNOTGate"), "distance": float(res["distance"]),
                               "stats": res["stats"], "launches": lib.launch_count() - l0, **extra}), flush=True)
 
