@@ -149,7 +149,8 @@ def solve_form(lib, n, dist, world, cpu_solve):
                         "instance_iterations_per_s": world * tot_it / tot_t, "best_distance": best}
         out["what"] = ("n={}: 48 children x 4 starts, once against qft (unreachable) and once against a reachable target, through "
                        "LeastSquares_Jac_Solver.solve_batch (host x0 in, xopt / distance out). reference_semantics: every start runs to "
-                       "its own convergence; frontier_rules: straggler cap 2x + sibling stop, as GpuParallelizer runs it".format(n))
+                       "its own convergence, everything fp64; frontier_rules: straggler cap 2x + sibling stop + TF32 Gram matrix (gradient, objective and "
+                       "outputs fp64), as GpuParallelizer runs it".format(n))
         if cpu_solve is not None:
             out["cpu"] = cpu_solve
             out["speedup_vs_cpu"] = out["reference_semantics"]["solves_per_s"] / cpu_solve["solves_per_s"]

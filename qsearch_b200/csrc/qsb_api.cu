@@ -11,7 +11,7 @@
 #include "qsb_host.h"
 #include "qsb_generic.cuh"
 #include "qsb_warp.cuh"
-#include "qsb_launch.h"
+#include "qsb_launch_eval.h"
 
 // ---------------------------------------------------------------------------- errors
 static thread_local std::string g_err;
