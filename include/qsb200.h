@@ -31,6 +31,7 @@ extern "C" {
 #define QSB_ERR_UNSUPPORTED (-4) /* e.g. more than QSB_MAX_QUBITS qubits */
 
 #define QSB_MAX_QUBITS 5
+#define QSB_MAX_QUTRITS 3 /* radix-3 programs (qsb_program_create_qudits): N = 3^n <= 27 */
 
 /* Flat gate program: the lowered form of a ProductGate / KroneckerGate tree (qsearch/gates.py:845-1051).
  * Ops are applied in array order, each one LEFT-multiplying the running unitary (gates.py:959). */
@@ -50,7 +51,11 @@ enum qsb_opcode {
    * (qsrs/src/circuits.rs:457-633; no Python twin in qsearch/gates.py).  1 param each. */
   QSB_OP_RXX = 12, /* circuits.rs:457-514 */
   QSB_OP_RYY = 13, /* circuits.rs:516-578 */
-  QSB_OP_RZZ = 14  /* circuits.rs:580-633 */
+  QSB_OP_RZZ = 14, /* circuits.rs:580-633 */
+  /* radix-3 programs only (qsb_program_create_qudits with radix 3): the arbitrary single-qutrit gate, 8 params
+   * (three angles, five phases), on qutrit q0.  Constants of a radix-3 program (CSUM, CPI, CPIPhase, upgraded qubit
+   * gates: gates.py:525-602, 761-788) are QSB_OP_CONSTK ops whose matrix is 3^k x 3^k. */
+  QSB_OP_QUTRIT1 = 15 /* SingleQutritGate gates.py:411-523 */
 };
 
 typedef struct qsb_op {
@@ -93,12 +98,20 @@ const char* qsb_version(void);
 /* ---- programs (replaces native_from_object, qsrs/src/lib.rs:543-554) ------------------------------------ */
 int qsb_program_create(qsb_ctx* ctx, int n_qubits, int n_ops, const qsb_op* ops, int n_params,
                        const double* const_pool, size_t const_len, qsb_program** out_prog);
+/* The same for qudits of size `radix` (2: identical to qsb_program_create; 3: qutrits, gates.py:411-602 -- the reference's
+ * native backend half-supports them, qsrs/src/circuits.rs:968-1100, its Python backend fully).  A radix-3 program has
+ * n_qudits <= QSB_MAX_QUTRITS, ops QSB_OP_QUTRIT1 and QSB_OP_CONSTK only (q0 / q1 count qutrits; a CONSTK constant is
+ * 3^k x 3^k, 2*9^k doubles), N = 3^n_qudits everywhere an output size says N, and runs in the interpreter kernels: every
+ * evaluation call and both solvers, not QSB_RUN_LMSYS. */
+int qsb_program_create_qudits(qsb_ctx* ctx, int radix, int n_qudits, int n_ops, const qsb_op* ops, int n_params,
+                              const double* const_pool, size_t const_len, qsb_program** out_prog);
 int qsb_program_destroy(qsb_ctx* ctx, qsb_program* prog);
+int qsb_program_radix(const qsb_program* prog);
 int qsb_program_num_params(const qsb_program* prog);
 int qsb_program_num_qubits(const qsb_program* prog);
 
 /* ---- host-buffer evaluation calls (replace PyGateWrapper.matrix / mat_jac and the objective functions) ---
- * progs[n_programs]; prog_of_instance[n_instances] indexes progs; all programs must have the same qubit count.
+ * progs[n_programs]; prog_of_instance[n_instances] indexes progs; all programs must have the same qubit count (and radix).
  * params: ragged concatenation, instance i uses the next P_i doubles.  Work is sharded over the context's
  * devices in contiguous instance ranges; host<->device copies are part of the call. */
 int qsb_eval_matrix(qsb_ctx* ctx, int n_programs, const qsb_program* const* progs, int n_instances,

@@ -109,7 +109,46 @@ def _rzz(v):  # qsrs/src/circuits.rs:580-633 (GateRZZ)
     return np.diag([neg, pos, pos, neg]).astype("complex128"), [np.diag([-0.5j * neg, 0.5j * pos, 0.5j * pos, -0.5j * neg]).astype("complex128")]
 
 
+def _qutrit_entries(s, c, p, m):
+    """The 3x3 of SingleQutritGate (gates.py:417-439) as a function of the sines s[0..2], cosines c[0..2] and the phase
+    factors p[b] = e^{+i v[3+b]}, m[b] = e^{-i v[3+b]}, b = 0..4, all passed as independent variables."""
+    return np.array([
+        [c[0] * c[1] * p[0], s[0] * p[2], c[0] * s[1] * p[3]],
+        [s[1] * s[2] * m[3] * m[4] - s[0] * c[1] * c[2] * p[0] * p[1] * m[2], c[0] * c[2] * p[1],
+         -c[1] * s[2] * m[0] * m[4] - s[0] * s[1] * c[2] * p[1] * m[2] * p[3]],
+        [-s[0] * c[1] * s[2] * p[0] * m[2] * p[4] - s[1] * c[2] * m[1] * m[3], c[0] * s[2] * p[4],
+         c[1] * c[2] * m[0] * m[1] - s[0] * s[1] * s[2] * m[2] * p[3] * p[4]],
+    ], dtype="complex128")
+
+
+def _single_qutrit(v):  # gates.py:411-523 (SingleQutritGate.matrix / mat_jac)
+    """The reference writes the eight Jacobian matrices out by hand (gates.py:441-517).  Here they follow from the matrix:
+    every entry is affine in (sin v_a, cos v_a) and in (p_b, m_b), so with U(...) the entries as a function of those,
+        dU/dv_a     = U(sin -> cos, cos -> -sin) - U(sin -> 0, cos -> 0)                       a = 0..2
+        dU/dv_{3+b} = i [U(m_b -> 0) - U(p_b -> 0, m_b -> 0)] - i [U(p_b -> 0) - U(p_b -> 0, m_b -> 0)]   b = 0..4
+    tests/golden/qutrit.npz pins both against the reference's hand-written matrices."""
+    v = np.asarray(v, dtype="float64")
+    s, c = np.sin(v[:3]), np.cos(v[:3])
+    p, m = np.exp(1j * v[3:8]), np.exp(-1j * v[3:8])
+    U = _qutrit_entries(s, c, p, m)
+    J = []
+    for a in range(3):
+        s1, c1, s0, c0 = s.copy(), c.copy(), s.copy(), c.copy()
+        s1[a], c1[a] = c[a], -s[a]
+        s0[a] = c0[a] = 0.0
+        J.append(_qutrit_entries(s1, c1, p, m) - _qutrit_entries(s0, c0, p, m))
+    for b in range(5):
+        p0, m0 = p.copy(), m.copy()
+        p0[b] = m0[b] = 0.0
+        base = _qutrit_entries(s, c, p0, m0)
+        only_p, only_m = p0.copy(), m0.copy()
+        only_p[b], only_m[b] = p[b], m[b]
+        J.append(1j * (_qutrit_entries(s, c, only_p, m0) - base) - 1j * (_qutrit_entries(s, c, p0, only_m) - base))
+    return U, J
+
+
 _PARAM_LEAVES = {
+    "SingleQutritGate": _single_qutrit,
     "XGate": lambda v: (_rx(v[0]), [_rx_d(v[0])]),
     "YGate": lambda v: (_ry(v[0]), [_ry_d(v[0])]),
     "ZGate": lambda v: (_rz(v[0]), [_rz_d(v[0])]),

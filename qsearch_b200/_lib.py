@@ -74,6 +74,8 @@ class Library:
         d.qsb_host_free.argtypes = [_vp, _vp]
         d.qsb_ctx_launch_count.argtypes = [_vp, ctypes.POINTER(ctypes.c_uint64)]
         d.qsb_program_create.argtypes = [_vp, ctypes.c_int, ctypes.c_int, _vp, ctypes.c_int, _c_dp, ctypes.c_size_t, pp]
+        d.qsb_program_create_qudits.argtypes = [_vp, ctypes.c_int, ctypes.c_int, ctypes.c_int, _vp, ctypes.c_int, _c_dp, ctypes.c_size_t, pp]
+        d.qsb_program_radix.argtypes = [_vp]
         d.qsb_program_destroy.argtypes = [_vp, _vp]
         common = [_vp, ctypes.c_int, pp, ctypes.c_int, _c_ip, _c_dp]
         d.qsb_eval_matrix.argtypes = common + [_c_dp]
@@ -167,8 +169,12 @@ class Library:
                 if ent is None:
                     ops = np.ascontiguousarray(gp.ops, dtype=OP_DTYPE)
                     h = _vp()
-                    self.check(self.dll.qsb_program_create(ctx, gp.n_qubits, len(ops), ops.ctypes.data_as(_vp), gp.n_params,
-                                                           _dp(gp.consts), gp.consts.size, ctypes.byref(h)))
+                    if getattr(gp, "radix", 2) == 2:
+                        self.check(self.dll.qsb_program_create(ctx, gp.n_qubits, len(ops), ops.ctypes.data_as(_vp), gp.n_params,
+                                                               _dp(gp.consts), gp.consts.size, ctypes.byref(h)))
+                    else:  # qutrit programs (radix 3)
+                        self.check(self.dll.qsb_program_create_qudits(ctx, gp.radix, gp.n_qubits, len(ops), ops.ctypes.data_as(_vp),
+                                                                      gp.n_params, _dp(gp.consts), gp.consts.size, ctypes.byref(h)))
                     ent = [h, gp, 0]  # keep gp alive so an id()-based key cannot be reused
                 else:
                     del self._programs[key]  # re-insert below: most recently used last
@@ -217,7 +223,7 @@ class Library:
     # ------------------------------------------------------------------ host-buffer evaluation
     def eval_matrix(self, gps, prog_of_instance, params):
         with self._pack(gps, prog_of_instance, params) as (handles, poi, params, _):
-            N = 1 << gps[0].n_qubits
+            N = gps[0].dim
             U = np.empty((len(poi), N, N), dtype="complex128")
             self.check(self.dll.qsb_eval_matrix(self.ctx, len(gps), handles, len(poi), poi.ctypes.data_as(_c_ip), _dp(params),
                                                 U.ctypes.data_as(_c_dp)))
@@ -225,7 +231,7 @@ class Library:
 
     def eval_mat_jac(self, gps, prog_of_instance, params):
         with self._pack(gps, prog_of_instance, params) as (handles, poi, params, sizes):
-            N = 1 << gps[0].n_qubits
+            N = gps[0].dim
             U = np.empty((len(poi), N, N), dtype="complex128")
             J = np.empty((int(sizes.sum()), N, N), dtype="complex128")
             self.check(self.dll.qsb_eval_mat_jac(self.ctx, len(gps), handles, len(poi), poi.ctypes.data_as(_c_ip), _dp(params),
@@ -252,7 +258,7 @@ class Library:
     def eval_residuals_jac(self, gps, prog_of_instance, params, target, out_r=None, out_Jr=None):
         """r: [inst, 2N^2]; Jr: [sum P, 2N^2] (row k = parameter k; the reference's array is its transpose view)."""
         with self._pack(gps, prog_of_instance, params) as (handles, poi, params, sizes):
-            N = 1 << gps[0].n_qubits
+            N = gps[0].dim
             T = np.ascontiguousarray(target, dtype="complex128")
             r = out_r if out_r is not None else np.empty((len(poi), 2 * N * N), dtype="float64")
             Jr = out_Jr if out_Jr is not None else np.empty((int(sizes.sum()), 2 * N * N), dtype="float64")
@@ -360,7 +366,7 @@ class Batch:
 
     def fetch(self):
         what, first, count = self._last
-        N = 1 << self.n_qubits
+        N = self.gps[0].dim
         npar = int(self.sizes[first:first + count].sum())
         a = b = c = None
         if what == RUN_MATRIX:

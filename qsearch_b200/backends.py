@@ -47,7 +47,7 @@ def program_for(circ):
     if gp is None:
         gp = lower(circ)
         if gp.consts.size:
-            gp.key = ("const", gp.n_qubits, gp.n_params, hashlib.sha1(np.ascontiguousarray(gp.ops).tobytes()).hexdigest(),
+            gp.key = ("const", gp.radix, gp.n_qubits, gp.n_params, hashlib.sha1(np.ascontiguousarray(gp.ops).tobytes()).hexdigest(),
                       hashlib.sha1(gp.consts.tobytes()).hexdigest())
             return gp
         gp.key = key

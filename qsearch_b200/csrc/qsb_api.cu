@@ -123,22 +123,38 @@ static int op_params(int opcode) {
     case QSB_OP_RX: case QSB_OP_RY: case QSB_OP_RZ: case QSB_OP_U1: case QSB_OP_RXX: case QSB_OP_RYY: case QSB_OP_RZZ: return 1;
     case QSB_OP_U2: case QSB_OP_XZXZ: return 2;
     case QSB_OP_U3: case QSB_OP_ZXZXZ: return 3;
+    case QSB_OP_QUTRIT1: return 8;
     default: return 0;
   }
 }
 
-extern "C" int qsb_program_create(qsb_ctx* ctx, int n_qubits, int n_ops, const qsb_op* ops, int n_params,
-                                  const double* const_pool, size_t const_len, qsb_program** out_prog) {
+static int program_create(qsb_ctx* ctx, int radix, int n_qubits, int n_ops, const qsb_op* ops, int n_params,
+                          const double* const_pool, size_t const_len, qsb_program** out_prog) {
   if (!ctx || !out_prog || (n_ops > 0 && !ops)) return qsb_fail(QSB_ERR_INVALID, "NULL argument");
-  if (n_qubits < 1 || n_qubits > QSB_MAX_QUBITS)
+  if (radix != 2 && radix != 3) return qsb_fail(QSB_ERR_UNSUPPORTED, "radix must be 2 (qubits) or 3 (qutrits)");
+  if (radix == 2 && (n_qubits < 1 || n_qubits > QSB_MAX_QUBITS))
     return qsb_fail(QSB_ERR_UNSUPPORTED, "n_qubits must be in 1.." + std::to_string(QSB_MAX_QUBITS));
+  if (radix == 3 && (n_qubits < 1 || n_qubits > QSB_MAX_QUTRITS))
+    return qsb_fail(QSB_ERR_UNSUPPORTED, "n_qudits must be in 1.." + std::to_string(QSB_MAX_QUTRITS) + " for radix 3");
   if (n_ops < 0 || n_params < 0) return qsb_fail(QSB_ERR_INVALID, "negative size");
   std::vector<char> seen(n_params, 0);
-  bool fast = true;
+  bool fast = radix == 2;
   for (int j = 0; j < n_ops; ++j) {
     const qsb_op& o = ops[j];
     int np = op_params(o.opcode);
+    if (radix == 3 && o.opcode != QSB_OP_QUTRIT1 && o.opcode != QSB_OP_CONSTK)
+      return qsb_fail(QSB_ERR_INVALID, "op " + std::to_string(j) + ": a radix-3 program takes QSB_OP_QUTRIT1 and QSB_OP_CONSTK ops only");
     switch (o.opcode) {
+      case QSB_OP_QUTRIT1:
+        if (radix != 3) return qsb_fail(QSB_ERR_INVALID, "op " + std::to_string(j) + ": QSB_OP_QUTRIT1 needs a radix-3 program");
+        if (o.q0 < 0 || o.q0 >= n_qubits) return qsb_fail(QSB_ERR_INVALID, "op " + std::to_string(j) + ": qutrit out of range");
+        if (o.param_off < 0 || o.param_off + np > n_params)
+          return qsb_fail(QSB_ERR_INVALID, "op " + std::to_string(j) + ": parameter range out of bounds");
+        for (int k = 0; k < np; ++k) {
+          if (seen[o.param_off + k]) return qsb_fail(QSB_ERR_INVALID, "parameter used by two ops");
+          seen[o.param_off + k] = 1;
+        }
+        break;
       case QSB_OP_RX: case QSB_OP_RY: case QSB_OP_RZ: case QSB_OP_U1: case QSB_OP_U2: case QSB_OP_U3:
       case QSB_OP_XZXZ: case QSB_OP_ZXZXZ:
         if (o.q0 < 0 || o.q0 >= n_qubits) return qsb_fail(QSB_ERR_INVALID, "op " + std::to_string(j) + ": qubit out of range");
@@ -168,7 +184,8 @@ extern "C" int qsb_program_create(qsb_ctx* ctx, int n_qubits, int n_ops, const q
       case QSB_OP_CONSTK: {
         int k = o.q1;
         if (k < 1 || o.q0 < 0 || o.q0 + k > n_qubits) return qsb_fail(QSB_ERR_INVALID, "op " + std::to_string(j) + ": bad CONSTK range");
-        if (o.const_off < 0 || (size_t)o.const_off + 2 * ((size_t)1 << (2 * k)) > const_len)
+        const size_t kk = qsb_geom_dim(radix, k);
+        if (o.const_off < 0 || (size_t)o.const_off + 2 * kk * kk > const_len)
           return qsb_fail(QSB_ERR_INVALID, "constant out of bounds");
         fast = false;
       } break;
@@ -181,6 +198,7 @@ extern "C" int qsb_program_create(qsb_ctx* ctx, int n_qubits, int n_ops, const q
   qsb_program* p = new (std::nothrow) qsb_program();
   if (!p) return qsb_fail(QSB_ERR_NOMEM, "out of host memory");
   p->n_qubits = n_qubits; p->n_ops = n_ops; p->n_params = n_params; p->fast_ok = fast;
+  p->radix = radix; p->dim = qsb_geom_dim(radix, n_qubits);
   p->ops.assign(ops, ops + n_ops);
   if (const_len) p->consts.assign(const_pool, const_pool + const_len);
   std::vector<double> pscale(std::max(1, n_params), 1.0);  // angle scale per parameter (half angles: gates.py:324-346 etc.)
@@ -202,7 +220,8 @@ extern "C" int qsb_program_create(qsb_ctx* ctx, int n_qubits, int n_ops, const q
       qsb_op& o = p->ops[j];
       const int np = op_params(o.opcode);
       o.reserved = j + used;
-      if (o.opcode != QSB_OP_CNOT && o.opcode != QSB_OP_CONSTK && o.opcode != QSB_OP_RXX && o.opcode != QSB_OP_RYY && o.opcode != QSB_OP_RZZ)
+      if (o.opcode != QSB_OP_CNOT && o.opcode != QSB_OP_CONSTK && o.opcode != QSB_OP_RXX && o.opcode != QSB_OP_RYY && o.opcode != QSB_OP_RZZ &&
+          o.opcode != QSB_OP_QUTRIT1)
         for (int w = 0; w <= np; ++w) slotmap[o.reserved + w] = (j << 2) | w;
       used += np;
     }
@@ -234,6 +253,15 @@ extern "C" int qsb_program_create(qsb_ctx* ctx, int n_qubits, int n_ops, const q
   return QSB_OK;
 }
 
+extern "C" int qsb_program_create(qsb_ctx* ctx, int n_qubits, int n_ops, const qsb_op* ops, int n_params,
+                                  const double* const_pool, size_t const_len, qsb_program** out_prog) {
+  return program_create(ctx, 2, n_qubits, n_ops, ops, n_params, const_pool, const_len, out_prog);
+}
+extern "C" int qsb_program_create_qudits(qsb_ctx* ctx, int radix, int n_qudits, int n_ops, const qsb_op* ops, int n_params,
+                                         const double* const_pool, size_t const_len, qsb_program** out_prog) {
+  return program_create(ctx, radix, n_qudits, n_ops, ops, n_params, const_pool, const_len, out_prog);
+}
+
 extern "C" int qsb_program_destroy(qsb_ctx* ctx, qsb_program* prog) {
   if (!prog) return QSB_OK;
   if (ctx) {
@@ -250,10 +278,10 @@ extern "C" int qsb_program_destroy(qsb_ctx* ctx, qsb_program* prog) {
 }
 extern "C" int qsb_program_num_params(const qsb_program* p) { return p ? p->n_params : -1; }
 extern "C" int qsb_program_num_qubits(const qsb_program* p) { return p ? p->n_qubits : -1; }
+extern "C" int qsb_program_radix(const qsb_program* p) { return p ? p->radix : -1; }
 
 // max |T T^dagger - I| <= 1e-9 (N <= 32: a few thousand flops): the body-frame LM forms (qsb_lm3.cuh) need a unitary target
-bool qsb_target_is_unitary(const double* T, int nq) {
-  const int N = 1 << nq;
+bool qsb_target_is_unitary(const double* T, int N) {
   for (int i = 0; i < N; ++i)
     for (int j = 0; j <= i; ++j) {
       double re = (i == j) ? -1.0 : 0.0, im = 0.0;
@@ -341,13 +369,14 @@ extern "C" int qsb_batch_create(qsb_ctx* ctx, int slot, int n_programs, const qs
   if (n_programs <= 0 || n_instances < 0) return qsb_fail(QSB_ERR_INVALID, "empty program list");
   for (int p = 0; p < n_programs; ++p) {
     if (!progs[p]) return qsb_fail(QSB_ERR_INVALID, "NULL program");
-    if (progs[p]->n_qubits != progs[0]->n_qubits)
+    if (progs[p]->n_qubits != progs[0]->n_qubits || progs[p]->radix != progs[0]->radix)
       return qsb_fail(QSB_ERR_INVALID, "all programs of a batch must act on the same number of qubits");
     if ((int)progs[p]->d_ops.size() <= slot) return qsb_fail(QSB_ERR_INVALID, "program was created on another context");
   }
   qsb_batch* b = new (std::nothrow) qsb_batch();
   if (!b) return qsb_fail(QSB_ERR_NOMEM, "out of host memory");
   b->ctx = ctx; b->slot = slot; b->n_qubits = progs[0]->n_qubits; b->n_instances = n_instances; b->n_programs = n_programs;
+  b->radix = progs[0]->radix; b->dim = progs[0]->dim;
   b->fast_ok = true;
   b->force_generic = ctx->force_generic;
   std::vector<QsbDevProgram> dp(n_programs);
@@ -378,7 +407,7 @@ extern "C" int qsb_batch_create(qsb_ctx* ctx, int slot, int n_programs, const qs
   b->sz_prog_idx = sizeof(int32_t) * std::max(1, n_instances);
   b->sz_param_off = sizeof(long long) * ((size_t)n_instances + 1);
   b->sz_params = sizeof(double) * std::max<long long>(1, off);
-  b->sz_target = sizeof(double) * 2 * ((size_t)1 << (2 * b->n_qubits));
+  b->sz_target = sizeof(double) * 2 * b->dim * b->dim;
   if ((rc = qsb_pool_alloc(d, (void**)&b->d_progs, b->sz_progs)) || (rc = qsb_pool_alloc(d, (void**)&b->d_prog_idx, b->sz_prog_idx)) ||
       (rc = qsb_pool_alloc(d, (void**)&b->d_param_off, b->sz_param_off)) || (rc = qsb_pool_alloc(d, (void**)&b->d_params, b->sz_params)) ||
       (rc = qsb_pool_alloc(d, (void**)&b->d_target, b->sz_target)))
@@ -426,15 +455,15 @@ extern "C" int qsb_batch_set_target(qsb_batch* b, const double* target) {
   if (!b || !target) return qsb_fail(QSB_ERR_INVALID, "NULL argument");
   const QsbDevice& d = b->ctx->devs[b->slot];
   QSB_CUDA(cudaSetDevice(d.id));
-  QSB_CUDA(cudaMemcpyAsync(b->d_target, target, sizeof(double) * 2 * ((size_t)1 << (2 * b->n_qubits)), cudaMemcpyHostToDevice, d.stream));
+  QSB_CUDA(cudaMemcpyAsync(b->d_target, target, sizeof(double) * 2 * b->dim * b->dim, cudaMemcpyHostToDevice, d.stream));
   QSB_CUDA(cudaStreamSynchronize(d.stream));
-  b->target_unitary = qsb_target_is_unitary(target, b->n_qubits);
+  b->target_unitary = qsb_target_is_unitary(target, (int)b->dim);
   return QSB_OK;
 }
 
 // sizes (in doubles) of the three output buffers of a run over [first, first+count)
 static void out_sizes(const qsb_batch* b, int what, int first, int count, size_t* a, size_t* bb, size_t* c) {
-  const size_t NN2 = 2 * ((size_t)1 << (2 * b->n_qubits));
+  const size_t NN2 = 2 * b->dim * b->dim;
   const size_t np = (size_t)(b->param_off[first + count] - b->param_off[first]);
   *a = *bb = *c = 0;
   switch (what) {
@@ -563,8 +592,8 @@ static int run_shard(const HostEvalJob& job, int slot, int i0, int i1, const std
   // chunk list (output bytes per chunk bounded; always at least one instance per chunk)
   std::vector<int> starts;
   {
-    qsb_batch probe;  // only param_off / n_qubits are needed by out_sizes
-    probe.n_qubits = job.progs[0]->n_qubits;
+    qsb_batch probe;  // only param_off / the dimension are needed by out_sizes
+    probe.n_qubits = job.progs[0]->n_qubits; probe.radix = job.progs[0]->radix; probe.dim = job.progs[0]->dim;
     probe.param_off.assign(poff.begin() + i0, poff.begin() + i1 + 1);
     size_t sa, sb, sc;
     out_sizes(&probe, job.what, 0, n, &sa, &sb, &sc);
@@ -596,7 +625,7 @@ static int run_shard(const HostEvalJob& job, int slot, int i0, int i1, const std
         cudaEventCreateWithFlags(&ev_copy[k], cudaEventDisableTiming) != cudaSuccess)
       return done(qsb_fail(QSB_ERR_CUDA, "cudaEventCreate failed"));
   }
-  const size_t NN2 = 2 * ((size_t)1 << (2 * batch[0]->n_qubits));
+  const size_t NN2 = 2 * batch[0]->dim * batch[0]->dim;
 #define QSB_R(call) do { cudaError_t _e = (call); if (_e != cudaSuccess) return done(qsb_cuda_fail(_e, #call)); } while (0)
   auto launch = [&](int c) -> int {
     const int k = c % n_sets;

@@ -19,7 +19,8 @@
 #define QSB_LAUNCH(kernel, grid, block, smem, stream, ...) kernel<<<(grid), (block), (smem), (stream)>>>(__VA_ARGS__)
 #endif
 
-#define QSB_TRIG_STRIDE 6  // doubles of cached sin/cos per parameterised op
+#define QSB_TRIG_STRIDE 6     // doubles of cached sin/cos per parameterised op (qubit programs)
+#define QSB_TRIG_STRIDE3 16   // the same for radix-3 programs (SingleQutritGate: 3 angles + 5 phases)
 
 struct QsbDevProgram {
   const qsb_op* ops;
@@ -63,6 +64,7 @@ QSB_DEVICE int qsb_num_params(int opcode) {
     case QSB_OP_RX: case QSB_OP_RY: case QSB_OP_RZ: case QSB_OP_U1: case QSB_OP_RXX: case QSB_OP_RYY: case QSB_OP_RZZ: return 1;
     case QSB_OP_U2: case QSB_OP_XZXZ: return 2;
     case QSB_OP_U3: case QSB_OP_ZXZXZ: return 3;
+    case QSB_OP_QUTRIT1: return 8;
     default: return 0;
   }
 }
@@ -94,6 +96,10 @@ QSB_DEVICE void qsb_trig(int opcode, const double* x, double* t) {
       sincos(0.5 * x[0], &t[1], &t[0]);
       sincos(0.5 * x[1], &t[3], &t[2]);
       sincos(0.5 * x[2], &t[5], &t[4]);
+      break;
+    case QSB_OP_QUTRIT1:  // (cos, sin) of the three angles, then of the five phases
+#pragma unroll
+      for (int k = 0; k < 8; ++k) sincos(x[k], &t[2 * k + 1], &t[2 * k]);
       break;
     default: break;
   }
@@ -186,5 +192,70 @@ QSB_DEVICE void qsb_op2x2(const qsb_op& op, const double* trig, const double* co
   if (dagger) {
     cplx t = g[1];
     g[0] = cconj(g[0]); g[1] = cconj(g[2]); g[2] = cconj(t); g[3] = cconj(g[3]);
+  }
+}
+
+// ---------------------------------------------------------------------------- the single-qutrit leaf
+// SingleQutritGate (qsearch/gates.py:411-523; the parameterisation of Phys. Rev. D 38, 1994 quoted in utils.py:122-150):
+// every entry of the 3x3 is a sum of at most two monomials  sign * f1(th1) f2(th2) f3(th3) * exp(i (e . phi)),
+// f in {1, sin, cos}, e in {-1, 0, 1}^5.  The eight parameter derivatives follow from the monomials by calculus
+// (d sin = cos, d cos = -sin, d/dphi_b = i e_b), so one table serves the gate and its Jacobian (gates.py:441-517 writes
+// the nine matrices out entry by entry; the tests compare against fixtures generated from that code).
+// t: (cos, sin) of v[0..7] as written by qsb_trig.  which = 0: the gate, 1..3: d/dtheta, 4..8: d/dphi.
+#define QSB_Q3_SIN 1
+#define QSB_Q3_COS 2
+QSB_DEVICE void qsb_q3_term(cplx* g, int which, const double* t, int entry, double sign, int f1, int f2, int f3,
+                            int e1, int e2, int e3, int e4, int e5) {
+  const int f[3] = {f1, f2, f3}, e[5] = {e1, e2, e3, e4, e5};
+  double r = sign;
+#pragma unroll
+  for (int a = 0; a < 3; ++a) {
+    const double c = t[2 * a], s = t[2 * a + 1];
+    if (which == 1 + a) {
+      if (f[a] == 0) return;
+      r *= (f[a] == QSB_Q3_SIN) ? c : -s;
+    } else if (f[a] != 0) {
+      r *= (f[a] == QSB_Q3_SIN) ? s : c;
+    }
+  }
+  cplx ph = cmk(r, 0.0);
+#pragma unroll
+  for (int b = 0; b < 5; ++b)
+    if (e[b] != 0) ph = cmul(ph, cmk(t[6 + 2 * b], e[b] * t[7 + 2 * b]));
+  if (which >= 4) {
+    const int eb = e[which - 4];
+    if (eb == 0) return;
+    ph = cscale(cmuli(ph), (double)eb);
+  }
+  g[entry] = cadd(g[entry], ph);
+}
+
+// g[9] row-major
+QSB_DEVICE void qsb_qutrit3x3(const double* t, int which, cplx* g) {
+  const int S = QSB_Q3_SIN, C = QSB_Q3_COS;
+#pragma unroll
+  for (int i = 0; i < 9; ++i) g[i] = cmk(0.0, 0.0);
+  //                       entry sign th1 th2 th3   phi1..phi5
+  qsb_q3_term(g, which, t, 0, +1.0, C, C, 0, +1, 0, 0, 0, 0);
+  qsb_q3_term(g, which, t, 1, +1.0, S, 0, 0, 0, 0, +1, 0, 0);
+  qsb_q3_term(g, which, t, 2, +1.0, C, S, 0, 0, 0, 0, +1, 0);
+  qsb_q3_term(g, which, t, 3, +1.0, 0, S, S, 0, 0, 0, -1, -1);
+  qsb_q3_term(g, which, t, 3, -1.0, S, C, C, +1, +1, -1, 0, 0);
+  qsb_q3_term(g, which, t, 4, +1.0, C, 0, C, 0, +1, 0, 0, 0);
+  qsb_q3_term(g, which, t, 5, -1.0, 0, C, S, -1, 0, 0, 0, -1);
+  qsb_q3_term(g, which, t, 5, -1.0, S, S, C, 0, +1, -1, +1, 0);
+  qsb_q3_term(g, which, t, 6, -1.0, S, C, S, +1, 0, -1, 0, +1);
+  qsb_q3_term(g, which, t, 6, -1.0, 0, S, C, 0, -1, 0, -1, 0);
+  qsb_q3_term(g, which, t, 7, +1.0, C, 0, S, 0, 0, 0, 0, +1);
+  qsb_q3_term(g, which, t, 8, +1.0, 0, C, C, -1, -1, 0, 0, 0);
+  qsb_q3_term(g, which, t, 8, -1.0, S, S, S, 0, 0, -1, +1, +1);
+}
+
+QSB_DEVICE void qsb_dagger3x3(cplx* g) {
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    g[4 * i] = cconj(g[4 * i]);
+#pragma unroll
+    for (int j = i + 1; j < 3; ++j) { const cplx a = g[3 * i + j]; g[3 * i + j] = cconj(g[3 * j + i]); g[3 * j + i] = cconj(a); }
   }
 }

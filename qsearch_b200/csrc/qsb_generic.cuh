@@ -13,11 +13,32 @@
 #pragma once
 #include "qsb_device.cuh"
 
+// The template parameter NQ of everything in this file is a GEOMETRY CODE: 1..QSB_MAX_QUBITS = that many qubits
+// (N = 2^NQ); QSB_GEOM_QUTRIT + m = m qutrits (N = 3^m; SingleQutritGate + constants, gates.py:411-602).  Index arithmetic
+// uses / N and % N (compile-time constants: shifts and masks for the qubit geometries).
+#define QSB_GEOM_QUTRIT 8
+template <int NQ>
+struct QsbDims {
+  static constexpr bool TRIT = NQ > QSB_GEOM_QUTRIT;
+  static constexpr int ND = TRIT ? NQ - QSB_GEOM_QUTRIT : NQ;  // qudits
+  static constexpr int RADIX = TRIT ? 3 : 2;
+  static constexpr int N = TRIT ? (ND == 1 ? 3 : ND == 2 ? 9 : 27) : (1 << ND);
+  static constexpr int NN = N * N;
+  static constexpr int TRIG = TRIT ? QSB_TRIG_STRIDE3 : QSB_TRIG_STRIDE;  // doubles of trig cache per op
+  static constexpr int MAXNP = TRIT ? 8 : 3;                              // most parameters of one op
+};
+QSB_HOST_DEVICE int qsb_geom_code(int radix, int n_qudits) { return radix == 3 ? QSB_GEOM_QUTRIT + n_qudits : n_qudits; }
+QSB_HOST_DEVICE size_t qsb_geom_dim(int radix, int n_qudits) {
+  size_t n = 1;
+  for (int i = 0; i < n_qudits; ++i) n *= (size_t)radix;
+  return n;
+}
+
 template <int NQ>
 struct QsbGeom {
-  static constexpr int N = 1 << NQ;
+  static constexpr int N = QsbDims<NQ>::N;
   static constexpr int NN = N * N;
-  static constexpr int T = (NN / 2 < 32) ? 32 : NN / 2;  // threads per CTA
+  static constexpr int T = (NN / 2 < 32) ? 32 : ((NN + 1) / 2 + 31) / 32 * 32;  // threads per CTA (a multiple of 32)
 };
 
 struct QsbBatchArgs {
@@ -92,18 +113,20 @@ QSB_DEVICE void qsb_right_cnot(cplx* M, int ctrl, int tgt) {
   }
 }
 
-// k-qubit constant C (K x K, row-major interleaved) on contiguous qubits q0..q0+k-1.
+// k-qudit constant C (K x K, K = radix^k, row-major interleaved) on contiguous qudits q0..q0+k-1.
 // left: M <- (I (x) C (x) I) M (or C^dagger); right: M <- M (I (x) C (x) I).
 template <int NQ>
 QSB_DEVICE void qsb_constk(cplx* M, int q0, int k, const double* C, bool dagger, bool right) {
-  constexpr int N = 1 << NQ;
-  const int K = 1 << k, lo_bits = NQ - q0 - k, lo_mask = (1 << lo_bits) - 1;
-  cplx v[1 << QSB_MAX_QUBITS];
+  constexpr int N = QsbDims<NQ>::N, R = QsbDims<NQ>::RADIX;
+  int K = 1, lo = 1;  // lo = radix^(qudits below the gate): stride of the gate's least significant digit
+  for (int i = 0; i < k; ++i) K *= R;
+  for (int i = 0; i < QsbDims<NQ>::ND - q0 - k; ++i) lo *= R;
+  cplx v[1 << QSB_MAX_QUBITS];  // 32 >= 27
   for (int idx = threadIdx.x; idx < (N / K) * N; idx += blockDim.x) {
     int other = idx % N, grp = idx / N;
-    int base = ((grp >> lo_bits) << (lo_bits + k)) | (grp & lo_mask);
+    int base = (grp / lo) * (lo * K) + grp % lo;
     for (int m = 0; m < K; ++m) {
-      int line = base | (m << lo_bits);
+      int line = base + m * lo;
       v[m] = right ? M[other * N + line] : M[line * N + other];
     }
     for (int m2 = 0; m2 < K; ++m2) {
@@ -115,7 +138,7 @@ QSB_DEVICE void qsb_constk(cplx* M, int q0, int k, const double* C, bool dagger,
         cplx c = cmk(C[2 * e], C[2 * e + 1]);
         acc = (dagger && !right) ? cfma_conj(c, v[m], acc) : cfma(c, v[m], acc);
       }
-      int line = base | (m2 << lo_bits);
+      int line = base + m2 * lo;
       if (right) M[other * N + line] = acc; else M[line * N + other] = acc;
     }
   }
@@ -152,40 +175,85 @@ QSB_DEVICE void qsb_rpp(cplx* dst, const cplx* src, int opcode, int q0, int q1, 
   }
 }
 
+// One-qutrit gate g (3x3 row-major) on qutrit q.  left: dst <- (I (x) g (x) I) src over row triples with stride
+// 3^(n-1-q) (out of place when dst != src; in place each thread owns a whole triple); right: M <- M (I (x) g (x) I).
+template <int NQ>
+QSB_DEVICE void qsb_left_3x3(cplx* dst, const cplx* src, int q, const cplx* g) {
+  constexpr int N = QsbDims<NQ>::N;
+  int s = 1;
+  for (int i = 0; i < QsbDims<NQ>::ND - 1 - q; ++i) s *= 3;
+  for (int idx = threadIdx.x; idx < N * N / 3; idx += blockDim.x) {
+    const int c = idx % N, tq = idx / N, r0 = (tq / s) * 3 * s + tq % s;
+    const cplx a = src[r0 * N + c], b = src[(r0 + s) * N + c], d = src[(r0 + 2 * s) * N + c];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) dst[(r0 + i * s) * N + c] = cfma(g[3 * i + 2], d, cfma(g[3 * i + 1], b, cmul(g[3 * i], a)));
+  }
+}
+
+template <int NQ>
+QSB_DEVICE void qsb_right_3x3(cplx* M, int q, const cplx* g) {
+  constexpr int N = QsbDims<NQ>::N;
+  int s = 1;
+  for (int i = 0; i < QsbDims<NQ>::ND - 1 - q; ++i) s *= 3;
+  for (int idx = threadIdx.x; idx < N * N / 3; idx += blockDim.x) {
+    const int i = idx / (N / 3), tq = idx % (N / 3), c0 = (tq / s) * 3 * s + tq % s;
+    const cplx a = M[i * N + c0], b = M[i * N + c0 + s], d = M[i * N + c0 + 2 * s];
+#pragma unroll
+    for (int j = 0; j < 3; ++j) M[i * N + c0 + j * s] = cfma(d, g[6 + j], cfma(b, g[3 + j], cmul(a, g[j])));
+  }
+}
+
 // Apply op j to M from the left (dagger: its inverse).  All threads call; caller synchronises afterwards.
 template <int NQ>
 QSB_DEVICE void qsb_apply_left(cplx* M, const qsb_op& op, const double* trig, const double* consts, bool dagger) {
+  if constexpr (QsbDims<NQ>::TRIT) {  // radix 3: the single-qutrit leaf and k-qutrit constants
+    if (op.opcode == QSB_OP_CONSTK) { qsb_constk<NQ>(M, op.q0, op.q1, consts + op.const_off, dagger, false); return; }
+    cplx g3[9];
+    qsb_qutrit3x3(trig, 0, g3);
+    if (dagger) qsb_dagger3x3(g3);
+    qsb_left_3x3<NQ>(M, M, op.q0, g3);
+    return;
+  } else {
   if (op.opcode == QSB_OP_CNOT) { qsb_left_cnot<NQ>(M, op.q0, op.q1); return; }
   if (op.opcode == QSB_OP_CONSTK) { qsb_constk<NQ>(M, op.q0, op.q1, consts + op.const_off, dagger, false); return; }
   if (qsb_is_rpp(op.opcode)) { qsb_rpp<NQ>(M, M, op.opcode, op.q0, op.q1, trig[0], dagger ? -trig[1] : trig[1], 1.0, false); return; }
   cplx g[4];
   qsb_op2x2(op, trig, consts, dagger, g);
   qsb_left_2x2<NQ>(M, op.q0, g);
+  }
 }
 
 template <int NQ>
 QSB_DEVICE void qsb_apply_right(cplx* M, const qsb_op& op, const double* trig, const double* consts) {
+  if constexpr (QsbDims<NQ>::TRIT) {
+    if (op.opcode == QSB_OP_CONSTK) { qsb_constk<NQ>(M, op.q0, op.q1, consts + op.const_off, false, true); return; }
+    cplx g3[9];
+    qsb_qutrit3x3(trig, 0, g3);
+    qsb_right_3x3<NQ>(M, op.q0, g3);
+    return;
+  } else {
   if (op.opcode == QSB_OP_CNOT) { qsb_right_cnot<NQ>(M, op.q0, op.q1); return; }
   if (op.opcode == QSB_OP_CONSTK) { qsb_constk<NQ>(M, op.q0, op.q1, consts + op.const_off, false, true); return; }
   if (qsb_is_rpp(op.opcode)) { qsb_rpp<NQ>(M, M, op.opcode, op.q0, op.q1, trig[0], trig[1], 1.0, true); return; }
   cplx g[4];
   qsb_op2x2(op, trig, consts, false, g);
   qsb_right_2x2<NQ>(M, op.q0, g);
+  }
 }
 
 // fill the per-instance sin/cos cache (one thread per op)
-QSB_DEVICE void qsb_fill_trig(const QsbDevProgram& P, const double* x, double* trig) {
+QSB_DEVICE void qsb_fill_trig(const QsbDevProgram& P, const double* x, double* trig, int stride = QSB_TRIG_STRIDE) {
   for (int j = threadIdx.x; j < P.n_ops; j += blockDim.x) {
     qsb_op op = P.ops[j];
-    if (qsb_num_params(op.opcode) > 0) qsb_trig(op.opcode, x + op.param_off, trig + j * QSB_TRIG_STRIDE);
+    if (qsb_num_params(op.opcode) > 0) qsb_trig(op.opcode, x + op.param_off, trig + j * stride);
   }
 }
 
 template <int NQ>
 QSB_DEVICE void qsb_load_init(cplx* M, const double* target_or_null, bool dagger) {
-  constexpr int N = 1 << NQ;
+  constexpr int N = QsbDims<NQ>::N;
   for (int e = threadIdx.x; e < N * N; e += blockDim.x) {
-    int r = e >> NQ, c = e & (N - 1);
+    int r = e / N, c = e % N;
     if (target_or_null == nullptr) M[e] = cmk(r == c ? 1.0 : 0.0, 0.0);
     else if (dagger) { const double* t = target_or_null + 2 * (c * N + r); M[e] = cmk(t[0], -t[1]); }
     else { const double* t = target_or_null + 2 * e; M[e] = cmk(t[0], t[1]); }
@@ -196,7 +264,7 @@ QSB_DEVICE void qsb_load_init(cplx* M, const double* target_or_null, bool dagger
 template <int NQ>
 QSB_DEVICE void qsb_forward(cplx* X, const QsbDevProgram& P, const double* trig) {
   for (int j = 0; j < P.n_ops; ++j) {
-    qsb_apply_left<NQ>(X, P.ops[j], trig + j * QSB_TRIG_STRIDE, P.consts, false);
+    qsb_apply_left<NQ>(X, P.ops[j], trig + j * QsbDims<NQ>::TRIG, P.consts, false);
     __syncthreads();
   }
 }
@@ -220,7 +288,7 @@ QSB_DEVICE cplx qsb_block_sum(cplx v, cplx* red) {
 // MATRIX: out_a[li] = U.    DIST: out_a[li] = |1 - |Tr(U T^dagger)|/N|   (comparison.py:8-22)
 template <int NQ, int WHAT>
 QSB_GLOBAL __launch_bounds__(QsbGeom<NQ>::T) qsb_k_forward(QsbBatchArgs a) {
-  constexpr int N = 1 << NQ;
+  constexpr int N = QsbDims<NQ>::N;
   QSB_DYN_SMEM(smem_raw);
   cplx* X = (cplx*)smem_raw;
   cplx* red = X + N * N;
@@ -228,7 +296,7 @@ QSB_GLOBAL __launch_bounds__(QsbGeom<NQ>::T) qsb_k_forward(QsbBatchArgs a) {
   for (int li = blockIdx.x; li < a.count; li += gridDim.x) {
     const int inst = a.first + li;
     const QsbDevProgram P = a.progs[a.prog_idx[inst]];
-    qsb_fill_trig(P, a.params + a.param_off[inst], trig);
+    qsb_fill_trig(P, a.params + a.param_off[inst], trig, QsbDims<NQ>::TRIG);
     qsb_load_init<NQ>(X, WHAT == QSB_RUN_DIST ? a.target : nullptr, true);
     __syncthreads();
     qsb_forward<NQ>(X, P, trig);
@@ -251,25 +319,30 @@ QSB_GLOBAL __launch_bounds__(QsbGeom<NQ>::T) qsb_k_forward(QsbBatchArgs a) {
 template <int NQ, int WHAT>
 QSB_DEVICE void qsb_jac_instance(cplx* X, cplx* S, cplx* Y, double* trig, const QsbDevProgram& P, const double* x,
                                  const double* target, double* out_u, double* out_j) {
-  constexpr int N = 1 << NQ, NN = N * N;
-  qsb_fill_trig(P, x, trig);
+  constexpr int N = QsbDims<NQ>::N, NN = N * N, TS = QsbDims<NQ>::TRIG;
+  qsb_fill_trig(P, x, trig, TS);
   qsb_load_init<NQ>(X, WHAT == QSB_RUN_RESID ? target : nullptr, true);
   qsb_load_init<NQ>(S, nullptr, false);
   __syncthreads();
   qsb_forward<NQ>(X, P, trig);
   for (int e = threadIdx.x; e < NN; e += blockDim.x) {
     if (WHAT == QSB_RUN_MATJAC) { out_u[2 * e] = X[e].x; out_u[2 * e + 1] = X[e].y; }
-    else { out_u[e] = X[e].x - (((e >> NQ) == (e & (N - 1))) ? 1.0 : 0.0); out_u[NN + e] = X[e].y; }
+    else { out_u[e] = X[e].x - ((e / N == e % N) ? 1.0 : 0.0); out_u[NN + e] = X[e].y; }
   }
   __syncthreads();  // X is about to be peeled by other threads
   for (int j = P.n_ops - 1; j >= 0; --j) {
     const qsb_op op = P.ops[j];
-    const double* tj = trig + j * QSB_TRIG_STRIDE;
+    const double* tj = trig + j * TS;
     const int np = qsb_num_params(op.opcode);
     if (np == 0 && j == 0) break;  // nothing left to differentiate
     qsb_apply_left<NQ>(X, op, tj, P.consts, true);  // X = R_j T^dagger
     __syncthreads();
     for (int k = 0; k < np; ++k) {
+      if constexpr (QsbDims<NQ>::TRIT) {  // Y = (dg (x) I) X for the 3x3 derivative, out of place
+        cplx dg3[9];
+        qsb_qutrit3x3(tj, 1 + k, dg3);
+        qsb_left_3x3<NQ>(Y, X, op.q0, dg3);
+      } else {
       cplx dg[4];
       qsb_gate2x2(op.opcode, tj, 1 + k, dg);
       if (qsb_is_rpp(op.opcode)) {  // Y = dR X = R(x + pi) X / 2, out of place
@@ -283,8 +356,10 @@ QSB_DEVICE void qsb_jac_instance(cplx* X, cplx* S, cplx* Y, double* trig, const 
           Y[r1 * N + c] = cfma(dg[3], xb, cmul(dg[2], xa));
         }
       }
+      }
       __syncthreads();
       double* o = out_j + (size_t)(op.param_off + k) * 2 * NN;
+      if constexpr (N % 2 == 0) {
       for (int pidx = threadIdx.x; pidx < NN / 2; pidx += blockDim.x) {  // K = S Y, two outputs per thread
         int i = pidx / (N / 2), c0 = 2 * (pidx % (N / 2));
         cplx acc0 = cmk(0, 0), acc1 = cmk(0, 0);
@@ -298,6 +373,16 @@ QSB_DEVICE void qsb_jac_instance(cplx* X, cplx* S, cplx* Y, double* trig, const 
         if (WHAT == QSB_RUN_MATJAC) { o[2 * e] = acc0.x; o[2 * e + 1] = acc0.y; o[2 * e + 2] = acc1.x; o[2 * e + 3] = acc1.y; }
         else { o[e] = acc0.x; o[e + 1] = acc1.x; o[NN + e] = acc0.y; o[NN + e + 1] = acc1.y; }
       }
+      } else {
+      for (int e = threadIdx.x; e < NN; e += blockDim.x) {  // odd N (qutrits): one output per thread
+        const int i = e / N, c = e % N;
+        cplx acc = cmk(0, 0);
+#pragma unroll 3
+        for (int m = 0; m < N; ++m) acc = cfma(S[i * N + m], Y[m * N + c], acc);
+        if (WHAT == QSB_RUN_MATJAC) { o[2 * e] = acc.x; o[2 * e + 1] = acc.y; }
+        else { o[e] = acc.x; o[NN + e] = acc.y; }
+      }
+      }
       __syncthreads();
     }
     if (j > 0) { qsb_apply_right<NQ>(S, op, tj, P.consts); __syncthreads(); }
@@ -307,7 +392,7 @@ QSB_DEVICE void qsb_jac_instance(cplx* X, cplx* S, cplx* Y, double* trig, const 
 
 template <int NQ, int WHAT>
 QSB_GLOBAL __launch_bounds__(QsbGeom<NQ>::T) qsb_k_jac(QsbBatchArgs a) {
-  constexpr int N = 1 << NQ, NN = N * N;
+  constexpr int N = QsbDims<NQ>::N, NN = N * N;
   QSB_DYN_SMEM(smem_raw);
   cplx* X = (cplx*)smem_raw;
   cplx* S = X + NN;
@@ -326,13 +411,14 @@ QSB_GLOBAL __launch_bounds__(QsbGeom<NQ>::T) qsb_k_jac(QsbBatchArgs a) {
 // comparison.py:37-55), S = sum(T o conj(U)), S_k = sum(T o conj(J_k)).
 // Adjoint sweep: S_k = conj(<L_j, (dg_k (x) I) R_j>) with L_j = (g_{M-1}..g_{j+1})^dagger T, R_j = g_{j-1}..g_0:
 // only structured one-qubit updates, no dense product.  Gradient is +inf when S == 0 (qsrs/src/utils.rs:144-146).
-// X, L: N*N tiles; red: 32 cplx; wpart: 96 cplx; acc: P cplx; all in shared memory.  grad may be shared or global.
+// X, L: N*N tiles; red: 32 cplx; wpart: QSB_HS_WPART cplx; acc: P cplx; all in shared memory.  grad may be shared or global.
+#define QSB_HS_WPART 256  // [8][32]: per-warp partial sums of up to 8 parameters of one op (qubit leaves use 3)
 template <int NQ>
 QSB_DEVICE double qsb_hs_instance(cplx* X, cplx* L, cplx* red, cplx* wpart, cplx* acc, double* trig,
                                   const QsbDevProgram& P, const double* x, const double* target, double* grad) {
-  constexpr int N = 1 << NQ, NN = N * N;
+  constexpr int N = QsbDims<NQ>::N, NN = N * N, TS = QsbDims<NQ>::TRIG, MAXNP = QsbDims<NQ>::MAXNP;
   __syncthreads();
-  qsb_fill_trig(P, x, trig);
+  qsb_fill_trig(P, x, trig, TS);
   qsb_load_init<NQ>(X, nullptr, false);
   qsb_load_init<NQ>(L, target, false);
   __syncthreads();
@@ -343,7 +429,7 @@ QSB_DEVICE double qsb_hs_instance(cplx* X, cplx* L, cplx* red, cplx* wpart, cplx
   const int w = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
   for (int j = P.n_ops - 1; j >= 0; --j) {
     const qsb_op op = P.ops[j];
-    const double* tj = trig + j * QSB_TRIG_STRIDE;
+    const double* tj = trig + j * TS;
     const int np = qsb_num_params(op.opcode);
     if (np == 0) {
       if (j == 0) break;
@@ -352,7 +438,40 @@ QSB_DEVICE double qsb_hs_instance(cplx* X, cplx* L, cplx* red, cplx* wpart, cplx
       __syncthreads();
       continue;
     }
-    cplx pk[3] = {cmk(0, 0), cmk(0, 0), cmk(0, 0)};
+    cplx pk[MAXNP];
+#pragma unroll
+    for (int k = 0; k < MAXNP; ++k) pk[k] = cmk(0, 0);
+    if constexpr (QsbDims<NQ>::TRIT) {
+      // single-qutrit leaf: peel X, correlate L with (dg_k (x) I) X for its eight parameters, peel L; every thread owns
+      // whole row triples, so no barrier is needed between the three steps
+      int s = 1;
+      for (int i = 0; i < QsbDims<NQ>::ND - 1 - op.q0; ++i) s *= 3;
+      cplx gd[9];
+      qsb_qutrit3x3(tj, 0, gd);
+      qsb_dagger3x3(gd);
+      for (int idx = threadIdx.x; idx < NN / 3; idx += blockDim.x) {
+        const int c = idx % N, tq = idx / N, r0 = (tq / s) * 3 * s + tq % s;
+        cplx xv[3], lv[3], rv[3];
+#pragma unroll
+        for (int i = 0; i < 3; ++i) { xv[i] = X[(r0 + i * s) * N + c]; lv[i] = L[(r0 + i * s) * N + c]; }
+#pragma unroll
+        for (int i = 0; i < 3; ++i) {
+          rv[i] = cfma(gd[3 * i + 2], xv[2], cfma(gd[3 * i + 1], xv[1], cmul(gd[3 * i], xv[0])));  // R_j triple
+          X[(r0 + i * s) * N + c] = rv[i];
+          L[(r0 + i * s) * N + c] = cfma(gd[3 * i + 2], lv[2], cfma(gd[3 * i + 1], lv[1], cmul(gd[3 * i], lv[0])));
+        }
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          cplx dg3[9];
+          qsb_qutrit3x3(tj, 1 + k, dg3);
+#pragma unroll
+          for (int i = 0; i < 3; ++i) {
+            const cplx y = cfma(dg3[3 * i + 2], rv[2], cfma(dg3[3 * i + 1], rv[1], cmul(dg3[3 * i], rv[0])));
+            pk[k] = cfma_conj(lv[i], y, pk[k]);
+          }
+        }
+      }
+    } else {
     if (qsb_is_rpp(op.opcode)) {  // two-qubit rotation: peel X, correlate L with dR X = R(x + pi) X / 2, peel L; pairs (k0, k0 ^ m0 ^ m1)
       const int m0 = 1 << (NQ - 1 - op.q0), m1 = 1 << (NQ - 1 - op.q1), sh0 = NQ - 1 - op.q0;
       const double c = tj[0], sn = tj[1];
@@ -389,7 +508,10 @@ QSB_DEVICE double qsb_hs_instance(cplx* X, cplx* L, cplx* red, cplx* wpart, cplx
       L[r1 * N + c] = cfma(gd[3], lb, cmul(gd[2], la));
     }
     }
-    for (int k = 0; k < np; ++k) {
+    }
+#pragma unroll
+    for (int k = 0; k < MAXNP; ++k) {
+      if (k >= np) break;
       for (int m = 16; m > 0; m >>= 1) {
         pk[k].x += __shfl_xor_sync(0xffffffffu, pk[k].x, m);
         pk[k].y += __shfl_xor_sync(0xffffffffu, pk[k].y, m);
@@ -417,13 +539,13 @@ QSB_DEVICE double qsb_hs_instance(cplx* X, cplx* L, cplx* red, cplx* wpart, cplx
 
 template <int NQ>
 QSB_GLOBAL __launch_bounds__(QsbGeom<NQ>::T) qsb_k_hs(QsbBatchArgs a) {
-  constexpr int N = 1 << NQ, NN = N * N;
+  constexpr int N = QsbDims<NQ>::N, NN = N * N;
   QSB_DYN_SMEM(smem_raw);
   cplx* X = (cplx*)smem_raw;
   cplx* L = X + NN;
   cplx* red = L + NN;           // 32
-  cplx* wpart = red + 32;       // [3][32]
-  cplx* acc = wpart + 96;       // [max_params]
+  cplx* wpart = red + 32;       // [8][32]
+  cplx* acc = wpart + QSB_HS_WPART;  // [max_params]
   const long long p_base = a.param_off[a.first];
   for (int li = blockIdx.x; li < a.count; li += gridDim.x) {
     const int inst = a.first + li;

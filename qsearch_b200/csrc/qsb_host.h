@@ -43,7 +43,9 @@ struct qsb_ctx {
 };
 
 struct qsb_program {
-  int n_qubits = 0, n_ops = 0, n_params = 0;
+  int n_qubits = 0, n_ops = 0, n_params = 0;   // n_qubits counts qudits of size radix
+  int radix = 2;
+  size_t dim = 0;                               // N = radix^n_qubits
   std::vector<qsb_op> ops;
   std::vector<double> consts;
   bool fast_ok = false;             // only U3/XZXZ/.../CONST1/CNOT ops: eligible for the register-tiled kernels
@@ -57,6 +59,8 @@ struct qsb_batch {
   qsb_ctx* ctx = nullptr;
   int slot = 0;
   int n_qubits = 0, n_instances = 0, n_programs = 0;
+  int radix = 2;
+  size_t dim = 0;                    // N = radix^n_qubits
   int max_ops = 0, max_params = 0;
   int max_pops = 0;                 // most ops with parameters in one program (snapshots of the body-frame LM's forward pass)
   bool fast_ok = false;
@@ -96,7 +100,7 @@ int qsb_buf_reserve(QsbBuf& b, size_t bytes);  // cudaMalloc-backed, for long-li
 int qsb_pool_alloc(const QsbDevice& d, void** out, size_t bytes);   // the device of d must be current
 void qsb_pool_free(const QsbDevice& d, void* p, size_t bytes);
 int qsb_pool_reserve(const QsbDevice& d, QsbBuf& b, size_t bytes);  // grow-only buffer on the pool
-bool qsb_target_is_unitary(const double* T, int n_qubits);
+bool qsb_target_is_unitary(const double* T, int dim);  // dim = N
 int qsb_fail(int code, const std::string& msg);
 int qsb_cuda_fail(cudaError_t e, const char* what);
 

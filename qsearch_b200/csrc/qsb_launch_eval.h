@@ -14,14 +14,16 @@ struct QsbLaunchShape {
   int ctas_per_sm;
 };
 
-static inline QsbLaunchShape qsb_shape_generic(int nq, int what, int max_ops, int max_params) {
-  const size_t NN = (size_t)1 << (2 * nq);
+// NQ: geometry code (qsb_generic.cuh)
+template <int NQ>
+static inline QsbLaunchShape qsb_shape_generic(int what, int max_ops, int max_params) {
+  const size_t NN = (size_t)QsbDims<NQ>::NN;
   QsbLaunchShape s;
-  s.threads = (int)std::max<size_t>(32, NN / 2);
-  const size_t trig = (size_t)max_ops * QSB_TRIG_STRIDE * sizeof(double);
+  s.threads = QsbGeom<NQ>::T;
+  const size_t trig = (size_t)max_ops * QsbDims<NQ>::TRIG * sizeof(double);
   switch (what) {
     case QSB_RUN_MATRIX: case QSB_RUN_DIST: s.smem = (NN + 32) * 16 + trig; break;
-    case QSB_RUN_HS: s.smem = (2 * NN + 32 + 96 + (size_t)max_params) * 16 + trig; break;
+    case QSB_RUN_HS: s.smem = (2 * NN + 32 + QSB_HS_WPART + (size_t)max_params) * 16 + trig; break;
     default: s.smem = 3 * NN * 16 + trig; break;
   }
   s.smem += 16;
@@ -32,7 +34,7 @@ static inline QsbLaunchShape qsb_shape_generic(int nq, int what, int max_ops, in
 
 template <int NQ>
 static int qsb_launch_generic_nq(qsb_batch* b, int what, const QsbBatchArgs& args, cudaStream_t st, int sm_count) {
-  QsbLaunchShape sh = qsb_shape_generic(NQ, what, b->max_ops, b->max_params);
+  QsbLaunchShape sh = qsb_shape_generic<NQ>(what, b->max_ops, b->max_params);
   if (sh.smem > 227 * 1024) return qsb_fail(QSB_ERR_UNSUPPORTED, "program too long for the shared-memory gate cache");
   int grid = std::max(1, std::min(args.count, sm_count * sh.ctas_per_sm));
   int rc = QSB_OK;
@@ -65,6 +67,14 @@ static int qsb_launch_generic_nq(qsb_batch* b, int what, const QsbBatchArgs& arg
 }
 
 static inline int qsb_launch_generic(qsb_batch* b, int what, const QsbBatchArgs& args, cudaStream_t st, int sm_count) {
+  if (b->radix == 3) {
+    switch (b->n_qubits) {
+      case 1: return qsb_launch_generic_nq<QSB_GEOM_QUTRIT + 1>(b, what, args, st, sm_count);
+      case 2: return qsb_launch_generic_nq<QSB_GEOM_QUTRIT + 2>(b, what, args, st, sm_count);
+      case 3: return qsb_launch_generic_nq<QSB_GEOM_QUTRIT + 3>(b, what, args, st, sm_count);
+      default: return qsb_fail(QSB_ERR_UNSUPPORTED, "unsupported qutrit count");
+    }
+  }
   switch (b->n_qubits) {
     case 1: return qsb_launch_generic_nq<1>(b, what, args, st, sm_count);
     case 2: return qsb_launch_generic_nq<2>(b, what, args, st, sm_count);
@@ -97,7 +107,7 @@ static int qsb_launch_warp_kernel(const QsbBatchArgs& args, cudaStream_t st, int
 }
 
 static inline bool qsb_warp_path(const qsb_batch* b, int what) {
-  return b->fast_ok && !b->force_generic && b->n_qubits >= 3 &&
+  return b->fast_ok && !b->force_generic && b->radix == 2 && b->n_qubits >= 3 &&
          (what == QSB_RUN_MATJAC || what == QSB_RUN_RESID || what == QSB_RUN_HS);
 }
 

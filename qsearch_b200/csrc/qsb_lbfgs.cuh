@@ -5,9 +5,10 @@
 #pragma once
 #include "qsb_solver.cuh"
 
-static inline size_t qsb_lbfgs_smem_bytes(int nq, int max_ops, int max_params, int mem) {
-  const size_t NN = (size_t)1 << (2 * nq), P = (size_t)max_params;
-  return (2 * NN + 32 + 96 + P) * 16 + (size_t)max_ops * QSB_TRIG_STRIDE * 8 + (5 * P + 2 * (size_t)mem * P + 2 * (size_t)mem) * 8 + 64;
+// nn = N^2, trig = QsbDims::TRIG of the geometry
+static inline size_t qsb_lbfgs_smem_bytes(size_t nn, int trig, int max_ops, int max_params, int mem) {
+  const size_t P = (size_t)max_params;
+  return (2 * nn + 32 + QSB_HS_WPART + P) * 16 + (size_t)max_ops * trig * 8 + (5 * P + 2 * (size_t)mem * P + 2 * (size_t)mem) * 8 + 64;
 }
 
 QSB_DEVICE double qsb_dot(const double* u, const double* v, int P, cplx* red) {
@@ -20,9 +21,9 @@ QSB_DEVICE double qsb_dot(const double* u, const double* v, int P, cplx* red) {
 template <int NQ>
 QSB_DEVICE double qsb_hs_value_at(cplx* X, double* trig, const QsbDevProgram& P, const double* x, const double* target,
                                   cplx* red) {
-  constexpr int N = 1 << NQ, NN = N * N;
+  constexpr int N = QsbDims<NQ>::N, NN = N * N;
   __syncthreads();
-  qsb_fill_trig(P, x, trig);
+  qsb_fill_trig(P, x, trig, QsbDims<NQ>::TRIG);
   qsb_load_init<NQ>(X, nullptr, false);
   __syncthreads();
   qsb_forward<NQ>(X, P, trig);
@@ -37,15 +38,15 @@ QSB_DEVICE double qsb_hs_value_at(cplx* X, double* trig, const QsbDevProgram& P,
 
 template <int NQ>
 QSB_GLOBAL __launch_bounds__(QsbGeom<NQ>::T) qsb_k_lbfgs(QsbSolveArgs a) {
-  constexpr int N = 1 << NQ, NN = N * N;
+  constexpr int N = QsbDims<NQ>::N, NN = N * N;
   QSB_DYN_SMEM(smem_raw);
   cplx* X = (cplx*)smem_raw;
   cplx* L = X + NN;
   cplx* red = L + NN;
   cplx* wpart = red + 32;
-  cplx* acc = wpart + 96;
+  cplx* acc = wpart + QSB_HS_WPART;
   double* trig = (double*)(acc + a.max_params);
-  double* x = trig + (size_t)a.max_ops * QSB_TRIG_STRIDE;
+  double* x = trig + (size_t)a.max_ops * QsbDims<NQ>::TRIG;
   double* g = x + a.max_params;
   double* xn = g + a.max_params;
   double* gn = xn + a.max_params;

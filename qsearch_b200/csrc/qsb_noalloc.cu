@@ -154,7 +154,7 @@ extern "C" int qsb_eval_lm_system_static(qsb_ctx* ctx, int device_slot, const qs
     const size_t NN = (size_t)1 << (2 * prog->n_qubits);
     QSB_CUDA(cudaMemcpyAsync(t_host, target, 2 * NN * 8, cudaMemcpyDefault, d.stream));
     QSB_CUDA(cudaStreamSynchronize(d.stream));
-    if (!qsb_target_is_unitary(t_host, prog->n_qubits))
+    if (!qsb_target_is_unitary(t_host, (int)prog->dim))
       return qsb_fail(QSB_ERR_UNSUPPORTED, "qsb_eval_lm_system_static needs a unitary target (use qsb_batch_run(QSB_RUN_LMSYS) otherwise)");
   }
   switch (prog->n_qubits) {

@@ -76,9 +76,8 @@ static int launch_solver_nq(const SolveJob& job, qsb_batch* b, QsbSolveArgs& arg
     args.cluster = csize;
     per_cta = (maxP + 1) * 2 * NN + 2 * (maxP + 1) * (maxP + 1) + (args.chol_smem ? 0 : (size_t)csize * (maxP + 1) * (maxP + 1));
   } else {
-    const size_t nb = (maxP + 1 + 3) / 4;
-    smem = (3 * NN + 32) * 16 + 7 * maxP * 8 + (size_t)b->max_ops * QSB_TRIG_STRIDE * 8 + 4 * nb * (QSB_SYRK_MC + 1) * 8 + 64;
-    per_cta = (maxP + 1) * 2 * NN + (maxP + 1) * (maxP + 1) + maxP * maxP;
+    smem = qsb_lm_smem_bytes(NN, QsbDims<NQ>::TRIG, b->max_ops, maxP);
+    per_cta = qsb_lm_scratch_doubles(NN, maxP);
   }
   if (smem > 227 * 1024) return qsb_fail(QSB_ERR_UNSUPPORTED, "circuit too large for the solver's shared-memory working set");
   int rc = QSB_OK;
@@ -142,7 +141,7 @@ static int launch_solver_nq(const SolveJob& job, qsb_batch* b, QsbSolveArgs& arg
     threads = 32 * ((1 << NQ) / 8);  // one warp per 8-column block
     smem = qsb_lbfgs2_smem_bytes(NQ, b->max_ops, b->max_params, mem);
   } else {
-    smem = qsb_lbfgs_smem_bytes(NQ, b->max_ops, b->max_params, mem);
+    smem = qsb_lbfgs_smem_bytes(NN, QsbDims<NQ>::TRIG, b->max_ops, b->max_params, mem);
   }
   if (smem > 227 * 1024) return qsb_fail(QSB_ERR_UNSUPPORTED, "circuit too large for the solver's shared-memory working set");
   int rc = QSB_OK;
@@ -168,6 +167,42 @@ static int launch_solver_nq(const SolveJob& job, qsb_batch* b, QsbSolveArgs& arg
     if ((rc = qsb_prepare_kernel(qsb_k_lbfgs<NQ>, smem))) return rc;
     QSB_LAUNCH((qsb_k_lbfgs<NQ>), grid, threads, smem, d.stream, args);
   }
+  QSB_CUDA(cudaGetLastError());
+  return QSB_OK;
+}
+#endif
+
+#if QSB_SOLVE_TU < 2
+// Interpreter solver kernels for a geometry code GQ (qsb_generic.cuh): the radix-3 programs, which have no warp kernels
+template <int GQ>
+static int launch_solver_interp(const SolveJob& job, qsb_batch* b, QsbSolveArgs& args, const QsbDevice& d) {
+  const size_t NN = (size_t)QsbDims<GQ>::NN, maxP = (size_t)b->max_params;
+  const int threads = QsbGeom<GQ>::T;
+#if QSB_SOLVE_TU == 0
+  const size_t smem = qsb_lm_smem_bytes(NN, QsbDims<GQ>::TRIG, b->max_ops, maxP);
+  size_t per_cta = qsb_lm_scratch_doubles(NN, maxP);
+#else
+  const int mem = job.opts.lbfgs_memory > 0 ? job.opts.lbfgs_memory : 10;
+  const size_t smem = qsb_lbfgs_smem_bytes(NN, QsbDims<GQ>::TRIG, b->max_ops, b->max_params, mem);
+  size_t per_cta = 2;
+#endif
+  if (smem > 227 * 1024) return qsb_fail(QSB_ERR_UNSUPPORTED, "circuit too large for the solver's shared-memory working set");
+  per_cta = (per_cta + 1) & ~(size_t)1;
+  const int by_threads = 2048 / threads, by_smem = (int)((size_t)220 * 1024 / smem);
+  const int ctas = std::max(1, std::min(std::min(by_threads, by_smem), 16));
+  const int grid = std::max(1, std::min(args.count, d.sm_count * ctas));
+  QsbBuf& scratch = job.ctx->devs[b->slot].solve_scratch;
+  int rc = qsb_buf_reserve(scratch, (size_t)grid * per_cta * sizeof(double));
+  if (rc) return rc;
+  args.scratch = (double*)scratch.p;
+  args.scratch_per_cta = per_cta;
+#if QSB_SOLVE_TU == 0
+  if ((rc = qsb_prepare_kernel(qsb_k_lm<GQ>, smem))) return rc;
+  QSB_LAUNCH((qsb_k_lm<GQ>), grid, threads, smem, d.stream, args);
+#else
+  if ((rc = qsb_prepare_kernel(qsb_k_lbfgs<GQ>, smem))) return rc;
+  QSB_LAUNCH((qsb_k_lbfgs<GQ>), grid, threads, smem, d.stream, args);
+#endif
   QSB_CUDA(cudaGetLastError());
   return QSB_OK;
 }
@@ -224,6 +259,14 @@ static int solve_shard(const SolveJob& job, int slot, int i0, int i1, const std:
   if (getenv("QSB_LM_PROFILE")) {
     if (cudaMalloc((void**)&d_prof, 12 * sizeof(long long)) == cudaSuccess) { cudaMemset(d_prof, 0, 12 * sizeof(long long)); args.prof = d_prof; }
   }
+  if (b->radix == 3) {
+    switch (b->n_qubits) {
+      case 1: rc = launch_solver_interp<QSB_GEOM_QUTRIT + 1>(job, b, args, d); break;
+      case 2: rc = launch_solver_interp<QSB_GEOM_QUTRIT + 2>(job, b, args, d); break;
+      case 3: rc = launch_solver_interp<QSB_GEOM_QUTRIT + 3>(job, b, args, d); break;
+      default: rc = qsb_fail(QSB_ERR_UNSUPPORTED, "unsupported qutrit count");
+    }
+  } else
   switch (b->n_qubits) {
     case 1: rc = launch_solver_nq<1>(job, b, args, d); break;
     case 2: rc = launch_solver_nq<2>(job, b, args, d); break;
@@ -274,7 +317,7 @@ static int solve_dispatch(SolveJob job) {
   }
   poff[job.n_instances] = off;
   if (off > 0 && (!job.x0 || !job.out_x)) return qsb_fail(QSB_ERR_INVALID, "x0 / out_x is NULL");
-  job.target_unitary = job.method == QSB_SOLVE_LM && qsb_target_is_unitary(job.target, job.progs[0]->n_qubits);
+  job.target_unitary = job.method == QSB_SOLVE_LM && qsb_target_is_unitary(job.target, (int)job.progs[0]->dim);
   const int used = std::min((int)job.ctx->devs.size(), job.n_instances);
   if (used == 1) return solve_shard(job, 0, 0, job.n_instances, poff);
   // Contiguous shards of equal COST, not equal count: an LM iteration is dominated by the Gram

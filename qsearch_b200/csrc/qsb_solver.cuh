@@ -61,15 +61,15 @@ QSB_DEVICE double qsb_block_max(double v, cplx* red) {
 template <int NQ>
 QSB_DEVICE double qsb_half_norm_at(cplx* X, double* trig, const QsbDevProgram& P, const double* x, const double* target,
                                    cplx* red) {
-  constexpr int N = 1 << NQ, NN = N * N;
+  constexpr int N = QsbDims<NQ>::N, NN = N * N;
   __syncthreads();
-  qsb_fill_trig(P, x, trig);
+  qsb_fill_trig(P, x, trig, QsbDims<NQ>::TRIG);
   qsb_load_init<NQ>(X, target, true);
   __syncthreads();
   qsb_forward<NQ>(X, P, trig);
   cplx part = cmk(0, 0);
   for (int e = threadIdx.x; e < NN; e += blockDim.x) {
-    double re = X[e].x - (((e >> NQ) == (e & (N - 1))) ? 1.0 : 0.0), im = X[e].y;
+    double re = X[e].x - ((e / N == e % N) ? 1.0 : 0.0), im = X[e].y;
     part.x = fma(re, re, part.x);
     part.x = fma(im, im, part.x);
   }
@@ -167,9 +167,18 @@ QSB_DEVICE void qsb_chol_solve(const double* L, int P, double* b, double* y, dou
   __syncthreads();
 }
 
+// shared memory of qsb_k_lm (bytes) and its scratch per CTA (doubles); nn = N^2, trig = QsbDims::TRIG
+static inline size_t qsb_lm_smem_bytes(size_t nn, int trig, int max_ops, size_t maxP) {
+  const size_t nb = (maxP + 1 + 3) / 4;
+  return (3 * nn + 32) * 16 + 7 * maxP * 8 + (size_t)max_ops * trig * 8 + 4 * nb * (QSB_SYRK_MC + 1) * 8 + 64;
+}
+static inline size_t qsb_lm_scratch_doubles(size_t nn, size_t maxP) {
+  return (maxP + 1) * 2 * nn + (maxP + 1) * (maxP + 1) + maxP * maxP;
+}
+
 template <int NQ>
 QSB_GLOBAL __launch_bounds__(QsbGeom<NQ>::T) qsb_k_lm(QsbSolveArgs a) {
-  constexpr int N = 1 << NQ, NN = N * N, M = 2 * NN;
+  constexpr int N = QsbDims<NQ>::N, NN = N * N, M = 2 * NN;
   QSB_DYN_SMEM(smem_raw);
   cplx* X = (cplx*)smem_raw;
   cplx* S = X + NN;
@@ -183,7 +192,7 @@ QSB_GLOBAL __launch_bounds__(QsbGeom<NQ>::T) qsb_k_lm(QsbSolveArgs a) {
   double* wk = d2 + a.max_params;   // work vector (rhs / column buffer)
   double* wy = wk + a.max_params;   // work vector
   double* trig = wy + a.max_params;
-  double* tile = trig + (size_t)a.max_ops * QSB_TRIG_STRIDE;
+  double* tile = trig + (size_t)a.max_ops * QsbDims<NQ>::TRIG;
   double* Rg = a.scratch + (size_t)blockIdx.x * a.scratch_per_cta;
   for (int inst = blockIdx.x; inst < a.count; inst += gridDim.x) {
     const QsbDevProgram prog = a.progs[a.prog_idx[inst]];

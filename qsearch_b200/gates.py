@@ -13,7 +13,7 @@ Constant gates carry their (tiny) constant matrix as data for the lowering's con
 import numpy as np
 from hashlib import md5
 
-from . import unitaries
+from . import unitaries, utils
 
 
 class Gate:
@@ -117,7 +117,8 @@ class U1Gate(_Param1Q):
 
 
 class SingleQutritGate(Gate):
-    """Structure-only placeholder: qutrit gates (d = 3) are rejected by the lowering (v1 scope)."""
+    """Arbitrary single-qutrit gate: three angles and five phases (reference: gates.py:411-523).  Lowered to one
+    QSB_OP_QUTRIT1 op of a radix-3 program."""
     num_inputs = 8
     qudits = 1
 
@@ -148,6 +149,60 @@ class IdentityGate(_Const):
 
 class SXGate(_Const):
     _const = unitaries.sqrt_x
+
+
+# ---------------------------------------------------------------------------- two-qutrit constants (d = 3)
+def _perm9(images):
+    """9x9 permutation matrix with M[images[j], j] = 1."""
+    M = np.zeros((9, 9), dtype="complex128")
+    for j, i in enumerate(images):
+        M[i, j] = 1.0
+    return M
+
+
+class CSUMGate(_Const):
+    """The reference's CSUM constant (gates.py:525-549): control 1 cycles the target b -> b + 1 mod 3, control 2 exchanges
+    its levels 0 and 1 (the matrix as the reference defines it, not the textbook |a, a + b>)."""
+    qudits = 2
+    _const = _perm9([0, 1, 2, 4, 5, 3, 7, 6, 8])
+
+
+class CPIGate(_Const):
+    """Exchanges |1,0> and |1,1> (reference: gates.py:551-575)."""
+    qudits = 2
+    _const = _perm9([0, 1, 2, 4, 3, 5, 6, 7, 8])
+
+
+class CPIPhaseGate(_Const):
+    """CPI with a sign on |1,0> -> |1,1> and five random phases on the last five basis states, drawn when the gate is
+    made (reference: gates.py:577-602; like there, every instance has its own phases and ``repr`` does not show them)."""
+    qudits = 2
+
+    def __init__(self):
+        M = _perm9([0, 1, 2, 4, 3, 5, 6, 7, 8])
+        M[3, 4] = -1.0
+        phases = np.concatenate([np.ones(4), np.exp(2j * np.pi * np.random.random(5))])
+        self._const = M @ np.diag(phases)
+
+
+class UpgradedConstantGate(_Const):
+    """A constant gate of a smaller qudit size acting on the low levels of larger qudits, identity elsewhere
+    (reference: gates.py:761-788; the embedding is utils.upgrade_qudits)."""
+
+    def __init__(self, other, df=3):
+        if other.num_inputs > 0:
+            raise AttributeError("UpgradedConstantGate is designed for only constant gates")
+        OU = np.asarray(other.const_matrix() if hasattr(other, "const_matrix") else other.matrix([]), dtype="complex128")
+        di = int(round(OU.shape[0] ** (1.0 / other.qudits)))
+        if df <= di:
+            raise AttributeError("Gate cannot be upgraded because it is already of an equal or higher dit level")
+        self.df = df
+        self.qudits = other.qudits
+        self.subgate = other
+        self._const = utils.upgrade_qudits(OU, di, df)
+
+    def __repr__(self):
+        return "UpgradedConstantGate({}, df={})".format(repr(self.subgate), self.df)
 
 
 class _Param2Q(Gate):

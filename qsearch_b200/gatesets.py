@@ -5,7 +5,7 @@ Host-side structure only; mirrors the interface of qsearch/gatesets.py (`initial
 gate programs - are identical to the reference's.
 """
 from .gates import (CNOTGate, CZGate, ISwapGate, XXGate, IdentityGate, KroneckerGate, NonadjacentCNOTGate,
-                    ProductGate, U3Gate, XZXZGate, ZXZXZGate)
+                    ProductGate, U3Gate, XZXZGate, ZXZXZGate, SingleQutritGate, CPIPhaseGate, UpgradedConstantGate)
 
 
 def fill_row(gate, n):
@@ -177,5 +177,35 @@ class QubitCNOTAdjacencyList(Gateset):
         return layers
 
 
+class QutritCPIPhaseLinear(Gateset):
+    """Single-qutrit gates and CPIPhase on adjacent pairs (reference: gatesets.py:283-293).  As in the reference, every call
+    of ``search_layers`` makes a new CPIPhaseGate, i.e. draws new phases."""
+    d = 3
+
+    def __init__(self):
+        self.single_gate = SingleQutritGate()
+
+    def initial_layer(self, n):
+        return fill_row(self.single_gate, n)
+
+    def search_layers(self, n):
+        return linear_topology(CPIPhaseGate(), self.single_gate, n, self.d)
+
+
+class QutritCNOTLinear(Gateset):
+    """Single-qutrit gates and the qubit CNOT embedded in two qutrits (reference: gatesets.py:295-305)."""
+    d = 3
+
+    def __init__(self):
+        self.single_gate = SingleQutritGate()
+
+    def initial_layer(self, n):
+        return fill_row(self.single_gate, n)
+
+    def search_layers(self, n):
+        return linear_topology(UpgradedConstantGate(CNOTGate()), self.single_gate, n, self.d)
+
+
 DefaultQubit = QubitCNOTLinear
+DefaultQutrit = QutritCPIPhaseLinear
 Default = DefaultQubit

@@ -25,7 +25,8 @@ def _num_devices():
 def _branching(opts):
     import math
     try:
-        return max(1, opts.gateset.branching_factor(int(round(math.log2(opts.target.shape[0])))))
+        d = getattr(opts.gateset, "d", 2)
+        return max(1, opts.gateset.branching_factor(int(round(math.log(opts.target.shape[0]) / math.log(d)))))
     except Exception:
         return 1
 

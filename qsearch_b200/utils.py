@@ -11,6 +11,24 @@ def nearest_unitary(A):
     return V @ Wh
 
 
+def upgrade_qudits(U, di=2, df=3):
+    """Embed a unitary on qudits of size di into qudits of size df: it acts on the basis states whose digits are all
+    below di (same digits, read in base di) and as the identity on the rest (qsearch/utils.py:205-230)."""
+    U = np.asarray(U, dtype="complex128")
+    qudits = int(round(np.log(U.shape[0]) / np.log(di)))
+    big = np.eye(df ** qudits, dtype="complex128")
+    idx = np.arange(df ** qudits)
+    digits = np.stack([(idx // df ** k) % df for k in range(qudits)])  # least significant first
+    low = np.all(digits < di, axis=0)
+    old = np.sum(digits * (di ** np.arange(qudits))[:, None], axis=0)
+    rows = idx[low]
+    big[np.ix_(rows, rows)] = U[np.ix_(old[low], old[low])]
+    return big
+
+
+upgrade_dits = upgrade_qudits
+
+
 class Logger:
     """Minimal stand-in for qsearch/logging.py:8-24."""
 

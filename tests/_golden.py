@@ -20,7 +20,13 @@ class Case:
     def __init__(self, blob, i):
         pre = "c{}_".format(i)
         self.repr = str(blob[pre + "repr"])
-        self.circuit = rebuild(self.repr)
+        if pre + "seed" in blob.files:  # a circuit with a CPIPhaseGate: its phases come from np.random (make_golden_qutrit.py)
+            state = np.random.get_state()
+            np.random.seed(int(blob[pre + "seed"]))
+            self.circuit = rebuild(self.repr)
+            np.random.set_state(state)
+        else:
+            self.circuit = rebuild(self.repr)
         self.xs = blob[pre + "x"]
         self.targets = {k[len(pre) + 2:]: blob[k] for k in blob.files if k.startswith(pre + "T_")}
         self.samples = []
@@ -41,4 +47,4 @@ def proj_weights(n):
     return np.random.default_rng(7).standard_normal(n)
 
 
-ALL_FILES = ["gates_small", "gateset_layers", "microbench", "leap_long"]
+ALL_FILES = ["gates_small", "gateset_layers", "microbench", "leap_long", "qutrit"]

@@ -16,7 +16,7 @@ def check_fixture_case(lib, case, tol=TOL):
     xs = np.asarray(case.xs, dtype="float64")
     U = lib.eval_matrix([gp], poi, xs)
     U2, J = lib.eval_mat_jac([gp], poi, xs)
-    P, N = gp.n_params, 1 << gp.n_qubits
+    P, N = gp.n_params, gp.dim
     J = J.reshape(n, P, N, N)
     for s, gold in enumerate(case.samples):
         assert np.abs(U[s] - gold["U"]).max() < tol
@@ -57,7 +57,7 @@ def check_against_oracle(lib, circuits, xs_per_circuit, T, tol=TOL):
             poi.append(ci)
             params.append(np.asarray(x, dtype="float64"))
     flat = np.concatenate(params) if params else np.zeros(0)
-    N = 1 << gps[0].n_qubits
+    N = gps[0].dim
     U = lib.eval_matrix(gps, poi, flat)
     U2, J = lib.eval_mat_jac(gps, poi, flat)
     f, g = lib.eval_hs_grad(gps, poi, flat, T)

@@ -84,6 +84,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--reps3", type=int, default=10)
     ap.add_argument("--reps4", type=int, default=3)
+    ap.add_argument("--repsq", type=int, default=3)
     ap.add_argument("--only", default="")
     a = ap.parse_args()
     only = set(x for x in a.only.split(",") if x)
@@ -94,6 +95,18 @@ def main():
         runs = db["runs"].setdefault(name, [])
         while len(runs) < a.reps3:
             r = one(SearchCompiler, U, {"gateset": gs()}, 1000 + len(runs))
+            runs.append(r)
+            save(db)
+            print(name, r, flush=True)
+    # two qutrits, the targets of examples/qutrit_csum.py with its QutritCNOTLinear gateset ("cnots" = two-qutrit gates)
+    qt = {"qt_csum": gates.CSUMGate().matrix([]), "qt_bswap": utils.upgrade_qudits(unitaries.swap),
+          "qt_tswap": unitaries.general_swap(3), "qt_qft2": unitaries.qft(9)}
+    for name, U in qt.items():
+        if name not in only:  # only on request: minutes to hours each
+            continue
+        runs = db["runs"].setdefault(name, [])
+        while len(runs) < a.repsq:
+            r = one(SearchCompiler, U, {"gateset": gatesets.QutritCNOTLinear()}, 3000 + len(runs))
             runs.append(r)
             save(db)
             print(name, r, flush=True)

@@ -8,7 +8,7 @@ from tests import _golden, _parity
 from tests.emu import emulated_library
 
 
-@pytest.mark.parametrize("fname,stride", [("gates_small", 1), ("gateset_layers", 3), ("microbench", 4), ("leap_long", 2)])
+@pytest.mark.parametrize("fname,stride", [("gates_small", 1), ("gateset_layers", 3), ("microbench", 4), ("leap_long", 2), ("qutrit", 1)])
 def test_emulated_kernels_match_reference_fixtures(fname, stride):
     lib = emulated_library()
     cases = _golden.load(fname)
@@ -39,8 +39,17 @@ def test_bad_programs_are_rejected():
     bad.ops["q0"][1] = 7
     with pytest.raises(_lib.QsbError):
         lib.eval_matrix([bad], [0], np.zeros(6))
-    with pytest.raises(ValueError):
-        lowering.lower(gates.SingleQutritGate())
+    with pytest.raises(ValueError):  # qubit and qutrit leaves in one tree
+        lowering.lower(gates.KroneckerGate(gates.SingleQutritGate(), gates.U3Gate()))
+    with pytest.raises(ValueError):  # more qutrits than the interpreter's tiles hold
+        lowering.lower(gates.KroneckerGate(*[gates.SingleQutritGate()] * 4))
+    q3 = lowering.lower(gates.SingleQutritGate())
+    assert (q3.radix, q3.dim, q3.n_params) == (3, 3, 8)
+    as_qubits = lowering.GateProgram(q3.n_qubits, q3.n_params, q3.ops, q3.consts)  # radix 2: QUTRIT1 is not a qubit op
+    with pytest.raises(_lib.QsbError):
+        lib.eval_matrix([as_qubits], [0], np.zeros(8))
+    with pytest.raises(_lib.QsbError):  # one batch, two radices
+        lib.eval_matrix([gp, q3], [0, 1], np.zeros(14))
     with pytest.raises(ValueError):
         lib.eval_matrix([gp], [0], np.zeros(5))
 
@@ -310,3 +319,30 @@ def test_tf32_gram_option_of_the_lm_kernel(n):
     assert f.min() < 1e-12
     for k, xk in enumerate(x.reshape(4, -1)):
         assert abs(O.matrix_distance_squared(T, O.matrix(c, xk)) - f[k]) < 1e-12
+
+
+def test_solvers_on_qutrit_circuits():
+    """SURVEY 8f rank 4 (qutrit leaves, gates.py:411-602): both solvers on a reachable two-qutrit target of the
+    QutritCNOTLinear gateset (gatesets.py:295-305), through the radix-3 interpreter kernels."""
+    from oracle import qs_oracle as O
+    from qsearch_b200 import gatesets, lowering
+    lib = emulated_library()
+    gs = gatesets.QutritCNOTLinear()
+    c = gatesets.ProductGate(gs.initial_layer(2)).appending(gs.search_layers(2)[0][0])
+    rng = np.random.default_rng(11)
+    x_star = rng.random(c.num_inputs) * 2 * np.pi
+    T = O.matrix(c, x_star)
+    gp = lowering.lower(c)
+    assert (gp.radix, gp.dim, gp.n_params) == (3, 9, 32)
+    x0 = x_star + 0.2 * rng.standard_normal((3, gp.n_params))
+    for method in ("lm", "lbfgs"):
+        x, f, iters, status = lib.solve(method, [gp], np.zeros(3, dtype="int32"), x0, T, max_iters=400 if method == "lbfgs" else 0)
+        assert f.min() < (1e-10 if method == "lm" else 1e-6), (method, f)
+        k = int(np.argmin(f))
+        assert abs(O.matrix_distance_squared(T, O.matrix(c, x.reshape(3, -1)[k])) - f[k]) < 1e-12
+    with pytest.raises(Exception):  # the LM-system run kind belongs to the qubit warp kernels
+        b = lib.batch([gp], [0])
+        try:
+            b.set_params(x0[0]); b.set_target(T); b.run(6)
+        finally:
+            b.close()

@@ -363,3 +363,67 @@ def test_tf32_gram_option_of_the_lm_kernel(lib, n):
     f64 = lib.solve("lm", [gp], poi, x0, Tq)[1]
     f32 = lib.solve("lm", [gp], poi, x0, Tq, gram_tf32=1.0)[1]
     assert f32.min() < f64.min() + 1e-4 and np.median(f32) < np.median(f64) + 1e-2
+
+
+# ---------------------------------------------------------------------------- qutrits (gates.py:411-602)
+def _qutrit_gate_list():
+    sq, i3 = gates.SingleQutritGate(), gates.IdentityGate(d=3)
+    ucnot = gates.UpgradedConstantGate(gates.CNOTGate())
+    return [sq, gates.ProductGate(sq, sq), gates.KroneckerGate(sq, sq), gates.KroneckerGate(sq, gates.CPIGate()),
+            gates.ProductGate(gates.KroneckerGate(sq, sq), gates.CSUMGate(), gates.KroneckerGate(sq, sq)),
+            gates.ProductGate(gates.KroneckerGate(sq, sq, sq), gates.KroneckerGate(gates.ProductGate(ucnot, gates.KroneckerGate(sq, sq)), i3))]
+
+
+@pytest.mark.parametrize("gate", _qutrit_gate_list(), ids=lambda g: repr(g)[:40])
+def test_qutrit_backend_matches_oracle_and_finite_differences(lib, gate):
+    """The d = 3 entries of the reference's backend tests (tests/test_circuit.py:36,41, tests/test_gradients.py:25) through the
+    radix-3 interpreter kernels: matrix / mat_jac against the oracle, mat_jac against central differences."""
+    circ = CudaBackend().prepare_circuit(gate)
+    assert circ.program.radix == 3 and circ.program.dim == 3 ** gate.qudits
+    rng = np.random.default_rng(5)
+    P = gate.num_inputs
+    for _ in range(5):
+        v = rng.random(P) * 2 * np.pi
+        U, J = circ.mat_jac(v)
+        Uo, Jo = O.mat_jac(gate, v)
+        assert np.abs(circ.matrix(v) - Uo).max() < 1e-12 and np.abs(U - Uo).max() < 1e-12
+        assert len(J) == len(Jo) == P
+        assert np.abs(J - np.array(Jo)).max() < 1e-12
+        eps = 1e-5
+        Us = circ.matrix_batch(np.concatenate([v + eps * np.eye(P), v - eps * np.eye(P)]))
+        assert np.abs((Us[:P] - Us[P:]) / (2 * eps) - J).sum(axis=(1, 2)).max() < 1e-7
+
+
+@pytest.mark.parametrize("n", [1, 2, 3])
+def test_qutrit_ragged_batches_against_oracle(lib, n):
+    """Several structures of different depth in one batch, every run kind, against the oracle; then a batch large enough to
+    fill the GPU several times over, checked through unitarity and agreement with the small batch."""
+    rng = np.random.default_rng(60 + n)
+    sq = gates.SingleQutritGate()
+    if n == 1:
+        circuits = [sq, gates.ProductGate(sq, sq), gates.ProductGate(sq, sq, sq)]
+    else:
+        gs = gatesets.QutritCNOTLinear()
+        layers = gs.search_layers(n)
+        c0 = gates.ProductGate(gs.initial_layer(n))
+        circuits = [c0]
+        for k in range(3):
+            circuits.append(circuits[-1].appending(layers[k % len(layers)][0]))
+        np.random.seed(9)
+        circuits.append(c0.appending(gatesets.QutritCPIPhaseLinear().search_layers(n)[-1][0]))
+    N = 3 ** n
+    T = workloads.haar_unitary(N, 77 + n)
+    xs = [rng.random((2, c.num_inputs)) * 2 * np.pi for c in circuits]
+    xs[0][1, :] = 0.0
+    assert _parity.check_against_oracle(lib, circuits, xs, T) == 2 * len(circuits)
+    c = circuits[-1]
+    gp = lowering.lower(c)
+    K = 3000
+    V = rng.random((K, gp.n_params)) * 2 * np.pi
+    V[:2] = xs[-1]
+    U = lib.eval_matrix([gp], np.zeros(K, dtype="int32"), V)
+    assert np.abs(U @ U.conj().transpose(0, 2, 1) - np.eye(N)).max() < 1e-12
+    f, g = lib.eval_hs_grad([gp], np.zeros(K, dtype="int32"), V, T)
+    f2, g2 = lib.eval_hs_grad([gp], np.zeros(2, dtype="int32"), V[:2], T)
+    assert np.array_equal(f[:2], f2) and np.array_equal(g.reshape(K, -1)[:2], g2.reshape(2, -1))
+    assert np.abs(f - (1 - np.abs(np.einsum("kij,ij->k", U, T.conj())) / N)).max() < 1e-12

@@ -120,3 +120,51 @@ def test_leap_reoptimizing_post_processor_on_the_device():
         padded, q.Options(target=T, seed=4, gateset=g, reoptimize_size=5))
     assert cnots(out["structure"]) < 12
     assert O.matrix_distance_squared(T, O.matrix(out["structure"], out["parameters"])) < 1e-10
+
+
+# ---------------------------------------------------------------------------- qutrits (gatesets.py:283-305)
+@pytest.mark.parametrize("method", ["lm", "lbfgs"])
+def test_qutrit_solvers_on_reachable_targets(method):
+    lib = _lib.get_library()
+    rng = np.random.default_rng(43)
+    for n, depth in [(2, 3), (3, 2)]:
+        g = gatesets.QutritCNOTLinear()
+        layers = g.search_layers(n)
+        c = gates.ProductGate(g.initial_layer(n))
+        for _ in range(depth):
+            c = c.appending(layers[int(rng.integers(len(layers)))][0])
+        x_star = rng.random(c.num_inputs) * 2 * np.pi
+        T = O.matrix(c, x_star)
+        gp = lowering.lower(c)
+        K = 16
+        # starts near the solution: from uniform random starts these landscapes trap LM in local minima (scipy's LM on the
+        # oracle ends at 1e-3..1e-1 from the same starts), which is why the reference pairs this gateset with its multistart solver
+        # (examples/qutrit_csum.py:18)
+        x0 = x_star + 0.15 * rng.standard_normal((K, gp.n_params))
+        x, f, iters, status = lib.solve(method, [gp], np.zeros(K, dtype="int32"), x0, T)
+        assert f.min() < (1e-10 if method == "lm" else 1e-8), (n, method, f)
+        k = int(np.argmin(f))
+        assert abs(O.matrix_distance_squared(T, O.matrix(c, x.reshape(K, -1)[k])) - f[k]) < 1e-12
+
+
+def test_qutrit_synthesis_with_the_search_compiler():
+    """A two-qutrit target one QutritCNOTLinear layer deep (gatesets.py:295-305), through SearchCompiler and the batched
+    on-device LM solver on the radix-3 kernels: found at distance < 1e-10 with one two-qutrit gate."""
+    g = gatesets.QutritCNOTLinear()
+    c = gates.ProductGate(g.initial_layer(2)).appending(g.search_layers(2)[0][0])
+    T = O.matrix(c, np.random.default_rng(8).random(c.num_inputs) * 2 * np.pi)
+    res = q.SearchCompiler().compile(q.Options(target=T, gateset=g, seed=5, timeout=300))
+    assert check(res, T) <= 1
+
+
+@pytest.mark.parametrize("name", ["qt_csum", "qt_bswap"])
+def test_two_qutrit_gate_counts_match_the_reference(name):
+    """The two-qutrit targets of examples/qutrit_csum.py with its QutritCNOTLinear gateset, 10 seeds, against the UNMODIFIED
+    reference on the same problems (tests/golden/reference_synthesis.json: CSUM 3-5 gates, median 4; embedded SWAP 3-7, median
+    5): best <= the reference's best, median <= the reference's median, every run converged."""
+    from qsearch_b200 import utils
+    T = gates.CSUMGate().const_matrix() if name == "qt_csum" else utils.upgrade_qudits(unitaries.swap)
+    ref = [r["cnots"] for r in _reference_runs()[name]]
+    got = [check(q.SearchCompiler().compile(q.Options(target=T, gateset=gatesets.QutritCNOTLinear(), seed=3000 + s)), T)
+           for s in range(10)]
+    assert min(got) <= min(ref) and np.median(got) <= np.median(ref), (got, ref)

@@ -13,7 +13,7 @@ import numpy as np
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import qsearch_b200 as q  # noqa: E402
-from qsearch_b200 import gatesets, solvers, unitaries, _lib  # noqa: E402
+from qsearch_b200 import gates, gatesets, solvers, unitaries, utils, _lib  # noqa: E402
 
 YORKTOWN = [(0, 1), (0, 2), (1, 2), (2, 3), (2, 4), (3, 4)]  # examples/qft5_ibm_yorktown.py:21
 
@@ -31,6 +31,12 @@ CASES = {
     "qft4_leap": (lambda: unitaries.qft(16), gatesets.QubitCNOTLinear, "leap"),
     "qft4_search": (lambda: unitaries.qft(16), gatesets.QubitCNOTLinear, "search"),
     "qft5_yorktown_leap": (lambda: unitaries.qft(32), lambda: gatesets.QubitCNOTAdjacencyList(YORKTOWN), "leap"),
+    # two qutrits (examples/qutrit_csum.py): "cnots" counts the two-qutrit gates of the result
+    "qt_csum": (lambda: gates.CSUMGate().const_matrix(), gatesets.QutritCNOTLinear, "search"),
+    "qt_bswap": (lambda: utils.upgrade_qudits(unitaries.swap), gatesets.QutritCNOTLinear, "search"),
+    "qt_tswap": (lambda: unitaries.general_swap(3), gatesets.QutritCNOTLinear, "search"),
+    "qt_qft2": (lambda: unitaries.qft(9), gatesets.QutritCNOTLinear, "search"),
+    "qt_csum_cpi": (lambda: gates.CSUMGate().const_matrix(), gatesets.QutritCPIPhaseLinear, "search"),
 }
 
 
@@ -81,7 +87,7 @@ def main():
                          "cnots_before": repr(res["structure"]).count("CNOTGate"), "reopt_stats": post.get("stats")}
                 res = dict(res, structure=post["structure"], parameters=post["parameters"], distance=post.get("distance", res["distance"]))
             print(json.dumps({"case": name, "rep": rep, "solver": a.solver, "starts": a.starts, "fstarts": a.fstarts, "straggler": a.straggler, "tf32": a.tf32, "beams": a.beams, "devices": lib.num_devices, "wall_s": round(dt, 3),
-                              "cnots": repr(res["structure"]).count("CNOTGate"), "distance": float(res["distance"]),
+                              "cnots": repr(res["structure"]).count("CNOTGate") + repr(res["structure"]).count("CPIPhaseGate"), "distance": float(res["distance"]),
                               "stats": res["stats"], "launches": lib.launch_count() - l0, **extra}), flush=True)
 
 
