@@ -30,6 +30,7 @@ UNITS = [
     ("solve_lbfgs", "qsb_solve.cu", ["-DQSB_SOLVE_TU=1"]),
     ("solve_lm5", "qsb_solve.cu", ["-DQSB_SOLVE_TU=2"]),
     ("solve_lm5t", "qsb_solve.cu", ["-DQSB_SOLVE_TU=3"]),
+    ("solve_lm4w", "qsb_solve.cu", ["-DQSB_SOLVE_TU=4"]),
     ("peak", "qsb_peak.cu", []),
     ("noalloc", "qsb_noalloc.cu", []),
 ]

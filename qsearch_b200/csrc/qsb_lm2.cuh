@@ -612,7 +612,8 @@ QSB_GLOBAL __launch_bounds__(QSB_LM_WARPS * 32) qsb_k_lm2(QsbSolveArgs a) {
   QsbCholSmem* cs = (QsbCholSmem*)(sops + a.max_ops);  // global-memory factorisation (large P)
   double* Ls = (double*)(sops + a.max_ops);             // or: packed factor in shared memory (a.chol_smem); during the
                                                         // Jacobian phase the same bytes are the warps' W tiles
-  double* wtiles = (double*)(((uintptr_t)Ls + 15) & ~(uintptr_t)15);
+  // aligned through the offset, not an integer cast of the pointer (which would turn the W-tile accesses into generic LD / ST)
+  double* wtiles = (double*)((unsigned char*)smem_raw + (((size_t)((unsigned char*)Ls - (unsigned char*)smem_raw) + 15) & ~(size_t)15));
   double* rinv = Ls + (size_t)(a.max_params + 1) * (a.max_params + 2) / 2;
   int* okflag = (int*)(rinv + QSB_CH_NB);
   const int lane = threadIdx.x & 31, warp = qsb_warp_index();
@@ -659,7 +660,8 @@ QSB_GLOBAL __launch_bounds__(QSB_LM_WARPS * 32) qsb_k_lm2(QsbSolveArgs a) {
       }
       F = 0.5 * QSB_LDCG(&A[(size_t)P * rows + P]);
       __syncthreads();
-      double mu = 1e-3, nu = 2.0;
+      double mu = 1e-3, nu = a.mu_up;
+      int streak = 0;
       int rejects = 0;
       while (true) {
         if (!(F > 1e-300) || (a.stop_f > 0.0 && F <= a.stop_f)) { status = 4; break; }
@@ -680,7 +682,7 @@ QSB_GLOBAL __launch_bounds__(QSB_LM_WARPS * 32) qsb_k_lm2(QsbSolveArgs a) {
           QSB_PROF_END(2);
         }
         if (!chol_ok) {
-          mu *= nu; nu *= 2.0;
+          mu *= nu; nu *= a.mu_up; streak = 0;
           if (++rejects > 60 || mu > 1e30) { status = 5; break; }
           continue;
         }
@@ -726,11 +728,13 @@ QSB_GLOBAL __launch_bounds__(QSB_LM_WARPS * 32) qsb_k_lm2(QsbSolveArgs a) {
           F = 0.5 * QSB_LDCG(&A[(size_t)P * rows + P]);
           __syncthreads();
           const double q = 2.0 * rho - 1.0;
-          mu *= fmax(1.0 / 3.0, 1.0 - q * q * q);
-          nu = 2.0;
+          double fac = fmax(a.mu_down, 1.0 - q * q * q);
+          if (++streak <= a.mu_streak) fac = fmax(fac, 1.0);  // damping schedule: see QsbSolveArgs
+          mu *= fac;
+          nu = a.mu_up;
         } else {
           if (hnorm <= a.xtol * xnorm) { status = 3; break; }
-          mu *= nu; nu *= 2.0;
+          mu *= nu; nu *= a.mu_up; streak = 0;
           if (++rejects > 60 || mu > 1e30) { status = 5; break; }
         }
       }

@@ -360,22 +360,45 @@ QSB_DEVICE void qsb_gram_tf32(const float* R, int rows, int K2, double* A, int w
 
 // diagonal block [kb, kb + nbk): lane = row, the row in registers.  Leaves L in Ls and, dense, in Dk (identity in the
 // padding of a short block), 1 / L_jj in Dk[NB * DLD + j].
+#ifdef QSB_EMU
+static inline double qsb_rcp_pos(double a) { return 1.0 / a; }
+#else
+// 1 / a for a positive, normal a (the caller has excluded everything else; garbage in, garbage out, no trap): hardware seed and
+// two Newton steps, the fast path of the library's division without its special-case branch
+__device__ __forceinline__ double qsb_rcp_pos(double a) {
+  double y;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(a));
+  y = fma(fma(-a, y, 1.0), y, y);
+  return fma(fma(-a, y, 1.0), y, y);
+}
+#endif
+
 QSB_DEVICE void qsb_ch4_diag(double* Ls, int kb, int nbk, double* Dk, int* okflag, int lane) {
   constexpr int NB = QSB_CH_NB, LD = QSB_CH4_DLD;
   const int base = QSB_TRI32(kb + lane, kb);
   double d[NB];
 #pragma unroll
   for (int j = 0; j < NB; ++j) d[j] = (lane < nbk && j <= lane) ? Ls[base + j] : ((j == lane) ? 1.0 : 0.0);
+  // Sixteen dependent pivot steps are the critical path of the whole factorisation, so the step is arranged for a short chain:
+  // the columns stay UNNORMALISED (c_ij = L_ij L_jj) while the block is eliminated, d_ik -= c_ij c_kj / p_j, which puts only
+  // pivot shuffle -> reciprocal -> scale -> update on the chain; the column shuffles do not wait for the reciprocal, and the
+  // sixteen square roots are taken afterwards, independently of each other.  No early exit: a non-positive pivot only clears the
+  // flag and the remaining steps run on garbage that nobody reads, so the steps are straight-line code.
+  double piv[NB];
   bool good = true;
 #pragma unroll
   for (int j = 0; j < NB; ++j) {
-    const double piv = __shfl_sync(QSB_FULL, d[j], j);
-    if (!(piv > 0.0) || !(piv < 1e300)) { good = false; break; }
-    const double inv = rsqrt(piv);
-    if (lane == j) Dk[NB * LD + j] = inv;
-    d[j] = (lane == j) ? piv * inv : d[j] * inv;
+    piv[j] = __shfl_sync(QSB_FULL, d[j], j);
+    good = good && (piv[j] > 0.0) && (piv[j] < 1e300);
+    const double t = d[j] * qsb_rcp_pos(piv[j]);
 #pragma unroll
-    for (int k = j + 1; k < NB; ++k) d[k] = fma(-d[j], __shfl_sync(QSB_FULL, d[j], k), d[k]);
+    for (int k = j + 1; k < NB; ++k) d[k] = fma(-t, __shfl_sync(QSB_FULL, d[j], k), d[k]);
+  }
+#pragma unroll
+  for (int j = 0; j < NB; ++j) {
+    const double inv = rsqrt(piv[j]);
+    if (lane == j) Dk[NB * LD + j] = inv;
+    d[j] *= inv;  // lane j: p_j / sqrt(p_j) = L_jj
   }
   if (!good && lane == 0) *okflag = 0;
   if (lane < NB) {
@@ -703,19 +726,20 @@ QSB_DEVICE void qsb_q_crow(const cplx* V, double* row) {
 // |V - I|^2 and Tr V), and on the way it leaves a snapshot of X in front of every op that has parameters
 // (snap + ordinal * 2 N^2 doubles, TRANSPOSED: [col][row] complex, so the stores of a warp are contiguous).  If the step
 // is accepted, the product phase below reads the snapshots: no warp ever recomputes a prefix.
-template <int NQ>
+#define QSB_ROWS_PART 32  // doubles of shared memory for the per-warp partial sums of qsb_cta_eval_rows (3 per active warp)
+template <int NQ, int NW = 8>
 struct QsbRowGeom {
   static constexpr int N = 1 << NQ;
   static constexpr int SLOTS = 32 / N;                          // columns that fit side by side in one warp (N <= 32)
-  static constexpr int CW = (N / 8 > SLOTS) ? N / 8 : SLOTS;    // columns per warp: n = 5: 4, n = 4: 2, n = 3: 4
+  static constexpr int CW = (N / NW > SLOTS) ? N / NW : SLOTS;  // columns per warp (8 warps): n = 5: 4, n = 4: 2, n = 3: 4
   static constexpr int EPL = CW / SLOTS;                        // elements per lane
   static constexpr int AW = N / CW;                             // warps that take part (n = 3: 2 of the 8)
 };
 
-template <int NQ>
+template <int NQ, int NW = 8>
 QSB_DEVICE void qsb_warp_forward_rows(const QsbDevProgram& P, const double* target, const cplx* gtab, int warp, int lane,
                                       double* snap, cplx* vout, double& norm2, cplx& tr) {
-  using R = QsbRowGeom<NQ>;
+  using R = QsbRowGeom<NQ, NW>;
   constexpr int N = R::N, EPL = R::EPL;
   const int r = lane & (N - 1), c0 = R::CW * warp + (lane >> NQ);
   double xr[EPL], xi[EPL];
@@ -778,11 +802,12 @@ QSB_DEVICE void qsb_warp_forward_rows(const QsbDevProgram& P, const double* targ
 }
 
 // CTA-wide: (cos, sin) table and body-frame gate table of x, the forward pass above, then F = |U T^dagger - I|_F^2 / 2 and
-// Tr(U T^dagger).  snap / vsm may be null (no snapshots / V not wanted).  part: >= 3 * 8 doubles.
-template <int NQ>
+// Tr(U T^dagger).  snap / vsm may be null (no snapshots / V not wanted).  part: QSB_ROWS_PART doubles.  NW: warps of the CTA.
+template <int NQ, int NW = 8>
 QSB_DEVICE double qsb_cta_eval_rows(const QsbDevProgram& P, const double* x, const double* target, double* trig, cplx* gtab,
                                     double* part, double* snap, cplx* vsm, cplx* tr_out) {
-  constexpr int AW = QsbRowGeom<NQ>::AW;
+  constexpr int AW = QsbRowGeom<NQ, NW>::AW;
+  static_assert(3 * AW <= QSB_ROWS_PART, "partial-sum buffer too small");
   const int lane = threadIdx.x & 31, warp = qsb_warp_index();
   __syncthreads();
   for (int p = threadIdx.x; p < P.n_params; p += blockDim.x) {
@@ -795,7 +820,7 @@ QSB_DEVICE double qsb_cta_eval_rows(const QsbDevProgram& P, const double* x, con
   __syncthreads();
   if (warp < AW) {
     double n2; cplx tr;
-    qsb_warp_forward_rows<NQ>(P, target, gtab, warp, lane, snap, vsm, n2, tr);
+    qsb_warp_forward_rows<NQ, NW>(P, target, gtab, warp, lane, snap, vsm, n2, tr);
     if (lane == 0) { part[3 * warp] = n2; part[3 * warp + 1] = tr.x; part[3 * warp + 2] = tr.y; }
   }
   __syncthreads();
@@ -854,10 +879,14 @@ QSB_DEVICE void qsb_cta_qrows_snap(const QsbDevProgram& P, const cplx* gtab, con
   __syncthreads();
 }
 
-template <int NQ, bool TF32>
-QSB_GLOBAL __launch_bounds__(QsbQGeom<NQ>::WARPS * 32) qsb_k_lm3(QsbSolveArgs a) {
+// NW = 8: one CTA per SM, the latency-optimal shape for a batch that fits the GPU once.  NW = 4 (n <= 4): two CTAs per SM at
+// the same 255 registers per thread; every phase of one instance is up to 2x slower, but the phases are latency-bound (one
+// warp per scheduler already drives the FP64 pipe at 92 % of its peak, profiles/r2/v_dmma_occupancy.log), so two instances per
+// SM overlap: the shape for batches of more than one instance per SM.
+template <int NQ, bool TF32, int NW = QsbQGeom<NQ>::WARPS>
+QSB_GLOBAL __launch_bounds__(NW * 32, (NW == 4 ? 2 : 1)) qsb_k_lm3(QsbSolveArgs a) {
   using G = QsbQGeom<NQ>;
-  constexpr int N = G::N, K2 = G::K2, NW = G::WARPS;
+  constexpr int N = G::N, K2 = G::K2;
   QSB_DYN_SMEM(smem_raw);
   cplx* red = (cplx*)smem_raw;  // 32
   double* x = (double*)(red + 32);
@@ -867,12 +896,15 @@ QSB_GLOBAL __launch_bounds__(QsbQGeom<NQ>::WARPS * 32) qsb_k_lm3(QsbSolveArgs a)
   double* d2 = h + a.max_params;
   double* wk = d2 + a.max_params;
   double* trig = wk + a.max_params;         // 2 * maxP
-  double* part = trig + 2 * a.max_params;   // 16
-  cplx* gtab = (cplx*)(part + 16);  // [max_ops + max_params][4]; 16-byte aligned: 8 maxP + 16 doubles precede it
+  double* part = trig + 2 * a.max_params;   // QSB_ROWS_PART
+  cplx* gtab = (cplx*)(part + QSB_ROWS_PART);  // [max_ops + max_params][4]; 16-byte aligned: 8 maxP + 32 doubles precede it
   int* seg = (int*)(gtab + (size_t)4 * (a.max_ops + a.max_params));  // 16 ints: [12] = queue slot, [13] = ok flag
   qsb_op* sops = (qsb_op*)(seg + 16);       // the program's ops, staged once per instance
-  double* Ls = (double*)(sops + a.max_ops); // packed Cholesky factor; during the sweep the same bytes hold V
-  Ls = (double*)(((uintptr_t)Ls + 15) & ~(uintptr_t)15);
+  // packed Cholesky factor; during the sweep the same bytes hold V.  Aligned through its OFFSET in the dynamic shared memory, not
+  // through an integer cast of the pointer: the cast hides the address space from the compiler, and every access to the factor
+  // (the whole Cholesky and the back-substitution) became a generic LD / ST instead of LDS / STS
+  const size_t ls_off = ((size_t)((unsigned char*)(sops + a.max_ops) - (unsigned char*)smem_raw) + 15) & ~(size_t)15;
+  double* Ls = (double*)((unsigned char*)smem_raw + ls_off);
   cplx* vsm = (cplx*)Ls;
   const size_t tri = (size_t)(a.max_params + 1) * (a.max_params + 2) / 2;
   double* Winv = Ls + (((tri > (size_t)2 * N * N ? tri : (size_t)2 * N * N) + 1) & ~(size_t)1);  // [ceil(maxP / 16)][256]
@@ -902,7 +934,7 @@ QSB_GLOBAL __launch_bounds__(QsbQGeom<NQ>::WARPS * 32) qsb_k_lm3(QsbSolveArgs a)
     for (int k = threadIdx.x; k < P; k += blockDim.x) x[k] = x0[k];
     int iters = 0, status = 0;
     cplx tr;
-    double F = qsb_cta_eval_rows<NQ>(prog, x, a.target, trig, gtab, part, snap, vsm, &tr);  // tables, snapshots and V of x
+    double F = qsb_cta_eval_rows<NQ, NW>(prog, x, a.target, trig, gtab, part, snap, vsm, &tr);  // tables, snapshots and V of x
     if (P > 0) {
       { QSB_PROF_BEGIN(); qsb_cta_qrows_snap<NQ, TF32>(prog, gtab, snap, vsm, Rg, g); QSB_PROF_END(0); }
       iters = 1;
@@ -925,10 +957,11 @@ QSB_GLOBAL __launch_bounds__(QsbQGeom<NQ>::WARPS * 32) qsb_k_lm3(QsbSolveArgs a)
         d2[k] = akk > 0.0 ? akk : 1.0;
       }
       __syncthreads();
-      double mu = 1e-3, nu = 2.0;
-      int rejects = 0;
+      double mu = 1e-3, nu = a.mu_up;
+      int rejects = 0, streak = 0;
       while (true) {
         if (!(F > 1e-300) || (a.stop_f > 0.0 && F <= a.stop_f)) { status = 4; break; }
+        if (a.prof && threadIdx.x == 0) atomicAdd((unsigned long long*)&a.prof[10], 1ull);  // factorisation attempts
         {  // MINPACK's gtol: max cosine between r and the columns of J_r; the batch-level stop rules ride on the same reduction
           double gm = 0.0;
           const double rn = sqrt(2.0 * F);
@@ -949,7 +982,7 @@ QSB_GLOBAL __launch_bounds__(QsbQGeom<NQ>::WARPS * 32) qsb_k_lm3(QsbSolveArgs a)
         bool chol_ok;
         { QSB_PROF_BEGIN(); chol_ok = qsb_chol4(A, rows, d2, mu, P, Ls, Dk, Winv, okflag, a.prof); QSB_PROF_END(2); }
         if (!chol_ok) {
-          mu *= nu; nu *= 2.0;
+          mu *= nu; nu *= a.mu_up; streak = 0;
           if (++rejects > 60 || mu > 1e30) { status = 5; break; }
           continue;
         }
@@ -965,7 +998,7 @@ QSB_GLOBAL __launch_bounds__(QsbQGeom<NQ>::WARPS * 32) qsb_k_lm3(QsbSolveArgs a)
         p2 = qsb_block_sum(p2, red);
         const double hnorm = sqrt(p1.x), xnorm = sqrt(p1.y), pred = 0.5 * p2.x;
         double Fn;
-        { QSB_PROF_BEGIN(); Fn = qsb_cta_eval_rows<NQ>(prog, xn, a.target, trig, gtab, part, snap, vsm, &tr); QSB_PROF_END(4); }  // tables, snapshots, V now belong to xn
+        { QSB_PROF_BEGIN(); Fn = qsb_cta_eval_rows<NQ, NW>(prog, xn, a.target, trig, gtab, part, snap, vsm, &tr); QSB_PROF_END(4); }  // tables, snapshots, V now belong to xn
         const double dF = F - Fn;
         const double rho = (pred > 0.0) ? dF / pred : -1.0;
         if (rho > 1e-4 && Fn == Fn) {
@@ -1001,17 +1034,19 @@ QSB_GLOBAL __launch_bounds__(QsbQGeom<NQ>::WARPS * 32) qsb_k_lm3(QsbSolveArgs a)
           }
           __syncthreads();
           const double q = 2.0 * rho - 1.0;
-          mu *= fmax(1.0 / 3.0, 1.0 - q * q * q);
-          nu = 2.0;
+          double fac = fmax(a.mu_down, 1.0 - q * q * q);
+          if (++streak <= a.mu_streak) fac = fmax(fac, 1.0);
+          mu *= fac;
+          nu = a.mu_up;
         } else {
           if (hnorm <= a.xtol * xnorm) { status = 3; break; }
-          mu *= nu; nu *= 2.0;
+          mu *= nu; nu *= a.mu_up; streak = 0;
           if (++rejects > 60 || mu > 1e30) { status = 5; break; }
         }
       }
     }
     // final distance 1 - |Tr(U T^dagger)| / N at x   (comparison.matrix_distance_squared, comparison.py:8-22)
-    qsb_cta_eval_rows<NQ>(prog, x, a.target, trig, gtab, part, nullptr, nullptr, &tr);
+    qsb_cta_eval_rows<NQ, NW>(prog, x, a.target, trig, gtab, part, nullptr, nullptr, &tr);
     double* ox = a.out_x + a.param_off[inst];
     for (int k = threadIdx.x; k < P; k += blockDim.x) ox[k] = x[k];
     if (a.prof && threadIdx.x == 0) atomicAdd((unsigned long long*)&a.prof[5], (unsigned long long)iters);
@@ -1032,7 +1067,7 @@ QSB_GLOBAL __launch_bounds__(QsbQGeom<NQ>::WARPS * 32) qsb_k_lm3(QsbSolveArgs a)
 
 static inline size_t qsb_lm3_smem_bytes(int nq, int max_ops, int max_params) {
   const size_t N = (size_t)1 << nq;
-  const size_t base = 32 * 16 + (size_t)8 * max_params * 8 + 16 * 8 + 8 + (size_t)64 * (max_ops + max_params) + 16 * 4 + (size_t)24 * max_ops + 16;
+  const size_t base = 32 * 16 + (size_t)8 * max_params * 8 + QSB_ROWS_PART * 8 + 8 + (size_t)64 * (max_ops + max_params) + 16 * 4 + (size_t)24 * max_ops + 16;
   const size_t packed = std::max((size_t)(max_params + 1) * (max_params + 2) / 2, 2 * N * N);
   return base + (packed + 1 + (size_t)((max_params + QSB_CH_NB - 1) / QSB_CH_NB) * QSB_CH3_WSZ + 32 + 2 * QSB_CH4_DSZ) * 8;
 }
@@ -1048,8 +1083,8 @@ QSB_GLOBAL __launch_bounds__(QsbQGeom<NQ>::WARPS * 32, (NQ <= 4 ? 2 : 1)) qsb_k_
   constexpr int N = G::N, K2 = G::K2, NW = G::WARPS;
   QSB_DYN_SMEM(smem_raw);
   double* trig = (double*)smem_raw;                       // 2 * maxP
-  double* part = trig + 2 * a.max_params;                 // 16
-  cplx* gtab = (cplx*)(part + 16);
+  double* part = trig + 2 * a.max_params;                 // QSB_ROWS_PART
+  cplx* gtab = (cplx*)(part + QSB_ROWS_PART);
   cplx* vsm = gtab + (size_t)4 * (a.max_ops + a.max_params);  // N * N
   int* seg = (int*)(vsm + N * N);                         // 16
   qsb_op* sops = (qsb_op*)(seg + 16);
@@ -1089,5 +1124,5 @@ QSB_GLOBAL __launch_bounds__(QsbQGeom<NQ>::WARPS * 32, (NQ <= 4 ? 2 : 1)) qsb_k_
 
 static inline size_t qsb_lmsys3_smem_bytes(int nq, int max_ops, int max_params) {
   const size_t N = (size_t)1 << nq;
-  return ((size_t)2 * max_params + 16 + 8 * (size_t)(max_ops + max_params) + 2 * N * N) * 8 + 16 * 4 + (size_t)24 * max_ops + 64;
+  return ((size_t)2 * max_params + QSB_ROWS_PART + 8 * (size_t)(max_ops + max_params) + 2 * N * N) * 8 + 16 * 4 + (size_t)24 * max_ops + 64;
 }

@@ -52,8 +52,8 @@ qsb_k_lmsys3_static(QsbDevProgram prog, int count, const double* params, const d
   QSB_DYN_SMEM(smem_raw);
   const int P = prog.n_params, rows = P + 1;
   double* trig = (double*)smem_raw;                       // 2 * P
-  double* part = trig + 2 * P;                            // 16
-  cplx* gtab = (cplx*)(part + 16);
+  double* part = trig + 2 * P;                            // QSB_ROWS_PART
+  cplx* gtab = (cplx*)(part + QSB_ROWS_PART);
   cplx* vsm = gtab + (size_t)4 * (prog.n_ops + P);        // N * N
   int* seg = (int*)(vsm + N * N);                         // 16
   qsb_op* sops = (qsb_op*)(seg + 16);

@@ -1,8 +1,9 @@
 // Host side of the batched solvers (C ABI: qsb_solve_lm / qsb_solve_lbfgs).  One source, three translation units
 // (build.py compiles them in parallel): QSB_SOLVE_TU = 0: Levenberg-Marquardt, 1..4 qubits + qsb_solve_lm;
-// 1: L-BFGS + qsb_solve_lbfgs; 2: Levenberg-Marquardt, 5 qubits; 3: the same with the TF32 Gram product (qsb_k_lm3<5, true>).
+// 1: L-BFGS + qsb_solve_lbfgs; 2: Levenberg-Marquardt, 5 qubits; 3: the same with the TF32 Gram product (qsb_k_lm3<5, true>);
+// 4: the 4-warp, two-CTAs-per-SM shape of the body-frame LM kernel for 3 and 4 qubits (qsb_k_lm3<n, tf32, 4>).
 #ifndef QSB_SOLVE_TU
-#error "compile with -DQSB_SOLVE_TU=0|1|2|3"
+#error "compile with -DQSB_SOLVE_TU=0|1|2|3|4"
 #endif
 #include <algorithm>
 #include <cstdio>
@@ -23,7 +24,34 @@
 #define QSB_TU_METHOD QSB_SOLVE_LM
 #endif
 
-#if QSB_SOLVE_TU != 1
+#if QSB_SOLVE_TU == 4
+// ---------------------------------------------------------------------------- body-frame LM, 4 warps per instance
+template <int NQ, bool TF32>
+static int launch_lm3_w4(const SolveJob& job, qsb_batch* b, QsbSolveArgs& args, const QsbDevice& d) {
+  const size_t NN = (size_t)1 << (2 * NQ), maxP = (size_t)b->max_params;
+  const int threads = 4 * 32;
+  const size_t smem = qsb_lm3_smem_bytes(NQ, b->max_ops, (int)maxP);
+  size_t per_cta = (maxP + 1) * NN + (maxP + 1) * (maxP + 2) / 2 + 2 + (size_t)b->max_pops * 2 * NN;  // slab, packed Gram, snapshots
+  per_cta = (per_cta + 1) & ~(size_t)1;
+  int rc = qsb_prepare_kernel(qsb_k_lm3<NQ, TF32, 4>, smem);
+  if (rc) return rc;
+  const int ctas = qsb_resident_ctas(qsb_k_lm3<NQ, TF32, 4>, threads, smem);
+  const int grid = std::max(1, std::min(args.count, d.sm_count * ctas));
+  QsbBuf& scratch = job.ctx->devs[b->slot].solve_scratch;
+  if ((rc = qsb_buf_reserve(scratch, (size_t)grid * per_cta * sizeof(double)))) return rc;
+  args.scratch = (double*)scratch.p;
+  args.scratch_per_cta = per_cta;
+  QSB_LAUNCH((qsb_k_lm3<NQ, TF32, 4>), grid, threads, smem, d.stream, args);
+  QSB_CUDA(cudaGetLastError());
+  return QSB_OK;
+}
+
+int qsb_launch_solver_lm_w4(const SolveJob& job, qsb_batch* b, QsbSolveArgs& args, const QsbDevice& d, int nq, bool tf32) {
+  if (nq == 3) return tf32 ? launch_lm3_w4<3, true>(job, b, args, d) : launch_lm3_w4<3, false>(job, b, args, d);
+  if (nq == 4) return tf32 ? launch_lm3_w4<4, true>(job, b, args, d) : launch_lm3_w4<4, false>(job, b, args, d);
+  return qsb_fail(QSB_ERR_UNSUPPORTED, "the 4-warp LM kernel exists for 3 and 4 qubits");
+}
+#elif QSB_SOLVE_TU != 1
 // ---------------------------------------------------------------------------- Levenberg-Marquardt launches
 // TF32: the body-frame kernel with the TF32 Gram product (qsb_solver_opts.gram_tf32); a separate instantiation, so that
 // neither variant pays registers for the other's code
@@ -35,6 +63,14 @@ static int launch_solver_nq(const SolveJob& job, qsb_batch* b, QsbSolveArgs& arg
   // body-frame LM (qsb_lm3.cuh): unitary target, packed factor in shared memory; QSB_LM_KERNEL=lm2 forces the general kernel
   bool body_lm = tensor_lm && job.target_unitary && qsb_lm3_smem_bytes(NQ, b->max_ops, (int)maxP) <= 227 * 1024;
   if (const char* e = getenv("QSB_LM_KERNEL")) { if (strcmp(e, "lm2") == 0) body_lm = false; }
+  if constexpr (NQ == 3 || NQ == 4) {
+    // more than one instance per SM: two 4-warp CTAs per SM instead of one 8-warp CTA (QSB_LM_WARPS=4 / 8 forces either)
+    // Only with the straggler rule: without it the wall time of a batch is its slowest instance (thousands of iterations against
+    // a mean of 200, profiles/r2/w_solve_w4_ab.log), i.e. per-iteration latency, where the 8-warp shape is 15-20 % better.
+    bool dense = body_lm && args.straggler_c > 0.0 && args.count > d.sm_count && qsb_lm3_smem_bytes(NQ, b->max_ops, (int)maxP) <= 110 * 1024;
+    if (const char* e = getenv("QSB_LM_WARPS")) { const int v = atoi(e); if (v == 4) dense = body_lm; else if (v == 8) dense = false; }
+    if (dense) return qsb_launch_solver_lm_w4(job, b, args, d, NQ, TF32);
+  }
   int threads = (int)std::max<size_t>(32, NN / 2);
   size_t smem, per_cta;
   if (body_lm) {
@@ -208,7 +244,9 @@ static int launch_solver_interp(const SolveJob& job, qsb_batch* b, QsbSolveArgs&
 }
 #endif
 
-#if QSB_SOLVE_TU == 2
+#if QSB_SOLVE_TU == 4
+// (launch function above)
+#elif QSB_SOLVE_TU == 2
 int qsb_launch_solver_lm5(const SolveJob& job, qsb_batch* b, QsbSolveArgs& args, const QsbDevice& d) {
   return launch_solver_nq<5, false>(job, b, args, d);
 }
@@ -252,6 +290,9 @@ static int solve_shard(const SolveJob& job, int slot, int i0, int i1, const std:
   if (cudaMemsetAsync(args.ctl, 0, n_ctl * sizeof(int32_t), job.ctx->devs[slot].stream) != cudaSuccess)
     return done(qsb_fail(QSB_ERR_CUDA, "cudaMemsetAsync of the solver control block failed"));
   b->max_params = args.max_params;
+  if (const char* e = getenv("QSB_LM_MU_DOWN")) { const double v = atof(e); if (v > 0.0 && v <= 1.0) args.mu_down = v; }
+  if (const char* e = getenv("QSB_LM_MU_UP")) { const double v = atof(e); if (v > 1.0) args.mu_up = v; }
+  if (const char* e = getenv("QSB_LM_MU_STREAK")) args.mu_streak = atoi(e);
   args.prof = nullptr;
   args.chol_smem = 0;
   args.cluster = 1;
@@ -295,8 +336,8 @@ static int solve_shard(const SolveJob& job, int slot, int i0, int i1, const std:
     cudaMemcpy(hp, d_prof, sizeof(hp), cudaMemcpyDeviceToHost);
     cudaFree(d_prof);
     const double it = hp[5] > 0 ? (double)hp[5] : 1.0;
-    fprintf(stderr, "[qsb lm profile] instances=%d jac_evals=%lld cycles/jac_eval: jac=%.0f syrk=%.0f cholesky=%.0f (fill=%.0f diag=%.0f panel=%.0f trailing=%.0f) solve=%.0f trial=%.0f\n", n,
-            hp[5], hp[0] / it, hp[1] / it, hp[2] / it, hp[6] / it, hp[7] / it, hp[8] / it, hp[9] / it, hp[3] / it, hp[4] / it);
+    fprintf(stderr, "[qsb lm profile] instances=%d jac_evals=%lld attempts=%lld cycles/jac_eval: jac=%.0f syrk=%.0f cholesky=%.0f (fill=%.0f diag=%.0f panel=%.0f trailing=%.0f) solve=%.0f trial=%.0f\n", n,
+            hp[5], hp[10], hp[0] / it, hp[1] / it, hp[2] / it, hp[6] / it, hp[7] / it, hp[8] / it, hp[9] / it, hp[3] / it, hp[4] / it);
   }
 #undef QSB_S
   return done(QSB_OK);

@@ -18,3 +18,5 @@ struct SolveJob {
 // Levenberg-Marquardt on 5 qubits lives in its own translation unit (compile time)
 int qsb_launch_solver_lm5(const SolveJob& job, qsb_batch* b, QsbSolveArgs& args, const QsbDevice& d);
 int qsb_launch_solver_lm5t(const SolveJob& job, qsb_batch* b, QsbSolveArgs& args, const QsbDevice& d);  // TF32 Gram product
+// The body-frame LM kernel as 4-warp CTAs, two per SM (n = 3, 4): for batches of more than one instance per SM.  Own unit too.
+int qsb_launch_solver_lm_w4(const SolveJob& job, qsb_batch* b, QsbSolveArgs& args, const QsbDevice& d, int nq, bool tf32);

@@ -346,3 +346,31 @@ def test_solvers_on_qutrit_circuits():
             b.set_params(x0[0]); b.set_target(T); b.run(6)
         finally:
             b.close()
+
+
+@pytest.mark.parametrize("n", [3, 4])
+def test_four_warp_shape_of_the_body_frame_lm(n, monkeypatch):
+    """qsb_k_lm3<n, tf32, 4>: the body-frame LM as 4-warp CTAs (two per SM; chosen for batches of more than one instance per
+    SM, forced here with QSB_LM_WARPS).  Same algorithm, different split of the work over warps: same end points."""
+    from oracle import qs_oracle as O
+    from qsearch_b200 import gates, gatesets, lowering
+    lib = emulated_library()
+    rng = np.random.default_rng(23 + n)
+    g = gatesets.QubitCNOTLinear()
+    c = gates.ProductGate(g.initial_layer(n)).appending(g.search_layers(n)[0][0]).appending(g.search_layers(n)[n - 2][0])
+    T = O.matrix(c, rng.random(c.num_inputs) * 2 * np.pi)
+    gp = lowering.lower(c)
+    K = 6
+    x0 = rng.random((K, c.num_inputs)) * 2 * np.pi
+    poi = np.zeros(K, dtype="int32")
+    out = {}
+    for warps in ("8", "4"):
+        monkeypatch.setenv("QSB_LM_WARPS", warps)
+        for tf32 in (0, 1):
+            out[warps, tf32] = lib.solve("lm", [gp], poi, x0, T, gram_tf32=tf32)
+    for tf32 in (0, 1):
+        (x8, f8, it8, st8), (x4, f4, it4, st4) = out["8", tf32], out["4", tf32]
+        assert f4.min() < 1e-10 and f8.min() < 1e-10
+        assert np.abs(np.sort(f4) - np.sort(f8)).max() < 1e-5 and abs(int(it4.sum()) - int(it8.sum())) <= 0.2 * it8.sum() + 4
+        for k in range(K):
+            assert abs(O.matrix_distance_squared(T, O.matrix(c, x4.reshape(K, -1)[k])) - f4[k]) < 1e-12

@@ -1,0 +1,61 @@
+#!/usr/bin/env python
+"""LM damping-schedule sweep for qsb_k_lm3: Jacobian evaluations, factorisation attempts, final distances
+and wall time of frontier-shaped batches under the QSB_LM_MU_* knobs.  Run with QSB_LM_PROFILE=1 so that the library prints its
+attempt counters (stderr) after every solve.
+
+    QSB_LM_PROFILE=1 python tools/mu_sweep.py 2>&1 | grep -v "^\\[qsb lm profile\\] instances=1 "
+"""
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from qsearch_b200 import _lib, gatesets, unitaries  # noqa: E402
+from tools.solve_bench import case, YORKTOWN  # noqa: E402
+
+VARIANTS = [{}, {"QSB_LM_MU_DOWN": "0.5"}, {"QSB_LM_MU_DOWN": "0.7"}, {"QSB_LM_MU_STREAK": "1"}, {"QSB_LM_MU_STREAK": "2"},
+            {"QSB_LM_MU_STREAK": "3"}, {"QSB_LM_MU_DOWN": "0.5", "QSB_LM_MU_STREAK": "2"},
+            {"QSB_LM_MU_DOWN": "0.7", "QSB_LM_MU_STREAK": "1"}, {"QSB_LM_MU_DOWN": "0.5", "QSB_LM_MU_UP": "3"},
+            {"QSB_LM_MU_DOWN": "0.6", "QSB_LM_MU_STREAK": "2"}]
+KEYS = ("QSB_LM_MU_DOWN", "QSB_LM_MU_UP", "QSB_LM_MU_STREAK")
+
+
+def main():
+    lib = _lib.get_library()
+    cases = [("n3 d6 4x74", 3, 6, 4, 74, gatesets.QubitCNOTLinear(), 5), ("n4 d10 4x74", 4, 10, 4, 74, gatesets.QubitCNOTRing(), 5),
+             ("n4 d8 3x98 reachable", 4, 8, 3, 98, gatesets.QubitCNOTLinear(), 6),
+             ("n5 d12 6x24", 5, 12, 6, 24, gatesets.QubitCNOTAdjacencyList(YORKTOWN), 5)]
+    for name, n, depth, nc, starts, gs, seed in cases:
+        gps, poi, x0 = case(n, depth, nc, starts, seed, gs)
+        if "reachable" in name:
+            from oracle import qs_oracle as O  # tools only: a target the first child reaches exactly
+            from qsearch_b200 import gates
+            rng = np.random.default_rng(1)
+            layers = gs.search_layers(n)
+            c = gates.ProductGate(gs.initial_layer(n))
+            rng2 = np.random.default_rng(seed)
+            for _ in range(depth - 1):
+                c = c.appending(layers[int(rng2.integers(len(layers)))][0])
+            c = c.appending(layers[0][0])
+            T = O.matrix(c, rng.random(c.num_inputs) * 2 * np.pi)
+        else:
+            T = unitaries.qft(1 << n)
+        lib.solve("lm", gps[:1], poi[:1] * 0, x0[:gps[0].n_params], T)
+        for v in VARIANTS:
+            for k in KEYS:
+                os.environ.pop(k, None)
+            os.environ.update(v)
+            sys.stdout.flush()
+            t0 = time.perf_counter()
+            x, f, iters, status = lib.solve("lm", gps, poi, x0, T)
+            dt = time.perf_counter() - t0
+            print(json.dumps({"case": name, "variant": v, "wall_ms": round(dt * 1e3, 1), "jac_sum": int(iters.sum()), "jac_max": int(iters.max()),
+                              "f_min": float(f.min()), "f_mean": float(f.mean()), "n_below_1e-10": int((f < 1e-10).sum()),
+                              "status": {int(s): int((status == s).sum()) for s in np.unique(status)}}), flush=True)
+
+
+if __name__ == "__main__":
+    main()
