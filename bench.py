@@ -78,8 +78,11 @@ QSRS_CAVEAT = ("CPU arm = NumPy restatement of the reference's NumPy backend (ki
                "ratios by up to 20 for a qsrs-equivalent figure")
 
 
-def _solve_target(n, which):
-    children, x0s, targets = workloads.frontier_workload(n)
+SOLVE_FORM_SEEDS = (0, 1, 2)  # three seeded frontiers: the wall time of a batch is its slowest instance, one draw of which is noisy
+
+
+def _solve_target(n, which, seed=0):
+    children, x0s, targets = workloads.frontier_workload(n, seed=seed)
     if which == "unreachable":
         return children, x0s, targets["unreachable"]
     from oracle import qs_oracle as O
@@ -129,8 +132,8 @@ def solve_form(lib, n, dist, world, cpu_solve):
         out = {}
         for frontier in (False, True):
             tot_t, tot_inst, tot_it, max_it, best = 0.0, 0, 0, 0, []
-            for which in ("unreachable", "reachable"):
-                children, x0s, T = _solve_target(n, which)
+            for which, seed in [(w, s) for s in SOLVE_FORM_SEEDS for w in ("unreachable", "reachable")]:
+                children, x0s, T = _solve_target(n, which, seed)
                 opts = q.Options(target=T, threshold=1e-10)
                 solver = solvers.LeastSquares_Jac_Solver(starts=4)
                 solver.solve_batch(children[:2], opts, x0s[:2], want_matrices=False, frontier=frontier)  # warm-up: module load, buffers
@@ -147,7 +150,7 @@ def solve_form(lib, n, dist, world, cpu_solve):
             out[key] = {"solves_per_s": world * tot_inst / tot_t, "instances": tot_inst, "wall_s": tot_t, "lm_iterations": tot_it,
                         "us_per_lm_iteration_latency": 1e6 * tot_t / max(1, max_it),
                         "instance_iterations_per_s": world * tot_it / tot_t, "best_distance": best}
-        out["what"] = ("n={}: 48 children x 4 starts, once against qft (unreachable) and once against a reachable target, through "
+        out["what"] = ("n={}: three seeded frontiers of 48 children x 4 starts, each once against qft (unreachable) and once against a reachable target, through "
                        "LeastSquares_Jac_Solver.solve_batch (host x0 in, xopt / distance out). reference_semantics: every start runs to "
                        "its own convergence, everything fp64; frontier_rules: straggler cap 2x + sibling stop + TF32 Gram matrix (gradient, objective and "
                        "outputs fp64), as GpuParallelizer runs it".format(n))

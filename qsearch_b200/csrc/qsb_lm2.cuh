@@ -728,7 +728,7 @@ QSB_GLOBAL __launch_bounds__(QSB_LM_WARPS * 32) qsb_k_lm2(QsbSolveArgs a) {
           F = 0.5 * QSB_LDCG(&A[(size_t)P * rows + P]);
           __syncthreads();
           const double q = 2.0 * rho - 1.0;
-          double fac = fmax(a.mu_down, 1.0 - q * q * q);
+          double fac = fmax((a.mu_fast > 0 && streak + 1 >= a.mu_fast) ? 1.0 / 3.0 : a.mu_down, 1.0 - q * q * q);
           if (++streak <= a.mu_streak) fac = fmax(fac, 1.0);  // damping schedule: see QsbSolveArgs
           mu *= fac;
           nu = a.mu_up;

@@ -1034,7 +1034,7 @@ QSB_GLOBAL __launch_bounds__(NW * 32, (NW == 4 ? 2 : 1)) qsb_k_lm3(QsbSolveArgs 
           }
           __syncthreads();
           const double q = 2.0 * rho - 1.0;
-          double fac = fmax(a.mu_down, 1.0 - q * q * q);
+          double fac = fmax((a.mu_fast > 0 && streak + 1 >= a.mu_fast) ? 1.0 / 3.0 : a.mu_down, 1.0 - q * q * q);
           if (++streak <= a.mu_streak) fac = fmax(fac, 1.0);
           mu *= fac;
           nu = a.mu_up;

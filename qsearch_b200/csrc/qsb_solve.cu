@@ -290,9 +290,11 @@ static int solve_shard(const SolveJob& job, int slot, int i0, int i1, const std:
   if (cudaMemsetAsync(args.ctl, 0, n_ctl * sizeof(int32_t), job.ctx->devs[slot].stream) != cudaSuccess)
     return done(qsb_fail(QSB_ERR_CUDA, "cudaMemsetAsync of the solver control block failed"));
   b->max_params = args.max_params;
+  if (args.straggler_c > 0.0) { args.mu_down = 0.7; args.mu_streak = 1; }  // capped batches: the cheaper schedule (QsbSolveArgs)
   if (const char* e = getenv("QSB_LM_MU_DOWN")) { const double v = atof(e); if (v > 0.0 && v <= 1.0) args.mu_down = v; }
   if (const char* e = getenv("QSB_LM_MU_UP")) { const double v = atof(e); if (v > 1.0) args.mu_up = v; }
   if (const char* e = getenv("QSB_LM_MU_STREAK")) args.mu_streak = atoi(e);
+  if (const char* e = getenv("QSB_LM_MU_FAST")) args.mu_fast = atoi(e);
   args.prof = nullptr;
   args.chol_smem = 0;
   args.cluster = 1;

@@ -44,14 +44,18 @@ struct QsbSolveArgs {
   int straggler_min;    // ... but never before this many evaluations
   double sibling_f;     // > 0: stop an instance once another instance of the same program finished below this distance (status 7)
   int gram_tf32;        // qsb_k_lm3: J_r^T J_r from TF32-rounded rows on the mma.sync TF32 path (the gradient and the objective stay fp64)
-  // Damping schedule of the LM kernels (Nielsen's gain-ratio rule with a gentler way down): accepted step:
-  // mu *= max(mu_down, 1 - (2 rho - 1)^3), and no decrease at all for the first mu_streak accepted steps after a rejection;
-  // rejected step: mu *= nu, nu *= mu_up.  Nielsen's own mu_down = 1/3 made almost every accepted step be followed by a rejected
-  // one on these objectives (1.7-2.0 factorisations + trial evaluations per Jacobian evaluation); 0.7 with a streak of 1 needs
-  // 1.2-1.25 at the same number of Jacobian evaluations: 11-18 % less work per solve (profiles/r2/zd_mu_sweep.log).
-  // QSB_LM_MU_DOWN / QSB_LM_MU_UP / QSB_LM_MU_STREAK in the environment override them (experiments).
-  double mu_down = 0.7, mu_up = 2.0;
-  int mu_streak = 1;
+  // Damping schedule of the LM kernels.  Accepted step: mu *= max(mu_down, 1 - (2 rho - 1)^3), with no decrease at all for the first
+  // mu_streak accepted steps after a rejection; rejected step: mu *= nu, nu *= mu_up.  (1/3, 0, 2) is Nielsen's rule, the default:
+  // on these objectives almost every accepted step is then followed by a rejected one (1.7-2.0 factorisations + trial evaluations
+  // per Jacobian evaluation), but the instances that crawl along a valley shed their damping fastest, and without a cap the wall
+  // time of a batch is its slowest instance.  Batches that run under the straggler cap (frontier expansions) use (0.7, 1, 2):
+  // 1.2-1.25 attempts per Jacobian evaluation at the same number of Jacobian evaluations, 11-18 % less work per solve and
+  // 15 % less time per iteration, at the price of a longer tail that the cap cuts anyway (profiles/r2/zd_mu_sweep.log,
+  // zg_bench_*.json: +17 % solves/s under the frontier rules at n = 4, -19 % without them).  mu_fast > 0: from the mu_fast-th
+  // consecutive accepted step on the floor is 1/3 again (tried, no consistent gain: zf_mu_sweep.log).
+  // QSB_LM_MU_DOWN / _UP / _STREAK / _FAST in the environment override (experiments).
+  double mu_down = 1.0 / 3.0, mu_up = 2.0;
+  int mu_streak = 0, mu_fast = 0;
 };
 
 QSB_DEVICE double qsb_block_max(double v, cplx* red) {
@@ -283,7 +287,7 @@ QSB_GLOBAL __launch_bounds__(QsbGeom<NQ>::T) qsb_k_lm(QsbSolveArgs a) {
           F = 0.5 * A[P * rows + P];
           __syncthreads();
           const double q = 2.0 * rho - 1.0;
-          double fac = fmax(a.mu_down, 1.0 - q * q * q);
+          double fac = fmax((a.mu_fast > 0 && streak + 1 >= a.mu_fast) ? 1.0 / 3.0 : a.mu_down, 1.0 - q * q * q);
           if (++streak <= a.mu_streak) fac = fmax(fac, 1.0);  // damping schedule: see QsbSolveArgs
           mu *= fac;
           nu = a.mu_up;

@@ -16,11 +16,9 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from qsearch_b200 import _lib, gatesets, unitaries  # noqa: E402
 from tools.solve_bench import case, YORKTOWN  # noqa: E402
 
-VARIANTS = [{}, {"QSB_LM_MU_DOWN": "0.5"}, {"QSB_LM_MU_DOWN": "0.7"}, {"QSB_LM_MU_STREAK": "1"}, {"QSB_LM_MU_STREAK": "2"},
-            {"QSB_LM_MU_STREAK": "3"}, {"QSB_LM_MU_DOWN": "0.5", "QSB_LM_MU_STREAK": "2"},
-            {"QSB_LM_MU_DOWN": "0.7", "QSB_LM_MU_STREAK": "1"}, {"QSB_LM_MU_DOWN": "0.5", "QSB_LM_MU_UP": "3"},
-            {"QSB_LM_MU_DOWN": "0.6", "QSB_LM_MU_STREAK": "2"}]
-KEYS = ("QSB_LM_MU_DOWN", "QSB_LM_MU_UP", "QSB_LM_MU_STREAK")
+VARIANTS = [{"QSB_LM_MU_DOWN": "0.3333333333333333", "QSB_LM_MU_STREAK": "0"}, {}, {"QSB_LM_MU_FAST": "3"}, {"QSB_LM_MU_FAST": "4"},
+            {"QSB_LM_MU_FAST": "6"}, {"QSB_LM_MU_FAST": "8"}, {"QSB_LM_MU_FAST": "4", "QSB_LM_MU_DOWN": "0.6"}]
+KEYS = ("QSB_LM_MU_DOWN", "QSB_LM_MU_UP", "QSB_LM_MU_STREAK", "QSB_LM_MU_FAST")
 
 
 def main():
@@ -28,9 +26,15 @@ def main():
     cases = [("n3 d6 4x74", 3, 6, 4, 74, gatesets.QubitCNOTLinear(), 5), ("n4 d10 4x74", 4, 10, 4, 74, gatesets.QubitCNOTRing(), 5),
              ("n4 d8 3x98 reachable", 4, 8, 3, 98, gatesets.QubitCNOTLinear(), 6),
              ("n5 d12 6x24", 5, 12, 6, 24, gatesets.QubitCNOTAdjacencyList(YORKTOWN), 5)]
+    from qsearch_b200 import workloads, lowering
+    children, x0s, tg = workloads.frontier_workload(4)
+    fw = ([lowering.lower(c) for c in children], np.repeat(np.arange(len(children), dtype="int32"), 4), np.concatenate([np.ravel(x) for x in x0s]))
+    cases.append(("bench solve_form n4 48x4 unreachable", 4, 0, 0, 0, None, 0))
     for name, n, depth, nc, starts, gs, seed in cases:
-        gps, poi, x0 = case(n, depth, nc, starts, seed, gs)
-        if "reachable" in name:
+        gps, poi, x0 = fw if gs is None else case(n, depth, nc, starts, seed, gs)
+        if gs is None:
+            T = tg["unreachable"]
+        elif "reachable" in name:
             from oracle import qs_oracle as O  # tools only: a target the first child reaches exactly
             from qsearch_b200 import gates
             rng = np.random.default_rng(1)
