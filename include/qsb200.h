@@ -168,8 +168,9 @@ typedef struct qsb_solver_opts {
   /* Batch-level stop rules of the LM solver (all off at 0, which reproduces the reference's per-solve semantics:
    * every start runs to its own convergence, qsearch/solvers.py:146-163).  A frontier expansion waits for its slowest
    * instance, so the search front-end turns them on (qsearch_b200/parallelizers.py). */
-  double straggler_factor;    /* > 0: once half of the batch has finished, stop an instance whose Jacobian-evaluation count
-                                 exceeds straggler_factor x the largest count among that first half (out_status 6) */
+  double straggler_factor;    /* > 0: once half of the batch has terminated (for any reason, the sibling rule included), stop
+                                 an instance whose Jacobian-evaluation count exceeds straggler_factor x the largest count among
+                                 the instances of that first half that converged by themselves (out_status 6) */
   double sibling_stop;        /* > 0: stop an instance once another instance of the SAME program finished with a distance
                                  below this value (out_status 7): the other starts of a solved child are not needed */
   double straggler_min_iters; /* the straggler rule never fires before this many evaluations (<= 0: 32) */

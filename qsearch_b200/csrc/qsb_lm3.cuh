@@ -971,7 +971,7 @@ QSB_GLOBAL __launch_bounds__(NW * 32, (NW == 4 ? 2 : 1)) qsb_k_lm3(QsbSolveArgs 
           }
           if (threadIdx.x == 0) {  // encoded as huge values: every thread sees the same maximum
             if (a.sibling_f > 0.0 && QSB_LDCG(&a.ctl[QSB_CTL_SOLVED + pidx]) != 0) gm = 1e301;
-            else if (a.straggler_c > 0.0 && 2 * QSB_LDCG(&a.ctl[QSB_CTL_FINISHED]) >= a.count &&
+            else if (a.straggler_c > 0.0 && 2 * QSB_LDCG(&a.ctl[QSB_CTL_FINISHED]) >= a.count && QSB_LDCG(&a.ctl[QSB_CTL_MEDIAN]) > 0 &&
                      (double)iters > a.straggler_c * (double)QSB_LDCG(&a.ctl[QSB_CTL_MEDIAN]) && iters >= a.straggler_min) gm = 1e300;
           }
           gm = qsb_block_max(gm, red);
@@ -1057,10 +1057,13 @@ QSB_GLOBAL __launch_bounds__(NW * 32, (NW == 4 ? 2 : 1)) qsb_k_lm3(QsbSolveArgs 
       a.out_status[inst] = status;
       // batch-level bookkeeping for the stop rules of the instances still running
       if (a.sibling_f > 0.0 && dist < a.sibling_f) atomicAdd(&a.ctl[QSB_CTL_SOLVED + pidx], 1);
-      if (status != 6 && status != 7) {
-        const int nfin = atomicAdd(&a.ctl[QSB_CTL_FINISHED], 1) + 1;
-        if (2 * nfin <= a.count + 1) atomicMax(&a.ctl[QSB_CTL_MEDIAN], iters);
-      }
+      // Every termination counts towards "half of the batch is done" (an instance stopped by the sibling rule is done as far
+      // as the frontier is concerned; counting only natural finishes left the cap switched off for good in batches where most
+      // instances end that way, and one uncapped start then ran its 100 P iterations: profiles/r2/zj_mu_bench.log).  The
+      // reference count comes from the natural finishes among that first half, or from the first one after it if there was none.
+      const int nfin = atomicAdd(&a.ctl[QSB_CTL_FINISHED], 1) + 1;
+      if (status != 6 && status != 7 && (2 * nfin <= a.count + 1 || QSB_LDCG(&a.ctl[QSB_CTL_MEDIAN]) == 0))
+        atomicMax(&a.ctl[QSB_CTL_MEDIAN], iters);
     }
   }
 }

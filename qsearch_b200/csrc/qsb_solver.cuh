@@ -14,8 +14,8 @@
 
 // device-side control block of one solve launch (ints, zeroed by the host before the launch)
 #define QSB_CTL_NEXT 0      // next instance of the queue
-#define QSB_CTL_FINISHED 1  // instances finished so far
-#define QSB_CTL_MEDIAN 2    // max Jacobian-evaluation count among the first half of the instances to finish
+#define QSB_CTL_FINISHED 1  // instances finished so far (any status)
+#define QSB_CTL_MEDIAN 2    // max Jacobian-evaluation count among the naturally finished instances of the first half to finish
 #define QSB_CTL_SOLVED 4    // + program index: 1 once an instance of that program finished below the sibling threshold
 
 struct QsbSolveArgs {
