@@ -624,7 +624,8 @@ QSB_GLOBAL __launch_bounds__(QSB_LM_WARPS * 32) qsb_k_lm2(QsbSolveArgs a) {
   const int cwarps = csize * QSB_LM_WARPS, cwarp = rank * QSB_LM_WARPS + warp;
   double* Rg = a.scratch + (size_t)cid * a.scratch_per_cta;
   for (int inst = cid; inst < a.count; inst += nclusters) {
-    QsbDevProgram prog = a.progs[a.prog_idx[inst]];
+    const int pidx = a.prog_idx[inst];
+    QsbDevProgram prog = a.progs[pidx];
     const int P = prog.n_params, rows = P + 1;
     __syncthreads();
     for (int e = threadIdx.x; e < prog.n_ops * 6; e += blockDim.x) ((int32_t*)sops)[e] = ((const int32_t*)prog.ops)[e];
@@ -672,7 +673,17 @@ QSB_GLOBAL __launch_bounds__(QSB_LM_WARPS * 32) qsb_k_lm2(QsbSolveArgs a) {
             const double akk = QSB_LDCG(&A[(size_t)k * rows + k]);
             if (akk > 0.0) gm = fmax(gm, fabs(g[k]) / (sqrt(akk) * rn));
           }
+          // batch-level stop rules as in qsb_k_lm3 (circuits too long for its shared-memory factor run here: P > ~190 at
+          // n = 5, the deep rounds of a LEAP search).  Only without a cluster: the CTAs of a cluster take their decisions
+          // from identical data, and a flag read from global memory at different moments would let them diverge.
+          if (csize == 1 && threadIdx.x == 0) {
+            if (a.sibling_f > 0.0 && QSB_LDCG(&a.ctl[QSB_CTL_SOLVED + pidx]) != 0) gm = 1e301;
+            else if (a.straggler_c > 0.0 && 2 * QSB_LDCG(&a.ctl[QSB_CTL_FINISHED]) >= a.count && QSB_LDCG(&a.ctl[QSB_CTL_MEDIAN]) > 0 &&
+                     (double)iters > a.straggler_c * (double)QSB_LDCG(&a.ctl[QSB_CTL_MEDIAN]) && iters >= a.straggler_min) gm = 1e300;
+          }
           gm = qsb_block_max(gm, red);
+          if (gm >= 1e301) { status = 7; break; }
+          if (gm >= 1e300) { status = 6; break; }
           if (gm <= a.gtol) { status = 1; break; }
         }
         bool chol_ok;
@@ -744,10 +755,17 @@ QSB_GLOBAL __launch_bounds__(QSB_LM_WARPS * 32) qsb_k_lm2(QsbSolveArgs a) {
     double* ox = a.out_x + a.param_off[inst];
     for (int k = threadIdx.x; k < P; k += blockDim.x) ox[k] = x[k];
     if (a.prof && threadIdx.x == 0) atomicAdd((unsigned long long*)&a.prof[5], (unsigned long long)iters);
-    if (threadIdx.x == 0) {
-      a.out_f[inst] = fabs(1.0 - sqrt(tr.x * tr.x + tr.y * tr.y) / N);
+    if (threadIdx.x == 0 && rank == 0) {
+      const double dist = fabs(1.0 - sqrt(tr.x * tr.x + tr.y * tr.y) / N);
+      a.out_f[inst] = dist;
       a.out_iters[inst] = iters;
       a.out_status[inst] = status;
+      if (csize == 1) {  // bookkeeping of the stop rules (see qsb_k_lm3)
+        if (a.sibling_f > 0.0 && dist < a.sibling_f) atomicAdd(&a.ctl[QSB_CTL_SOLVED + pidx], 1);
+        const int nfin = atomicAdd(&a.ctl[QSB_CTL_FINISHED], 1) + 1;
+        if (status != 6 && status != 7 && (2 * nfin <= a.count + 1 || QSB_LDCG(&a.ctl[QSB_CTL_MEDIAN]) == 0))
+          atomicMax(&a.ctl[QSB_CTL_MEDIAN], iters);
+      }
     }
     __syncthreads();
   }

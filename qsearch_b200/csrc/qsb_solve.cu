@@ -108,6 +108,8 @@ static int launch_solver_nq(const SolveJob& job, qsb_batch* b, QsbSolveArgs& arg
       }
     }
 #endif
+    // the batch-level stop rules need one CTA per instance (qsb_k_lm2); a capped tail beats a faster iteration by far
+    if (args.straggler_c > 0.0 || args.sibling_f > 0.0) csize = 1;
     if (const char* e = getenv("QSB_LM_CLUSTER")) { int v = atoi(e); if (v >= 1 && v <= QSB_LM_MAX_CLUSTER) csize = v; }
     args.cluster = csize;
     per_cta = (maxP + 1) * 2 * NN + 2 * (maxP + 1) * (maxP + 1) + (args.chol_smem ? 0 : (size_t)csize * (maxP + 1) * (maxP + 1));

@@ -14,6 +14,10 @@ Every solver also has ``solve_batch(circuits, options, x0s=None)``: one launch f
 """
 import math
 
+import os
+import sys
+import time
+
 import numpy as np
 
 from . import _lib
@@ -105,7 +109,15 @@ class Solver:
                 chunks.append(p)
                 owner.append(ci)
         flat = np.concatenate(chunks) if chunks else np.zeros(0)
+        trace = os.environ.get("QSB_TRACE_SOLVES")
+        t0 = time.perf_counter() if trace else 0.0
         x, f, iters, status = lib.solve(self.method, gps, poi, flat, T, **self._solve_opts(options, frontier))
+        if trace:  # one line per batched solve: size, parameter counts, wall, iteration tail, how the instances ended
+            st = np.asarray(status)
+            print("[qsb solve] {} instances={} programs={} P={}..{} wall_ms={:.1f} iters median={} max={} status={} best_f={:.2e}".format(
+                self.method, len(poi), len(gps), min(g.n_params for g in gps), max(g.n_params for g in gps),
+                1e3 * (time.perf_counter() - t0), int(np.median(iters)), int(np.max(iters)),
+                {int(k): int((st == k).sum()) for k in np.unique(st)}, float(np.min(f))), file=sys.stderr, flush=True)
         owner = np.asarray(owner)
         offs = np.concatenate([[0], np.cumsum([gps[c].n_params for c in owner])]).astype(np.int64)
         best_x, best_f, best_it, best_st = [], [], [], []

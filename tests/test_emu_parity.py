@@ -253,12 +253,15 @@ def test_general_lm_kernel_for_a_non_unitary_target():
         assert abs(0.5 * r @ r - 0.5 * 8 * 0.2 ** 2) < 1e-9  # U T^dagger = 0.8 I at the optimum: |0.8 I - I|^2 / 2
 
 
-def test_batch_stop_rules():
+@pytest.mark.parametrize("kernel", ["lm3", "lm2"])
+def test_batch_stop_rules(kernel, monkeypatch):
     """qsb_solver_opts.straggler_factor / sibling_stop: off by default (every start runs to its own convergence); with a
-    sibling threshold the other starts of a solved circuit stop (status 7) and the best result is unchanged."""
+    sibling threshold the other starts of a solved circuit stop (status 7) and the best result is unchanged.  Both the
+    body-frame kernel and the general one (circuits too long for the former's shared-memory factor) implement them."""
     from oracle import qs_oracle as O
     from qsearch_b200 import gates, gatesets, lowering
     lib = emulated_library()
+    monkeypatch.setenv("QSB_LM_KERNEL", kernel)
     rng = np.random.default_rng(17)
     g = gatesets.QubitCNOTLinear()
     c = gates.ProductGate(g.initial_layer(3)).appending(g.search_layers(3)[0][0]).appending(g.search_layers(3)[1][0])

@@ -296,8 +296,11 @@ def test_body_frame_lm_agrees_with_the_general_kernel(lib, monkeypatch):
                 assert abs(O.matrix_distance_squared(T, O.matrix(c, x3.reshape(K, -1)[k])) - f3[k]) < 1e-12
 
 
-def test_batch_stop_rules(lib):
-    """Straggler cap and sibling stop (qsb_solver_opts): fewer iterations, same best value, consistent outputs."""
+@pytest.mark.parametrize("kernel", ["lm3", "lm2"])
+def test_batch_stop_rules(lib, kernel, monkeypatch):
+    """Straggler cap and sibling stop (qsb_solver_opts): fewer iterations, same best value, consistent outputs; in the
+    body-frame kernel and in the general one that takes over for circuits too long for it."""
+    monkeypatch.setenv("QSB_LM_KERNEL", kernel)
     rng = np.random.default_rng(5)
     g = gatesets.QubitCNOTLinear()
     layers = g.search_layers(4)
