@@ -6,6 +6,7 @@ context created on first use, so the package can be imported before a fork (SURV
 If the library is missing, or no CUDA device is visible, every entry point raises -- there is no other path.
 """
 import ctypes
+import time
 import os
 import threading
 
@@ -280,8 +281,10 @@ class Library:
             iters = np.empty(len(poi), dtype="int32")
             status = np.empty(len(poi), dtype="int32")
             fn = self.dll.qsb_solve_lm if method == "lm" else self.dll.qsb_solve_lbfgs
+            t0 = time.perf_counter()
             self.check(fn(self.ctx, len(gps), handles, len(poi), poi.ctypes.data_as(_c_ip), _dp(x0), T.ctypes.data_as(_c_dp),
                           ctypes.byref(opts), _dp(x), _dp(f), iters.ctypes.data_as(_c_ip), status.ctypes.data_as(_c_ip)))
+            self.last_solve_call_ms = 1e3 * (time.perf_counter() - t0)  # the C call alone (QSB_TRACE_SOLVES prints it)
         return x, f, iters, status
 
     def eval_lm_system_static(self, gp, params, target, slot=0):

@@ -352,6 +352,10 @@ int qsb_pool_reserve(const QsbDevice& d, QsbBuf& b, size_t bytes) {
 
 int qsb_buf_reserve(QsbBuf& b, size_t bytes) {
   if (bytes <= b.bytes) return QSB_OK;
+  // grow by at least half: a search asks for a little more with every layer it adds (the solver scratch is proportional to P),
+  // and a cudaFree + cudaMalloc of several hundred MB per frontier expansion is not free
+  bytes = std::max(bytes, b.bytes + b.bytes / 2);
+  bytes = (bytes + ((size_t)2 << 20) - 1) & ~(((size_t)2 << 20) - 1);
   if (b.p) { cudaFree(b.p); b.p = nullptr; b.bytes = 0; }
   cudaError_t e = cudaMalloc(&b.p, bytes);
   if (e != cudaSuccess) {

@@ -114,9 +114,9 @@ class Solver:
         x, f, iters, status = lib.solve(self.method, gps, poi, flat, T, **self._solve_opts(options, frontier))
         if trace:  # one line per batched solve: size, parameter counts, wall, iteration tail, how the instances ended
             st = np.asarray(status)
-            print("[qsb solve] {} instances={} programs={} P={}..{} wall_ms={:.1f} iters median={} max={} status={} best_f={:.2e}".format(
+            print("[qsb solve] {} instances={} programs={} P={}..{} wall_ms={:.1f} c_call_ms={:.1f} iters median={} max={} status={} best_f={:.2e}".format(
                 self.method, len(poi), len(gps), min(g.n_params for g in gps), max(g.n_params for g in gps),
-                1e3 * (time.perf_counter() - t0), int(np.median(iters)), int(np.max(iters)),
+                1e3 * (time.perf_counter() - t0), getattr(lib, "last_solve_call_ms", float("nan")), int(np.median(iters)), int(np.max(iters)),
                 {int(k): int((st == k).sum()) for k in np.unique(st)}, float(np.min(f))), file=sys.stderr, flush=True)
         owner = np.asarray(owner)
         offs = np.concatenate([[0], np.cumsum([gps[c].n_params for c in owner])]).astype(np.int64)
