@@ -172,3 +172,23 @@ def test_frontier_sizing_and_stop_rule_plumbing(emu):
     assert plain["gram_tf32"] == 0.0 and front["gram_tf32"] == 1.0
     assert solvers.LeastSquares_Jac_Solver(gram_tf32=False)._solve_opts(opts, frontier=True)["gram_tf32"] == 0.0
     assert solvers.LeastSquares_Jac_Solver(straggler_factor=0.0)._solve_opts(opts, frontier=True)["straggler_factor"] == 0.0
+
+
+def test_qutrit_search_and_multistart(emu):
+    """d = 3 through the host code of the search (gatesets.py:283-305, compiler.py:70-78): the qudit count comes from
+    log_d of the target's size, the gateset's layers lower to radix-3 programs, SearchCompiler finds a one-layer two-qutrit
+    target with one two-qutrit gate, and MultiStart_Solver solves a single-qutrit gate."""
+    g = gatesets.QutritCNOTLinear()
+    assert g.d == 3 and gatesets.DefaultQutrit is gatesets.QutritCPIPhaseLinear
+    c = gates.ProductGate(g.initial_layer(2)).appending(g.search_layers(2)[0][0])
+    T = O.matrix(c, np.random.default_rng(8).random(c.num_inputs) * 2 * np.pi)
+    res = q.SearchCompiler().compile(q.Options(target=T, gateset=g, seed=5, timeout=300))
+    assert O.matrix_distance_squared(T, O.matrix(res["structure"], res["parameters"])) < 1e-10
+    assert repr(res["structure"]).count("UpgradedConstantGate") == 1
+    with pytest.raises(ValueError):  # an 8 x 8 target is not a whole number of qutrits (compiler.py:72-73)
+        q.SearchCompiler().compile(q.Options(target=unitaries.qft(8), gateset=g))
+    sq = gates.SingleQutritGate()
+    T1 = O.matrix(sq, np.random.default_rng(1).random(8) * 6)
+    opts = q.Options(target=T1, gateset=g, solver=solvers.MultiStart_Solver(2), seed=3)
+    U, x = opts.solver.solve_for_unitary(sq, opts)
+    assert O.matrix_distance_squared(T1, O.matrix(sq, x)) < 1e-10 and np.abs(U - O.matrix(sq, x)).max() < 1e-12
