@@ -35,8 +35,7 @@ def main():
         if gs is None:
             T = tg["unreachable"]
         elif "reachable" in name:
-            from oracle import qs_oracle as O  # tools only: a target the first child reaches exactly
-            from qsearch_b200 import gates
+            from qsearch_b200 import gates, lowering as _low  # a target the first child reaches exactly
             rng = np.random.default_rng(1)
             layers = gs.search_layers(n)
             c = gates.ProductGate(gs.initial_layer(n))
@@ -44,7 +43,7 @@ def main():
             for _ in range(depth - 1):
                 c = c.appending(layers[int(rng2.integers(len(layers)))][0])
             c = c.appending(layers[0][0])
-            T = O.matrix(c, rng.random(c.num_inputs) * 2 * np.pi)
+            T = lib.eval_matrix([_low.lower(c)], [0], rng.random(c.num_inputs) * 2 * np.pi)[0]
         else:
             T = unitaries.qft(1 << n)
         lib.solve("lm", gps[:1], poi[:1] * 0, x0[:gps[0].n_params], T)
