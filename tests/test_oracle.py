@@ -82,6 +82,31 @@ def test_oracle_against_live_reference():
         assert abs(f - fo) < TOL and np.abs(g - go).max() < TOL
 
 
+@pytest.mark.reference
+def test_oracle_against_live_reference_on_qutrits():
+    """The same on qutrit circuits (gates.py:411-602, gatesets.py:283-305): fresh random inputs, the reference's own trees."""
+    import sys
+    sys.path.insert(0, "/root/reference")
+    from qsearch import gatesets as rgs, gates as rg, comparison as rc
+    from qsearch_b200 import workloads
+    rng = np.random.default_rng(101)
+    np.random.seed(3)  # CPIPhaseGate draws its phases when it is made (gates.py:590); the oracle reads them off the object
+    for gs, n in [(rgs.QutritCNOTLinear(), 2), (rgs.QutritCPIPhaseLinear(), 2), (rgs.QutritCNOTLinear(), 3)]:
+        layers = gs.search_layers(n)
+        c = rg.ProductGate(gs.initial_layer(n))
+        for _ in range(3):
+            c = c.appending(layers[int(rng.integers(len(layers)))][0])
+        x = rng.random(c.num_inputs) * 2 * np.pi
+        T = workloads.haar_unitary(3 ** n, 5 + n)
+        U, J = c.mat_jac(x)
+        Uo, Jo = O.mat_jac(c, x)
+        assert np.abs(U - Uo).max() < TOL and max(np.abs(a - b).max() for a, b in zip(J, Jo)) < TOL
+        assert np.abs(rc.matrix_residuals_jac(T, U, J) - O.matrix_residuals_jac(T, Uo, Jo)).max() < TOL
+        f, g = rc.matrix_distance_squared_jac(T, U, J)
+        fo, go = O.matrix_distance_squared_jac(T, Uo, Jo)
+        assert abs(f - fo) < TOL and np.abs(g - go).max() < TOL
+
+
 def test_aposmm_start_selection_matches_the_reference():
     """MultiStart_Solver's start points (qsearch/multistart_solvers.py:66-88): `solvers.aposmm_start_indices` against indices
     produced by the reference's own persistent_aposmm functions (tests/golden/make_golden_aposmm.py): 22 seeded samples,
