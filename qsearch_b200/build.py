@@ -100,28 +100,33 @@ def build_cuda(force=False, verbose=False, only=None):
     return LIB
 
 
-def build_emu(force=False):
-    """TEST INFRASTRUCTURE: compile the same .cu sources for the host with tests/emu/cuda_emu.h."""
+def build_emu(force=False, sanitize=None):
+    """TEST INFRASTRUCTURE: compile the same .cu sources for the host with tests/emu/cuda_emu.h.
+    sanitize = "address" | "undefined": an instrumented copy (own directory) for tests/emu/run_sanitized.py."""
     hdr = os.path.join(ROOT, "tests", "emu", "cuda_emu.h")
     deps = _sources() + [hdr]
-    if not force and not _stale(EMU_LIB, deps):
-        return EMU_LIB
-    os.makedirs(EMU_DIR, exist_ok=True)
+    out_dir = EMU_DIR if not sanitize else os.path.join(EMU_DIR, sanitize)
+    lib = EMU_LIB if not sanitize else os.path.join(out_dir, "libqsb200_emu_{}.so".format(sanitize))
+    if not force and not _stale(lib, deps):
+        return lib
+    os.makedirs(out_dir, exist_ok=True)
+    opt = ["-O2"] if not sanitize else ["-O1", "-g", "-fno-omit-frame-pointer", "-fsanitize=" + sanitize, "-fno-sanitize=vptr"]
     jobs, objs = [], []
     for name, src, defs in UNITS:
-        obj = os.path.join(EMU_DIR, name + ".o")
+        obj = os.path.join(out_dir, name + ".o")
         objs.append(obj)
         if force or _stale(obj, _unit_deps(src) + [hdr]):
-            jobs.append((obj, ["g++", "-x", "c++", "-std=c++20", "-O2", "-fPIC", "-pthread", "-DQSB_EMU"] +
+            jobs.append((obj, ["g++", "-x", "c++", "-std=c++20"] + opt + ["-fPIC", "-pthread", "-DQSB_EMU"] +
                          (["-DQSB_EMU_DEFINE"] if name == "api" else []) + defs +
                          ["-include", hdr, "-c", "-o", obj, os.path.join(CSRC, src)]))
     _compile_all(jobs, False)
-    subprocess.run(["g++", "-shared", "-pthread", "-o", EMU_LIB] + objs, check=True)
-    return EMU_LIB
+    subprocess.run(["g++", "-shared", "-pthread"] + (["-fsanitize=" + sanitize] if sanitize else []) + ["-o", lib] + objs, check=True)
+    return lib
 
 
 if __name__ == "__main__":
     if "--emu" in sys.argv:
-        print(build_emu(force="--force" in sys.argv))
+        san = sys.argv[sys.argv.index("--sanitize") + 1] if "--sanitize" in sys.argv else None
+        print(build_emu(force="--force" in sys.argv, sanitize=san))
     else:
         print(build_cuda(force="--force" in sys.argv, verbose="-v" in sys.argv))
